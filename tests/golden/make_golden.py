@@ -1,0 +1,156 @@
+"""Generate golden fixtures from the REFERENCE itself (build container only).
+
+Runs /root/reference's own PyTorch modules (TTSModel built by its own constructors) on the
+deterministic weights of `oracle.pocket_oracle.make_weights`, with token ids, voice
+conditioning and noise injected, in the decomposed order of FlowLMModel.forward
+(flow_lm.py:121-139) so the noise is an input instead of an RNG draw.  Outputs are stored
+as tests/golden/<case>.npz.  /root/reference does not exist on the GPU box; the fixtures
+are what travels.
+
+    python tests/golden/make_golden.py            # regenerates every fixture
+"""
+
+import sys
+from functools import partial
+from pathlib import Path
+
+import numpy as np
+import torch
+
+ROOT = Path(__file__).resolve().parents[2]
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, "/root/reference")
+
+import pocket_tts.conditioners.text as _text  # noqa: E402
+
+
+class _StubTokenizer:  # the only network dependency on the construction path (text.py:26-29)
+    def __init__(self, nbins, tokenizer_path):
+        self.sp = None
+
+
+_text.SentencePieceTokenizer = _StubTokenizer
+
+from pocket_tts.models.flow_lm import lsd_decode  # noqa: E402
+from pocket_tts.models.tts_model import TTSModel  # noqa: E402
+from pocket_tts.modules.stateful_module import increment_steps, init_states  # noqa: E402
+from pocket_tts.utils.config import CONFIGS_DIR, load_config  # noqa: E402
+
+from oracle import pocket_oracle as po  # noqa: E402
+
+ENCODE_ONLY = ("mimi.encoder.", "mimi.encoder_transformer.", "mimi.downsample.")
+
+
+def build_reference(config_name: str, n_layers: int, weights: dict, lsd_steps: int):
+    cfg = load_config(CONFIGS_DIR / f"{config_name}.yaml")
+    cfg.weights_path = None
+    cfg.weights_path_without_voice_cloning = None
+    cfg.flow_lm.transformer.num_layers = n_layers
+    torch.manual_seed(0)
+    m = TTSModel._from_pydantic_config_with_weights(cfg, 0.7, lsd_steps, None, -4.0).eval()
+    sd = {k: v for k, v in weights.items()}
+    res = m.load_state_dict(sd, strict=False)
+    assert not res.unexpected_keys, res.unexpected_keys
+    bad = [k for k in res.missing_keys if not k.startswith(ENCODE_ONLY)]
+    assert not bad, bad
+    return m
+
+
+@torch.no_grad()
+def run_reference_stream(m, cond, tokens, noise, keep_kv_layers=()):
+    """One stream at B=1 through the reference modules. cond [1,P,1024] (bos row included),
+    tokens [1,T], noise [G,1,32]."""
+    fl = m.flow_lm
+    G = noise.shape[0]
+    T = tokens.shape[1]
+    # voice prefill (tts_model.py:896-899)
+    state = init_states(fl, batch_size=1, sequence_length=cond.shape[1])
+    m._run_flow_lm_and_increment_step(model_state=state, audio_conditioning=cond)
+    voice_kv = {f"voice_kv_{i}": state[f"transformer.layers.{i}.self_attn"]["cache"].numpy().copy()
+                for i in keep_kv_layers}
+    # text prefill (tts_model.py:718-725)
+    m._expand_kv_cache(state, sequence_length=cond.shape[1] + T + G)
+    m._run_flow_lm_and_increment_step(model_state=state, text_tokens=tokens)
+    # AR loop, decomposed (flow_lm.py:121-139) with injected noise
+    mimi_state = init_states(m.mimi, batch_size=1, sequence_length=G * 16)
+    prev = torch.full((1, 1, fl.ldim), float("nan"))
+    empty = torch.empty((1, 0, fl.dim))
+    lat, logit, pcm = [], [], []
+    for g in range(G):
+        seq = torch.where(torch.isnan(prev), fl.bos_emb, prev)
+        h = fl.backbone(fl.input_linear(seq), empty, seq, model_state=state)[:, -1]
+        logit.append(fl.out_eos(h)[0, 0])
+        latent = lsd_decode(partial(fl.flow_net, h), noise[g].clone(), m.lsd_decode_steps)
+        increment_steps(fl, state, increment=1)
+        lat.append(latent[0])
+        # tts_model.py:449-455
+        x = (latent[:, None, :] * fl.emb_std + fl.emb_mean).transpose(-1, -2)
+        audio = m.mimi.decode_from_latent(m.mimi.quantizer(x), mimi_state)
+        increment_steps(m.mimi, mimi_state, increment=16)
+        pcm.append(audio[0, 0])
+        prev = latent[:, None, :]
+    return torch.stack(lat), torch.stack(logit), torch.cat(pcm), voice_kv
+
+
+@torch.no_grad()
+def run_reference_mimi(m, latents):
+    """latents [G,1,32] -> pcm [G*1920] through the reference Mimi decode worker math."""
+    fl = m.flow_lm
+    G = latents.shape[0]
+    mimi_state = init_states(m.mimi, batch_size=1, sequence_length=G * 16)
+    out = []
+    for g in range(G):
+        x = (latents[g][:, None, :] * fl.emb_std + fl.emb_mean).transpose(-1, -2)
+        audio = m.mimi.decode_from_latent(m.mimi.quantizer(x), mimi_state)
+        increment_steps(m.mimi, mimi_state, increment=16)
+        out.append(audio[0, 0])
+    return torch.cat(out)
+
+
+def case_generate(name, preset, n_layers, streams, G, lsd_steps, seed, keep_kv_layers=()):
+    dims = po.ModelDims(n_layers=n_layers)
+    W = po.make_weights(dims, seed=0)
+    ref = build_reference(preset, n_layers, W, lsd_steps)
+    g = torch.Generator().manual_seed(seed)
+    out = dict(n_layers=n_layers, lsd_steps=lsd_steps, G=G, n_streams=len(streams),
+               torch_version=str(torch.__version__), weights_seed=0)
+    for si, (P, T) in enumerate(streams):
+        cond = torch.randn(1, P, dims.d_model, generator=g) * 0.3
+        tokens = torch.randint(0, dims.n_bins, (1, T), generator=g)
+        noise = torch.randn(G, 1, dims.ldim, generator=g) * (0.7 ** 0.5)
+        full_cond = torch.cat([ref.flow_lm.bos_before_voice, cond], dim=1)
+        lat, logit, pcm, vkv = run_reference_stream(ref, full_cond, tokens, noise,
+                                                    keep_kv_layers if si == 0 else ())
+        out[f"cond_{si}"] = cond[0].numpy()
+        out[f"tokens_{si}"] = tokens[0].numpy()
+        out[f"noise_{si}"] = noise[:, 0].numpy()
+        out[f"latents_{si}"] = lat.numpy()
+        out[f"eos_logits_{si}"] = logit.numpy()
+        out[f"pcm_{si}"] = pcm.numpy()
+        out.update(vkv)
+        print(name, "stream", si, "P", P, "T", T, "pcm rms", float(pcm.pow(2).mean().sqrt()),
+              "lat rms", float(lat.pow(2).mean().sqrt()))
+    np.savez_compressed(Path(__file__).parent / f"{name}.npz", **out)
+
+
+def case_mimi(name, G, seed):
+    dims = po.ModelDims(n_layers=1)
+    W = po.make_weights(dims, seed=0)
+    ref = build_reference("english", 1, W, 1)
+    g = torch.Generator().manual_seed(seed)
+    latents = torch.randn(G, 1, dims.ldim, generator=g)
+    pcm = run_reference_mimi(ref, latents)
+    print(name, "pcm rms", float(pcm.pow(2).mean().sqrt()))
+    np.savez_compressed(Path(__file__).parent / f"{name}.npz", latents=latents[:, 0].numpy(),
+                        pcm=pcm.numpy(), G=G, torch_version=str(torch.__version__), weights_seed=0)
+
+
+if __name__ == "__main__":
+    torch.set_num_threads(8)
+    # (voice length P without the bos row, text tokens T)
+    case_generate("gen_2l", "english", 2, [(20, 12), (33, 9), (7, 5)], G=6, lsd_steps=1, seed=11,
+                  keep_kv_layers=(0, 1))
+    case_generate("gen_2l_lsd2", "english", 2, [(11, 7)], G=3, lsd_steps=2, seed=12)
+    case_generate("gen_english_6l", "english", 6, [(40, 16), (25, 10)], G=6, lsd_steps=1, seed=13)
+    case_generate("gen_italian_24l", "italian_24l", 24, [(18, 8)], G=3, lsd_steps=1, seed=14)
+    case_mimi("mimi_20f", G=20, seed=15)
