@@ -1,0 +1,147 @@
+/*
+ * pocket_tts_b200 — C ABI of the B200-native per-frame generation engine.
+ *
+ * This header is the drop-in boundary for the hot path of kyutai-labs/pocket-tts
+ * (SURVEY.md section 8b).  The reference has no FFI of its own: its boundary is the Python
+ * API in pocket_tts/models/tts_model.py, so every entry point below cites the reference
+ * Python function whose work it replaces.  Plain pointers and sizes only, no torch types;
+ * every call returns 0 on success or a negative PTTS_E* code, with a thread-local message
+ * available from ptts_last_error().  No C++ exception crosses this boundary.
+ *
+ * Pointers named *_any may be host (pageable or pinned) or device pointers; they are
+ * copied with cudaMemcpyAsync(cudaMemcpyDefault) on the engine stream.  All floats are
+ * IEEE fp32 on the ABI regardless of the engine's internal precision mode.
+ */
+#ifndef POCKET_TTS_B200_H
+#define POCKET_TTS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PTTS_OK 0
+#define PTTS_EINVAL (-1)   /* bad argument / unknown tensor name / shape mismatch  */
+#define PTTS_ECUDA (-2)    /* CUDA runtime error (message holds cudaGetErrorString) */
+#define PTTS_ESTATE (-3)   /* call order violated (e.g. step before finalize)       */
+#define PTTS_ENOSLOT (-4)  /* no free stream slot / capacity exceeded               */
+
+#define PTTS_PRECISION_FP32 0 /* fp32 storage, FFMA accumulate: parity mode (rel-L2 <= 1e-4) */
+#define PTTS_PRECISION_BF16 1 /* bf16 weights/activations/KV, fp32 accumulate (tcgen05)     */
+
+/* Architecture of the model, mirrors pocket_tts/utils/config.py:11-118 (the YAML schema)
+ * for the fields the decode path uses (config/english.yaml:7-60). */
+typedef struct ptts_config {
+  int32_t n_layers;       /* flow_lm.transformer.num_layers: 6 or 24              */
+  int32_t d_model;        /* 1024                                                  */
+  int32_t n_heads;        /* 16                                                    */
+  int32_t ffn;            /* d_model * hidden_scale = 4096                         */
+  int32_t ldim;           /* mimi.quantizer.dimension = 32                         */
+  int32_t flow_dim;       /* flow.dim = 512                                        */
+  int32_t flow_depth;     /* flow.depth = 6                                        */
+  int32_t mimi_d;         /* mimi.transformer.d_model = 512                        */
+  int32_t mimi_heads;     /* 8                                                     */
+  int32_t mimi_layers;    /* 2                                                     */
+  int32_t mimi_ffn;       /* 2048                                                  */
+  int32_t mimi_context;   /* 250                                                   */
+  int32_t n_filters;      /* seanet.n_filters = 64                                 */
+  int32_t ratios[3];      /* seanet.ratios = 6,5,4                                 */
+  int32_t kernel;         /* seanet.kernel_size = 7                                */
+  int32_t res_kernel;     /* seanet.residual_kernel_size = 3                       */
+  int32_t last_kernel;    /* seanet.last_kernel_size = 3                           */
+  int32_t upsample_stride;/* encoder_frame_rate / frame_rate = 16                  */
+  /* engine sizing */
+  int32_t max_streams;    /* stream slots resident on this GPU                     */
+  int32_t kv_capacity;    /* FlowLM positions per slot (voice + text + frames)     */
+  int32_t max_prefill_rows; /* max sum of rows in one ptts_prefill call            */
+  int32_t max_lsd_steps;  /* rows accepted for the "flow.tcomb" table              */
+  int32_t precision;      /* PTTS_PRECISION_*                                      */
+  int32_t device;         /* CUDA ordinal                                          */
+} ptts_config;
+
+typedef struct ptts_engine ptts_engine;
+
+const char* ptts_last_error(void);
+int ptts_version(void);
+
+/* TTSModel._from_pydantic_config_with_weights (tts_model.py:130-230): build the model. */
+int ptts_engine_create(const ptts_config* cfg, ptts_engine** out);
+int ptts_engine_destroy(ptts_engine* e);
+
+/* load_state_dict (tts_model.py:209-210): one call per state_dict entry, names exactly as in
+ * TTSModel.state_dict() ("flow_lm.transformer.layers.0.self_attn.in_proj.weight", ...).
+ * Encode-only / unknown names return PTTS_EINVAL unless they start with an ignorable prefix
+ * (mimi.encoder*, mimi.downsample*), which return PTTS_OK and are skipped.  Two derived,
+ * input-independent tables are loaded the same way: "rope.freqs" [head_dim/2]
+ * (rope.py:28-29) and "flow.tcomb" [lsd_steps, flow_dim] (mlp.py:205-209 evaluated at
+ * s=i/n, t=(i+1)/n, flow_lm.py:33-37). */
+int ptts_load_tensor(ptts_engine* e, const char* name, const float* host_data,
+                     const int64_t* shape, int32_t ndim);
+/* Checks that every required tensor arrived and freezes the weights. */
+int ptts_finalize(ptts_engine* e);
+
+/* init_states (stateful_module.py:7-16): a slot owns a FlowLM KV cache (offset 0) and a fresh
+ * Mimi decoder state (tts_model.py:444). */
+int ptts_stream_open(ptts_engine* e, int32_t* slot_out);
+int ptts_stream_close(ptts_engine* e, int32_t slot);
+/* Fresh Mimi state + BOS previous-latent for the slot; FlowLM KV is kept (new text chunk on a
+ * forked voice state, tts_model.py:637-658). */
+int ptts_stream_reset_decoder(ptts_engine* e, int32_t slot);
+/* copy.deepcopy(model_state) (tts_model.py:637-638): dst gets src's FlowLM KV prefix+offset. */
+int ptts_stream_fork(ptts_engine* e, int32_t src_slot, int32_t dst_slot);
+/* model_state import/export in the reference layout cache[2, 1, P, H, D] per layer
+ * (transformer.py:46-57, tts_model.py:1047-1072). */
+int ptts_stream_import_kv(ptts_engine* e, int32_t slot, int32_t layer, const float* cache_any,
+                          int32_t n_positions);
+int ptts_stream_export_kv(ptts_engine* e, int32_t slot, int32_t layer, float* cache_any,
+                          int32_t n_positions);
+int ptts_stream_set_offset(ptts_engine* e, int32_t slot, int32_t offset);
+int ptts_stream_get_offset(ptts_engine* e, int32_t slot, int32_t* offset_out);
+/* Teacher forcing for parity tests: overwrite the fed-back latent (tts_model.py:768). */
+int ptts_stream_set_prev_latent(ptts_engine* e, int32_t slot, const float* latent_any);
+
+/* _run_flow_lm_and_increment_step with text / audio conditioning (tts_model.py:317-346,
+ * 722-725, 896-899): rows are already-embedded conditioning vectors [sum(lens), d_model],
+ * stream i owning lens[i] consecutive rows; only the KV cache is kept (the reference discards
+ * the sampled latent of a prefill call, tts_model.py:723-725). */
+int ptts_prefill(ptts_engine* e, int32_t n, const int32_t* slots, const int32_t* lens,
+                 const float* embeds_any);
+
+/* One frame for n streams: FlowLM step + flow head (+ optional Mimi decode).
+ * _autoregressive_generation body (tts_model.py:756-768) + _decode_audio_worker body
+ * (tts_model.py:449-455).  noise_any [n, ldim] is the injected N(0, temp) draw
+ * (flow_lm.py:131-137).  Outputs may be NULL.  out_eos_logit is out_eos(h) before the
+ * threshold (flow_lm.py:129) so callers apply eos_threshold themselves. */
+int ptts_step(ptts_engine* e, int32_t n, const int32_t* slots, const float* noise_any,
+              int32_t lsd_steps, int32_t decode_audio, float* out_latents_any,
+              float* out_eos_logit_any, float* out_pcm_any);
+
+/* MimiModel.decode_from_latent on explicit latents (mimi.py:89-94; BASELINE config 4). */
+int ptts_mimi_decode(ptts_engine* e, int32_t n, const int32_t* slots, const float* latents_any,
+                     float* out_pcm_any);
+
+/* Device-resident multi-frame loop for throughput runs: n_frames frames back to back with
+ * noise [n_frames, n, ldim] already on the device, PCM written to a device buffer
+ * [n, n_frames*1920] (or NULL), no host round trip in between (CUDA-graph replay). */
+int ptts_run_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames,
+                    const float* noise_dev, int32_t lsd_steps, float* out_pcm_dev,
+                    float* out_latents_dev);
+
+int ptts_synchronize(ptts_engine* e);
+/* Number of engine kernels launched (or replayed through a graph) since creation. */
+int64_t ptts_launch_count(ptts_engine* e);
+/* CUDA stream the engine launches on (for event timing by the caller), as a void*. */
+void* ptts_stream_handle(ptts_engine* e);
+/* Enable / disable CUDA-graph replay of the frame step (default on). */
+int ptts_set_graphs(ptts_engine* e, int32_t enabled);
+
+/* Debug taps for per-kernel parity tests: copy a named internal activation buffer
+ * (fp32-converted) to out_any; returns the element count through n_out. */
+int ptts_debug_read(ptts_engine* e, const char* what, float* out_any, int64_t max_elems,
+                    int64_t* n_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* POCKET_TTS_B200_H */

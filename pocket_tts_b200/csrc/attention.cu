@@ -1,0 +1,290 @@
+// Streaming attention kernels (transformer.py:135-158, rope.py:28-58) with per-stream
+// offsets.  RoPE, the KV append and the softmax(QK^T)V read are fused: q/k/v of the new
+// position(s) are read once from the packed projection, K/V are streamed once from HBM.
+//
+// Layout: one (stream, head) pair per CTA.  Each lane owns the interleaved RoPE pair
+// (2*lane, 2*lane+1) of the 64-wide head, so a K or V row is one coalesced 256 B (fp32) /
+// 128 B (bf16) warp load, the rotation needs no shuffles, and the score is a 5-step
+// butterfly.  Warps split the positions and are merged with a log-sum-exp combine.
+#include "kernels.cuh"
+
+namespace ptts {
+
+template <typename TK>
+__device__ __forceinline__ TK* kv_row(const KvGeom& g, int layer, int slot, int kv, int h, int pos) {
+  const int p = g.ring ? (pos & (g.cap - 1)) : pos;
+  const long long idx = ((((long long)layer * g.n_slots + slot) * 2 + kv) * g.H + h) * g.cap + p;
+  return reinterpret_cast<TK*>(g.base) + idx * g.D;
+}
+
+__device__ __forceinline__ float2 rope_pair(float2 x, float pos, float freq) {
+  // rope.py:42-50: angle = freq * position in fp32; (r, i) -> (r cos - i sin, r sin + i cos)
+  float s, c;
+  sincosf(freq * pos, &s, &c);
+  return make_float2(x.x * c - x.y * s, x.x * s + x.y * c);
+}
+
+// online-softmax state of one warp for one query: running max m, sum l, accumulator pair
+struct OnlineSm {
+  float m, l;
+  float2 acc;
+};
+
+// scores of 4 consecutive positions p..p+3 (count valid), lane-owned q pair, D == 64
+template <typename TK>
+__device__ __forceinline__ void attend4(OnlineSm& s, const TK* __restrict__ kbase,
+                                        const TK* __restrict__ vbase, int idx0, int count,
+                                        float2 q, float scale, int lane) {
+  float2 kk[4], vv[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if (j < count) {
+      kk[j] = load2(kbase + (long long)(idx0 + j) * 64 + 2 * lane);
+      vv[j] = load2(vbase + (long long)(idx0 + j) * 64 + 2 * lane);
+    } else {
+      kk[j] = make_float2(0.f, 0.f);
+      vv[j] = make_float2(0.f, 0.f);
+    }
+  }
+  float sc[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) sc[j] = q.x * kk[j].x + q.y * kk[j].y;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) sc[j] += __shfl_xor_sync(0xffffffffu, sc[j], o);
+  }
+  float mx = s.m;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    sc[j] = (j < count) ? sc[j] * scale : -INFINITY;
+    mx = fmaxf(mx, sc[j]);
+  }
+  const float corr = expf(s.m - mx);  // s.m == -inf on first use -> 0
+  s.l *= corr;
+  s.acc.x *= corr;
+  s.acc.y *= corr;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float p = expf(sc[j] - mx);  // -inf -> 0
+    s.l += p;
+    s.acc.x = fmaf(p, vv[j].x, s.acc.x);
+    s.acc.y = fmaf(p, vv[j].y, s.acc.y);
+  }
+  s.m = mx;
+}
+
+// =====================================================================================
+// decode: one new position per stream.  grid (H, n), 128 threads.
+// =====================================================================================
+template <typename TK, typename TO>
+__global__ void __launch_bounds__(128)
+attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs,
+                   const int* __restrict__ offsets, const int* __restrict__ slot_ids, KvGeom g,
+                   int layer, TO* __restrict__ out) {
+  constexpr int NW = 4;
+  __shared__ float sm_m[NW], sm_l[NW];
+  __shared__ float2 sm_acc[NW][32];
+  const int h = blockIdx.x, i = blockIdx.y;
+  const int slot = slot_ids[i];
+  const int pos = offsets[slot];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int d_model = g.H * 64;
+  const float* row = qkv + (long long)i * 3 * d_model + h * 64 + 2 * lane;
+  const float fr = freqs[lane];
+
+  // every warp rotates q redundantly (registers); warp 0 appends k and v
+  const float2 q = rope_pair(load2(row), (float)pos, fr);
+  if (w == 0) {
+    const float2 k = rope_pair(load2(row + d_model), (float)pos, fr);
+    const float2 v = load2(row + 2 * d_model);
+    store2(kv_row<TK>(g, layer, slot, 0, h, pos) + 2 * lane, k);
+    store2(kv_row<TK>(g, layer, slot, 1, h, pos) + 2 * lane, v);
+  }
+  __syncthreads();  // appended row visible to the block
+
+  const TK* kbase = kv_row<TK>(g, layer, slot, 0, h, 0);
+  const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0);
+  const int L = pos + 1;
+  OnlineSm s{-INFINITY, 0.0f, make_float2(0.f, 0.f)};
+  for (int p0 = w * 4; p0 < L; p0 += NW * 4) {
+    const int cnt = min(4, L - p0);
+    attend4<TK>(s, kbase, vbase, p0, cnt, q, 0.125f, lane);
+  }
+  if (lane == 0) { sm_m[w] = s.m; sm_l[w] = s.l; }
+  sm_acc[w][lane] = s.acc;
+  __syncthreads();
+  if (w == 0) {
+    float m = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) m = fmaxf(m, sm_m[j]);
+    float l = 0.0f;
+    float2 a = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+      const float c = expf(sm_m[j] - m);  // warps without positions hold m=-inf -> 0
+      l += sm_l[j] * c;
+      a.x += sm_acc[j][lane].x * c;
+      a.y += sm_acc[j][lane].y * c;
+    }
+    const float inv = 1.0f / l;
+    store2(out + (long long)i * d_model + h * 64 + 2 * lane, make_float2(a.x * inv, a.y * inv));
+  }
+}
+
+cudaError_t launch_attn_decode(const float* qkv, const float* rope_freqs, const int* offsets,
+                               const int* slot_ids, KvGeom kv, int layer, void* out, int out_type,
+                               int n, cudaStream_t st) {
+  if (kv.D != 64) return cudaErrorInvalidValue;
+  dim3 grid(kv.H, n);
+  if (kv.type == 0 && out_type == 0)
+    attn_decode_kernel<float, float><<<grid, 128, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out);
+  else if (kv.type == 1 && out_type == 1)
+    attn_decode_kernel<bf16, bf16><<<grid, 128, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+  else if (kv.type == 0 && out_type == 1)
+    attn_decode_kernel<float, bf16><<<grid, 128, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+  else
+    return cudaErrorInvalidValue;
+  return cudaGetLastError();
+}
+
+// =====================================================================================
+// chunk: len[i] new positions per stream (prefill, Mimi's 16 tokens per frame).
+// grid (H, n), 256 threads.  Phase 1 rotates q in place and appends rotated k / v;
+// phase 2: one warp per query, causal + optional window (transformer.py:22-29).
+// =====================================================================================
+template <typename TK, typename TO>
+__global__ void __launch_bounds__(256)
+attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
+                  const int* __restrict__ offsets, const int* __restrict__ slot_ids,
+                  const int* __restrict__ row_start, const int* __restrict__ lens, KvGeom g, int layer,
+                  int context, TO* __restrict__ out) {
+  constexpr int NW = 8;
+  const int h = blockIdx.x, i = blockIdx.y;
+  const int slot = slot_ids[i];
+  const int off = offsets[slot];
+  const int r0 = row_start[i], T = lens[i];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int d_model = g.H * 64;
+  const float fr = freqs[lane];
+
+  for (int t = w; t < T; t += NW) {
+    float* row = qkv + (long long)(r0 + t) * 3 * d_model + h * 64 + 2 * lane;
+    const float pos = (float)(off + t);
+    store2(row, rope_pair(load2(row), pos, fr));
+    const float2 k = rope_pair(load2(row + d_model), pos, fr);
+    const float2 v = load2(row + 2 * d_model);
+    store2(kv_row<TK>(g, layer, slot, 0, h, off + t) + 2 * lane, k);
+    store2(kv_row<TK>(g, layer, slot, 1, h, off + t) + 2 * lane, v);
+  }
+  __syncthreads();
+
+  const TK* kbase = kv_row<TK>(g, layer, slot, 0, h, 0);
+  const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0);
+  for (int t = w; t < T; t += NW) {
+    const float* row = qkv + (long long)(r0 + t) * 3 * d_model + h * 64 + 2 * lane;
+    const float2 q = load2(row);
+    const int pq = off + t;
+    int lo = pq - context + 1;
+    if (lo < 0) lo = 0;
+    OnlineSm s{-INFINITY, 0.0f, make_float2(0.f, 0.f)};
+    for (int p0 = lo; p0 <= pq; p0 += 4) {
+      int cnt = min(4, pq + 1 - p0);
+      if (g.ring) {
+        // ring storage: the 4 positions may wrap; handle one at a time when they do
+        const int i0 = p0 & (g.cap - 1);
+        if (i0 + cnt > g.cap) {
+          for (int j = 0; j < cnt; ++j) attend4<TK>(s, kbase, vbase, (p0 + j) & (g.cap - 1), 1, q, 0.125f, lane);
+        } else {
+          attend4<TK>(s, kbase, vbase, i0, cnt, q, 0.125f, lane);
+        }
+      } else {
+        attend4<TK>(s, kbase, vbase, p0, cnt, q, 0.125f, lane);
+      }
+    }
+    const float inv = 1.0f / s.l;
+    store2(out + (long long)(r0 + t) * d_model + h * 64 + 2 * lane, make_float2(s.acc.x * inv, s.acc.y * inv));
+  }
+}
+
+cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* offsets,
+                              const int* slot_ids, const int* row_start, const int* lens, KvGeom kv,
+                              int layer, int context, void* out, int out_type, int n, cudaStream_t st) {
+  if (kv.D != 64) return cudaErrorInvalidValue;
+  if (kv.ring && (kv.cap & (kv.cap - 1))) return cudaErrorInvalidValue;
+  dim3 grid(kv.H, n);
+  if (kv.type == 0 && out_type == 0)
+    attn_chunk_kernel<float, float><<<grid, 256, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (float*)out);
+  else if (kv.type == 1 && out_type == 1)
+    attn_chunk_kernel<bf16, bf16><<<grid, 256, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
+  else if (kv.type == 0 && out_type == 1)
+    attn_chunk_kernel<float, bf16><<<grid, 256, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
+  else
+    return cudaErrorInvalidValue;
+  return cudaGetLastError();
+}
+
+// =====================================================================================
+// KV import / export / fork (model_state dict <-> slot)   tts_model.py:637-638,1047-1072
+// reference layout per layer: cache[2, 1, P, H, D]
+// =====================================================================================
+template <typename TK>
+__global__ void kv_import_kernel(const float* __restrict__ ref, KvGeom g, int layer, int slot, int P) {
+  const long long total = 2LL * P * g.H * g.D;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(idx % g.D);
+    long long r = idx / g.D;
+    const int h = (int)(r % g.H); r /= g.H;
+    const int p = (int)(r % P);
+    const int kv = (int)(r / P);
+    kv_row<TK>(g, layer, slot, kv, h, p)[d] = from_f<TK>(ref[idx]);
+  }
+}
+template <typename TK>
+__global__ void kv_export_kernel(float* __restrict__ ref, KvGeom g, int layer, int slot, int P) {
+  const long long total = 2LL * P * g.H * g.D;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(idx % g.D);
+    long long r = idx / g.D;
+    const int h = (int)(r % g.H); r /= g.H;
+    const int p = (int)(r % P);
+    const int kv = (int)(r / P);
+    ref[idx] = to_f(kv_row<TK>(g, layer, slot, kv, h, p)[d]);
+  }
+}
+template <typename TK>
+__global__ void kv_fork_kernel(KvGeom g, int n_layers, int src, int dst, int P) {
+  // copy positions [0,P) of every (layer, kv, head): P*D contiguous elements each
+  const int seg = blockIdx.x;  // layer*2*H + kv*H + h
+  const int h = seg % g.H, kv = (seg / g.H) % 2, layer = seg / (2 * g.H);
+  const TK* s = kv_row<TK>(g, layer, src, kv, h, 0);
+  TK* d = kv_row<TK>(g, layer, dst, kv, h, 0);
+  const int total = P * g.D;
+  for (int idx = threadIdx.x * 4; idx < total; idx += blockDim.x * 4) store4(d + idx, load4(s + idx));
+}
+
+cudaError_t launch_kv_import(const float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st) {
+  if (P <= 0) return cudaSuccess;
+  const int blocks = (int)min(1024LL, (2LL * P * kv.H * kv.D + 255) / 256);
+  if (kv.type == 0) kv_import_kernel<float><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
+  else kv_import_kernel<bf16><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
+  return cudaGetLastError();
+}
+cudaError_t launch_kv_export(float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st) {
+  if (P <= 0) return cudaSuccess;
+  const int blocks = (int)min(1024LL, (2LL * P * kv.H * kv.D + 255) / 256);
+  if (kv.type == 0) kv_export_kernel<float><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
+  else kv_export_kernel<bf16><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
+  return cudaGetLastError();
+}
+cudaError_t launch_kv_fork(KvGeom kv, int n_layers, int src, int dst, int P, cudaStream_t st) {
+  if (P <= 0) return cudaSuccess;
+  const int blocks = n_layers * 2 * kv.H;
+  if (kv.type == 0) kv_fork_kernel<float><<<blocks, 256, 0, st>>>(kv, n_layers, src, dst, P);
+  else kv_fork_kernel<bf16><<<blocks, 256, 0, st>>>(kv, n_layers, src, dst, P);
+  return cudaGetLastError();
+}
+
+}  // namespace ptts

@@ -1,0 +1,90 @@
+// GEMM front-end shared by the SIMT (fp32-exact) and tcgen05 (bf16) back-ends.
+//
+//   D[m, n] = epilogue( sum_k A[m, k] * W[n, k] )        A, W both K-major ("TN")
+//
+// A is addressed through a RowMap so that one kernel covers plain linears, streaming
+// Conv1d (row t of a stream's channels-last buffer is the K*C_in contiguous elements that
+// start at time t: rows overlap, ld = C_in) and K=2S ConvTranspose1d (rows of 2*C_in,
+// ld = C_in, N = S*C_out) — see DESIGN.md "convolutions as overlapping-row GEMMs".
+#pragma once
+#include "common.cuh"
+
+namespace ptts {
+
+struct GemmEpilogue {
+  const float* bias = nullptr;      // [N]
+  const float* colscale = nullptr;  // [N]   LayerScale (layer_scale.py:10-11)
+  const float* gate = nullptr;      // [M, gate_ld] AdaLN gate (mlp.py:107-111)
+  int gate_ld = 0;
+  const void* res = nullptr;        // residual, same element type as `out`
+  RowMap res_map{0, 1 << 30, 1 << 30, 0};
+  float alpha = 1.0f;               // v = alpha * gate * colscale * act_pre(acc + bias) + res
+  int act_pre = ACT_NONE;
+  int act_post = ACT_NONE;          // out = act_post(v); out2 = v
+  void* out = nullptr;
+  RowMap out_map{0, 1 << 30, 1 << 30, 0};
+  void* out2 = nullptr;             // optional pre-act_post copy
+  RowMap out2_map{0, 1 << 30, 1 << 30, 0};
+};
+
+struct GemmProblem {
+  const void* A = nullptr;
+  RowMap a_map{0, 1 << 30, 1 << 30, 0};
+  const void* W = nullptr;  // [N, K] row-major
+  int M = 0, N = 0, K = 0;
+  GemmEpilogue ep;
+};
+
+// element types: 0 = float, 1 = bf16
+cudaError_t gemm_simt_launch(const GemmProblem& p, int in_type, int out_type, cudaStream_t st);
+
+// shared epilogue math (used by both back-ends): returns v (pre act_post)
+template <typename TO>
+__device__ __forceinline__ void epilogue_store4(const GemmEpilogue& ep, int m, int n0, int N,
+                                                float acc[4]) {
+  // row validity / addresses
+  const int ob = m / ep.out_map.rows_per_batch, ot = m - ob * ep.out_map.rows_per_batch;
+  if (ot >= ep.out_map.valid_rows) return;
+  float v[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int n = n0 + j;
+    float x = acc[j];
+    if (n < N) {
+      if (ep.bias) x += ep.bias[n];
+      x = apply_act(x, ep.act_pre);
+      if (ep.gate) x *= ep.gate[(long long)m * ep.gate_ld + n];
+      if (ep.colscale) x *= ep.colscale[n];
+      x *= ep.alpha;
+    }
+    v[j] = x;
+  }
+  if (ep.res) {
+    const int rb = m / ep.res_map.rows_per_batch, rt = m - rb * ep.res_map.rows_per_batch;
+    const TO* r = reinterpret_cast<const TO*>(ep.res) + rb * ep.res_map.batch_stride +
+                  (long long)rt * ep.res_map.ld + n0;
+    if (n0 + 3 < N) {
+      float4 rv = load4(r);
+      v[0] += rv.x; v[1] += rv.y; v[2] += rv.z; v[3] += rv.w;
+    } else {
+      for (int j = 0; j < 4 && n0 + j < N; ++j) v[j] += to_f(r[j]);
+    }
+  }
+  if (ep.out2) {
+    const int b2 = m / ep.out2_map.rows_per_batch, t2 = m - b2 * ep.out2_map.rows_per_batch;
+    TO* o2 = reinterpret_cast<TO*>(ep.out2) + b2 * ep.out2_map.batch_stride +
+             (long long)t2 * ep.out2_map.ld + n0;
+    if (n0 + 3 < N) store4(o2, make_float4(v[0], v[1], v[2], v[3]));
+    else for (int j = 0; j < 4 && n0 + j < N; ++j) o2[j] = from_f<TO>(v[j]);
+  }
+  TO* o = reinterpret_cast<TO*>(ep.out) + ob * ep.out_map.batch_stride +
+          (long long)ot * ep.out_map.ld + n0;
+  if (n0 + 3 < N) {
+    store4(o, make_float4(apply_act(v[0], ep.act_post), apply_act(v[1], ep.act_post),
+                          apply_act(v[2], ep.act_post), apply_act(v[3], ep.act_post)));
+  } else {
+    for (int j = 0; j < 4 && n0 + j < N; ++j) o[j] = from_f<TO>(apply_act(v[j], ep.act_post));
+  }
+}
+
+}  // namespace ptts

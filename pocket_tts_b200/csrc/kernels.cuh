@@ -1,0 +1,102 @@
+// Launchers for the non-GEMM kernels of the frame step.  Element types are passed as
+// 0 = float, 1 = bf16 ("act" = activation storage feeding GEMMs, "kv" = KV-cache storage).
+#pragma once
+#include "common.cuh"
+
+namespace ptts {
+
+// KV cache geometry: element (layer, slot, kv, h, pos, d) lives at
+//   base + ((((layer*n_slots + slot)*2 + kv)*H + h)*cap + pos)*D + d
+struct KvGeom {
+  void* base;
+  int n_slots, H, cap, D;
+  int type;        // 0 float, 1 bf16
+  int ring;        // 1: pos stored at pos & (cap-1) (Mimi sliding window), 0: linear
+};
+
+// h[i,:] = input_linear(where(isnan(prev), bos, prev))            flow_lm.py:121-122
+cudaError_t launch_flow_embed(const float* prev_latent, const int* slot_ids, const float* bos,
+                              const float* w_in /*[d,ldim]*/, float* h, int n, int d, int ldim,
+                              cudaStream_t st);
+
+// y = LayerNorm(x; w, b, eps) rows of width d (<= 1024), x fp32 -> y (act type)
+cudaError_t launch_ln_rows(const float* x, const float* w, const float* b, float eps, void* y,
+                           int y_type, int rows, int d, cudaStream_t st);
+
+// FlowLM decode attention for one new position per stream: RoPE(q,k) at offset[slot], append
+// K/V, softmax(q K^T / sqrt(D)) V over positions [0, offset].   transformer.py:135-158
+cudaError_t launch_attn_decode(const float* qkv /*[n,3*H*D]*/, const float* rope_freqs,
+                               const int* offsets, const int* slot_ids, KvGeom kv, int layer,
+                               void* out, int out_type, int n, cudaStream_t st);
+
+// Multi-query variant (prefill, Mimi): stream i owns rows [row_start[i], row_start[i]+len[i])
+// of qkv, appended at positions offset[slot]..; causal with optional window `context`.
+// q is rotated in place inside qkv.
+cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* offsets,
+                              const int* slot_ids, const int* row_start, const int* lens, KvGeom kv,
+                              int layer, int context, void* out, int out_type, int n, cudaStream_t st);
+
+// offsets[slot_ids[i]] += inc[i] (inc == nullptr: += const_inc)
+cudaError_t launch_advance(int* offsets, const int* slot_ids, const int* inc, int const_inc, int n,
+                           cudaStream_t st);
+
+// c = out_norm(h) (act type) ; eos_logit = w_eos . c + b_eos (from the fp32 normalised row)
+// flow_lm.py:128-129,153-154
+cudaError_t launch_final_norm_eos(const float* h, const float* w, const float* b, float eps,
+                                  const float* w_eos, const float* b_eos, void* c, int c_type,
+                                  float* eos_logit, int n, int d, cudaStream_t st);
+
+// sy = silu(cemb + tcomb_row) (mlp.py:209, 99-100 SiLU of adaLN_modulation)
+cudaError_t launch_silu_add(const float* cemb, const float* tcomb_row, void* sy, int sy_type,
+                            int n, int d, cudaStream_t st);
+
+// g = LN_flow(u; w,b (nullable), eps=1e-6) * (1 + scale) + shift     mlp.py:16-17,49-55,107-109
+cudaError_t launch_ln_modulate(const float* u, const float* w, const float* b, const float* shift,
+                               const float* scale, int mod_ld, void* g, int g_type, int n, int d,
+                               cudaStream_t st);
+
+// x[i,:] -> prev_latent[slot] and out (nullable)
+cudaError_t launch_commit_latent(const float* x, const int* slot_ids, float* prev_latent,
+                                 float* out, int n, int ldim, cudaStream_t st);
+
+// tts_model.py:449-451 + resample.py:41-48: de-normalise, 1x1 projection, depthwise x16
+// transposed conv with the previous frame's embedding as streaming state.
+cudaError_t launch_mimi_embed(const float* latents, const int* slot_ids, const float* emb_std,
+                              const float* emb_mean, const float* w_q /*[C,ldim]*/,
+                              const float* w_up /*[C,2S]*/, float* e_prev /*[slots,C]*/,
+                              float* xm /*[n*S,C]*/, int n, int C, int ldim, int S, cudaStream_t st);
+
+// rows of xm (fp32 [n*T, C]) -> buf[i][hist + t][c] (act type)
+cudaError_t launch_stage_rows(const float* xm, void* buf, int buf_type, int n, int T, int C,
+                              int hist, cudaStream_t st);
+
+// streaming-conv history: per conv input buffer, `hist` leading rows come from the per-slot
+// state (gather) and the trailing `hist` rows of this frame go back to it (scatter).
+struct HistDesc {
+  void* buf;          // [n][hist+T][C] act type
+  void* state;        // [slots][hist][C] act type
+  int hist, T, C;
+};
+#define PTTS_MAX_HIST 8
+struct HistTable {
+  HistDesc d[PTTS_MAX_HIST];
+  int count;
+};
+cudaError_t launch_hist_gather(const HistTable& t, const int* slot_ids, int type, int n, cudaStream_t st);
+cudaError_t launch_hist_scatter(const HistTable& t, const int* slot_ids, int type, int n, cudaStream_t st);
+
+// final Conv1d C->1, kernel K: pcm[i][t] = b + sum_k sum_c w[k*C + c] * buf[i][t+k][c]
+cudaError_t launch_last_conv(const void* buf, int buf_type, const float* w, const float* b,
+                             float* pcm, int n, int T, int C, int K, cudaStream_t st);
+
+// fp32 -> bf16 conversion (weights at load time), strided fill helpers
+cudaError_t launch_f32_to_bf16(const float* src, bf16* dst, long long n, cudaStream_t st);
+cudaError_t launch_fill_f32(float* dst, float v, long long n, cudaStream_t st);
+
+// KV import/export between the reference layout cache[2,1,P,H,D] (fp32) and the engine layout
+cudaError_t launch_kv_import(const float* ref /*[2,P,H,D]*/, KvGeom kv, int layer, int slot, int P,
+                             cudaStream_t st);
+cudaError_t launch_kv_export(float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st);
+cudaError_t launch_kv_fork(KvGeom kv, int n_layers, int src, int dst, int P, cudaStream_t st);
+
+}  // namespace ptts
