@@ -1,0 +1,201 @@
+// Engine implementation, part 1: memory, weight loading and re-layout.
+#include "engine.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+namespace ptts {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+void set_error_cuda(cudaError_t e, const char* expr, const char* file, int line) {
+  char buf[512];
+  snprintf(buf, sizeof buf, "CUDA error %s (%s) at %s:%d: %s", cudaGetErrorName(e), cudaGetErrorString(e),
+           file, line, expr);
+  g_err = buf;
+}
+const char* get_error() { return g_err.c_str(); }
+
+Engine::~Engine() {
+  for (auto& kv : graphs)
+    if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+  for (void* p : allocs) cudaFree(p);
+  if (h_pinned) cudaFreeHost(h_pinned);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+void* Engine::act_alloc(size_t elems) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, elems * act_size + 256) != cudaSuccess) return nullptr;
+  cudaMemsetAsync(p, 0, elems * act_size + 256, stream);
+  allocs.push_back(p);
+  return p;
+}
+
+int Engine::init() {
+  const ptts_config& c = cfg;
+  if (c.d_model != c.n_heads * 64 || c.mimi_d != c.mimi_heads * 64)
+    PTTS_FAIL(PTTS_EINVAL, "head_dim must be 64 (d_model=%d heads=%d)", c.d_model, c.n_heads);
+  if (c.d_model > 1024 || c.mimi_d > 1024 || c.flow_dim > 512 || c.ldim > 64 || c.ldim % 16)
+    PTTS_FAIL(PTTS_EINVAL, "unsupported widths");
+  if (c.max_streams < 1 || c.kv_capacity < 8 || c.n_layers < 1)
+    PTTS_FAIL(PTTS_EINVAL, "bad sizing (max_streams=%d kv_capacity=%d)", c.max_streams, c.kv_capacity);
+  if (c.precision != PTTS_PRECISION_FP32 && c.precision != PTTS_PRECISION_BF16)
+    PTTS_FAIL(PTTS_EINVAL, "unknown precision %d", c.precision);
+  PTTS_CUDA_CHECK(cudaSetDevice(c.device));
+  PTTS_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  act_type = c.precision == PTTS_PRECISION_BF16 ? 1 : 0;
+  act_size = act_type ? 2 : 4;
+  const int S = c.max_streams;
+  const int U = c.upsample_stride;
+
+  // ---- per-slot state
+  kv_flow = KvGeom{nullptr, S, c.n_heads, c.kv_capacity, 64, act_type, 0};
+  const size_t kvf = (size_t)c.n_layers * S * 2 * c.n_heads * c.kv_capacity * 64;
+  kv_flow.base = act_alloc(kvf);
+  int ring = 256;
+  while (ring < c.mimi_context + U) ring *= 2;
+  kv_mimi = KvGeom{nullptr, S, c.mimi_heads, ring, 64, act_type, 1};
+  kv_mimi.base = act_alloc((size_t)c.mimi_layers * S * 2 * c.mimi_heads * ring * 64);
+  offsets = dmalloc<int>(allocs, S, stream);
+  mimi_offsets = dmalloc<int>(allocs, S, stream);
+  prev_latent = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
+  e_prev = dmalloc<float>(allocs, (size_t)S * c.mimi_d, stream);
+  if (!kv_flow.base || !kv_mimi.base || !offsets || !mimi_offsets || !prev_latent || !e_prev)
+    PTTS_FAIL(PTTS_ECUDA, "out of device memory for stream state");
+  host_offsets.assign(S, 0);
+  host_mimi_offsets.assign(S, 0);
+  slot_used.assign(S, 0);
+
+  // ---- per-batch buffers
+  max_rows = std::max(std::max(S, c.max_prefill_rows), 1);
+  const int D = c.d_model, F = c.flow_dim, Md = c.mimi_d;
+  d_slot_ids = dmalloc<int>(allocs, S, stream);
+  d_row_start = dmalloc<int>(allocs, S, stream);
+  d_lens = dmalloc<int>(allocs, S, stream);
+  d_mimi_row_start = dmalloc<int>(allocs, S, stream);
+  d_mimi_lens = dmalloc<int>(allocs, S, stream);
+  h = dmalloc<float>(allocs, (size_t)max_rows * D, stream);
+  qkv = dmalloc<float>(allocs, (size_t)max_rows * 3 * D, stream);
+  a_ln = act_alloc((size_t)max_rows * D);
+  attn_o = act_alloc((size_t)max_rows * D);
+  mid = act_alloc((size_t)max_rows * c.ffn);
+  eos_logit = dmalloc<float>(allocs, S, stream);
+  noise_buf = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
+  lat_in = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
+  x_lat = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
+  c_cond = act_alloc((size_t)S * D);
+  cemb = dmalloc<float>(allocs, (size_t)S * F, stream);
+  sy = act_alloc((size_t)S * F);
+  mod = dmalloc<float>(allocs, (size_t)S * (c.flow_depth * 3 + 2) * F, stream);
+  u = dmalloc<float>(allocs, (size_t)S * F, stream);
+  g = act_alloc((size_t)S * F);
+  g1 = act_alloc((size_t)S * F);
+  xm = dmalloc<float>(allocs, (size_t)S * U * Md, stream);
+  mqkv = dmalloc<float>(allocs, (size_t)S * U * 3 * Md, stream);
+  m_ln = act_alloc((size_t)S * U * Md);
+  m_attn = act_alloc((size_t)S * U * Md);
+  m_mid = act_alloc((size_t)S * U * c.mimi_ffn);
+  if (!h || !qkv || !a_ln || !attn_o || !mid || !mod || !xm || !mqkv || !m_ln || !m_attn || !m_mid)
+    PTTS_FAIL(PTTS_ECUDA, "out of device memory for activations");
+
+  // ---- conv chain buffers + history table
+  int C = c.n_filters * 8;  // 512
+  if (C != Md) PTTS_FAIL(PTTS_EINVAL, "seanet width %d != mimi_d %d", C, Md);
+  int T = U;
+  hist_tab.count = 0;
+  auto add_hist = [&](void* buf, int hist, int Tn, int Cn) {
+    HistDesc& hd = hist_tab.d[hist_tab.count];
+    hd.buf = buf; hd.hist = hist; hd.T = Tn; hd.C = Cn;
+    hd.state = act_alloc((size_t)S * hist * Cn);
+    hist_state[hist_tab.count] = hd.state;
+    hist_tab.count++;
+  };
+  b_conv0 = act_alloc((size_t)S * (c.kernel - 1 + T) * C);
+  add_hist(b_conv0, c.kernel - 1, T, C);
+  for (int i = 0; i < 3; ++i) {
+    const int r = c.ratios[i], T2 = T * r, C2 = C / 2, hc = C2 / 2;
+    b_tr[i] = act_alloc((size_t)S * (1 + T) * C);
+    add_hist(b_tr[i], 1, T, C);
+    b_raw[i] = act_alloc((size_t)S * T2 * C2);
+    b_res[i] = act_alloc((size_t)S * (c.res_kernel - 1 + T2) * C2);
+    add_hist(b_res[i], c.res_kernel - 1, T2, C2);
+    b_hid[i] = act_alloc((size_t)S * T2 * hc);
+    T = T2; C = C2;
+  }
+  b_last = act_alloc((size_t)S * (c.last_kernel - 1 + T) * C);
+  add_hist(b_last, c.last_kernel - 1, T, C);
+  pcm = dmalloc<float>(allocs, (size_t)S * T, stream);
+  if (!b_last || !pcm) PTTS_FAIL(PTTS_ECUDA, "out of device memory for conv buffers");
+  PTTS_CUDA_CHECK(cudaMallocHost(&h_pinned, (size_t)S * 4 * sizeof(int) + 64));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return PTTS_OK;
+}
+
+// -------------------------------------------------------------------------------------
+// weights
+// -------------------------------------------------------------------------------------
+int Engine::load_tensor(const char* name, const float* data, const int64_t* shape, int ndim) {
+  if (ready) PTTS_FAIL(PTTS_ESTATE, "load_tensor after finalize");
+  if (!name || !data || ndim < 0 || ndim > 4) PTTS_FAIL(PTTS_EINVAL, "bad load_tensor arguments");
+  std::string nm(name);
+  static const char* skip[] = {"mimi.encoder.", "mimi.encoder_transformer.", "mimi.downsample."};
+  for (const char* s : skip)
+    if (nm.rfind(s, 0) == 0) return PTTS_OK;  // encode-only (voice prompt, host side)
+  HostTensor t;
+  t.shape.assign(shape, shape + ndim);
+  const int64_t n = t.numel();
+  if (n <= 0 || n > (1LL << 31)) PTTS_FAIL(PTTS_EINVAL, "bad shape for %s", name);
+  t.data.assign(data, data + n);
+  host_w[nm] = std::move(t);
+  return PTTS_OK;
+}
+
+float* Engine::upload(const std::vector<float>& host) {
+  float* p = dmalloc<float>(allocs, host.size(), stream);
+  if (!p) return nullptr;
+  if (cudaMemcpyAsync(p, host.data(), host.size() * sizeof(float), cudaMemcpyHostToDevice, stream) != cudaSuccess)
+    return nullptr;
+  cudaStreamSynchronize(stream);  // host vector may be a temporary
+  return p;
+}
+
+float* Engine::dev_f32(const std::string& name, const std::vector<int64_t>& shape) {
+  auto it = host_w.find(name);
+  if (it == host_w.end()) { set_error("missing tensor " + name); return nullptr; }
+  if (it->second.shape != shape) {
+    std::string s = "shape mismatch for " + name + ": got [";
+    for (auto v : it->second.shape) s += std::to_string(v) + ",";
+    s += "] expected [";
+    for (auto v : shape) s += std::to_string(v) + ",";
+    set_error(s + "]");
+    return nullptr;
+  }
+  float* p = upload(it->second.data);
+  if (!p) set_error("device upload failed for " + name);
+  return p;
+}
+
+int Engine::make_mat_from(const std::vector<float>& host, int N, int K, Mat* m, bool want_b16) {
+  if ((int64_t)host.size() != (int64_t)N * K) PTTS_FAIL(PTTS_EINVAL, "matrix size mismatch");
+  m->N = N; m->K = K;
+  m->f32 = upload(host);
+  if (!m->f32) PTTS_FAIL(PTTS_ECUDA, "upload failed");
+  if (act_type == 1 && want_b16) {
+    m->b16 = dmalloc<bf16>(allocs, host.size(), stream);
+    if (!m->b16) PTTS_FAIL(PTTS_ECUDA, "alloc failed");
+    PTTS_CUDA_CHECK(launch_f32_to_bf16(m->f32, m->b16, (long long)host.size(), stream));
+  }
+  return PTTS_OK;
+}
+
+int Engine::make_mat(const std::string& name, int N, int K, Mat* m, bool want_b16) {
+  auto it = host_w.find(name);
+  if (it == host_w.end()) PTTS_FAIL(PTTS_EINVAL, "missing tensor %s", name.c_str());
+  if (it->second.numel() != (int64_t)N * K || it->second.shape.empty() || it->second.shape[0] != N)
+    PTTS_FAIL(PTTS_EINVAL, "shape mismatch for %s (want [%d,%d])", name.c_str(), N, K);
+  return make_mat_from(it->second.data, N, K, m, want_b16);
+}
+
+}  // namespace ptts

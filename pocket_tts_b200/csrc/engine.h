@@ -1,0 +1,182 @@
+// Engine: weights, per-slot state (FlowLM KV slabs, Mimi ring KV, conv history), per-batch
+// activation buffers and the kernel sequences of the frame step.  Host-side C++ only sees
+// this header; the C ABI (c_api.cu) is a thin wrapper.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/pocket_tts_b200.h"
+#include "gemm.cuh"
+#include "kernels.cuh"
+
+namespace ptts {
+
+void set_error(const std::string& msg);
+void set_error_cuda(cudaError_t e, const char* expr, const char* file, int line);
+const char* get_error();
+
+struct HostTensor {
+  std::vector<float> data;
+  std::vector<int64_t> shape;
+  int64_t numel() const { int64_t n = 1; for (auto s : shape) n *= s; return n; }
+};
+
+// a GEMM weight [N, K] row-major in device memory, fp32 and (bf16 mode) bf16
+struct Mat {
+  float* f32 = nullptr;
+  bf16* b16 = nullptr;
+  int N = 0, K = 0;
+};
+
+struct LayerW {
+  float *n1w, *n1b, *n2w, *n2b;
+  Mat in_proj, out_proj, lin1, lin2;
+  float *ls1 = nullptr, *ls2 = nullptr;  // Mimi LayerScale
+};
+
+struct FlowBlockW {
+  float *lnw, *lnb, *b0, *b2;
+  Mat mlp0, mlp2;
+};
+
+struct ConvStageW {
+  Mat tr;  float* tr_b;      // [S*Cout, 2Cin], bias expanded to [S*Cout]
+  Mat c3;  float* c3_b;      // [h, 3*C2]
+  Mat c1;  float* c1_b;      // [C2, h]
+};
+
+struct GraphKey {
+  int n, lsd, audio;
+  bool operator<(const GraphKey& o) const {
+    if (n != o.n) return n < o.n;
+    if (lsd != o.lsd) return lsd < o.lsd;
+    return audio < o.audio;
+  }
+};
+struct GraphEntry {
+  cudaGraphExec_t exec = nullptr;
+  long long kernels = 0;
+};
+
+class Engine {
+ public:
+  explicit Engine(const ptts_config& c) : cfg(c) {}
+  ~Engine();
+  int init();
+  int load_tensor(const char* name, const float* data, const int64_t* shape, int ndim);
+  int finalize();
+
+  int stream_open(int* slot);
+  int stream_close(int slot);
+  int stream_reset_decoder(int slot);
+  int stream_fork(int src, int dst);
+  int import_kv(int slot, int layer, const float* cache_any, int P);
+  int export_kv(int slot, int layer, float* cache_any, int P);
+  int set_offset(int slot, int off);
+  int get_offset(int slot, int* off);
+  int set_prev_latent(int slot, const float* latent_any);
+
+  int prefill(int n, const int* slots, const int* lens, const float* embeds_any);
+  int step(int n, const int* slots, const float* noise_any, int lsd, int audio, float* out_lat,
+           float* out_eos, float* out_pcm);
+  int mimi_decode(int n, const int* slots, const float* latents_any, float* out_pcm);
+  int run_frames(int n, const int* slots, int n_frames, const float* noise_dev, int lsd,
+                 float* out_pcm_dev, float* out_lat_dev);
+  int debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out);
+
+  ptts_config cfg;
+  cudaStream_t stream = nullptr;
+  long long launches = 0;
+  bool use_graphs = true;
+
+ private:
+  // ---- helpers
+  int check_slots(int n, const int* slots, bool need_decode_room);
+  int upload_slots(int n, const int* slots);
+  float* dev_f32(const std::string& name, const std::vector<int64_t>& shape);
+  int make_mat(const std::string& name, int N, int K, Mat* m, bool want_b16 = true);
+  int make_mat_from(const std::vector<float>& host, int N, int K, Mat* m, bool want_b16 = true);
+  float* upload(const std::vector<float>& host);
+  int gemm(const void* A, bool a_is_act, RowMap amap, const Mat& W, int M, GemmEpilogue ep,
+           bool out_is_act);
+  int transformer_layer_common(const LayerW& L, float* h, int rows, int d, int ffn, void* a,
+                               float* qkv, void* ao, void* mid, bool mimi, int li, int n);
+  int flow_sequence(int n, int lsd);
+  int mimi_sequence(int n, const float* latents);
+  int frame(int n, int lsd, int audio);  // eager or graph
+  void* act_alloc(size_t elems);
+
+  bool ready = false;
+  int act_type = 0;  // 0 fp32, 1 bf16
+  size_t act_size = 4;
+  std::map<std::string, HostTensor> host_w;
+  std::vector<void*> allocs;
+
+  // weights
+  float *bos_emb, *w_in, *out_norm_w, *out_norm_b, *eos_w, *eos_b, *emb_std, *emb_mean;
+  float *rope_freqs, *tcomb;
+  int tcomb_rows = 0;
+  std::vector<LayerW> flow_layers, mimi_layers;
+  Mat cond_embed, input_proj, mod_all, final_lin;
+  float *cond_b, *inproj_b, *mod_b, *final_b;
+  std::vector<FlowBlockW> flow_blocks;
+  float *wq, *wup;
+  Mat conv0; float* conv0_b;
+  ConvStageW stages[3];
+  float *last_w, *last_b;
+
+  // per-slot state
+  KvGeom kv_flow{}, kv_mimi{};
+  int *offsets = nullptr, *mimi_offsets = nullptr;  // device [slots]
+  float* prev_latent = nullptr;                      // device [slots, ldim]
+  float* e_prev = nullptr;                           // device [slots, mimi_d]
+  void* hist_state[PTTS_MAX_HIST] = {};
+  std::vector<int> host_offsets, host_mimi_offsets;
+  std::vector<char> slot_used;
+
+  // per-batch buffers
+  int max_rows = 0;
+  int *d_slot_ids, *d_row_start, *d_lens, *d_mimi_row_start, *d_mimi_lens;
+  float *h, *qkv, *eos_logit, *noise_buf, *x_lat, *cemb, *mod, *u, *pcm, *lat_in;
+  void *a_ln, *attn_o, *mid, *c_cond, *sy, *g, *g1;
+  float *xm, *mqkv;
+  void *m_ln, *m_attn, *m_mid;
+  // conv chain buffers
+  void* b_conv0;                  // [n][6+16][512]
+  void* b_tr[3];                  // [n][1+T][C]
+  void* b_raw[3];                 // [n][T2][C2]
+  void* b_res[3];                 // [n][2+T2][C2]
+  void* b_hid[3];                 // [n][T2][h]
+  void* b_last;                   // [n][2+1920][64]
+  HistTable hist_tab{};
+  int frame_T0 = 16;
+
+  std::map<GraphKey, GraphEntry> graphs;
+  std::vector<int> cur_slots;
+  float* h_pinned = nullptr;
+  std::map<std::string, std::pair<const void*, std::pair<int, long long>>> debug_bufs;  // name -> (ptr,(type,elems per row unit))
+};
+
+
+template <typename T>
+static inline T* dmalloc(std::vector<void*>& allocs, size_t n, cudaStream_t st) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, n * sizeof(T) + 256) != cudaSuccess) return nullptr;
+  cudaMemsetAsync(p, 0, n * sizeof(T) + 256, st);
+  allocs.push_back(p);
+  return reinterpret_cast<T*>(p);
+}
+
+}  // namespace ptts
+
+#define PTTS_FAIL(code, ...)                       \
+  do {                                             \
+    char _b[512];                                  \
+    snprintf(_b, sizeof _b, __VA_ARGS__);          \
+    ptts::set_error(_b);                           \
+    return code;                                   \
+  } while (0)

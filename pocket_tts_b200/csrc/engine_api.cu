@@ -1,0 +1,332 @@
+// Engine implementation, part 4: stream slots, prefill, frame step (eager / CUDA graph).
+#include "engine.h"
+
+#include <cmath>
+#include <cstring>
+
+namespace ptts {
+
+#define NEED_READY() \
+  if (!ready) PTTS_FAIL(PTTS_ESTATE, "engine not finalized")
+#define CHECK_SLOT(s)                                                        \
+  if ((s) < 0 || (s) >= cfg.max_streams || !slot_used[s])                    \
+  PTTS_FAIL(PTTS_EINVAL, "invalid or closed stream slot %d", (int)(s))
+
+int Engine::stream_open(int* slot) {
+  NEED_READY();
+  for (int s = 0; s < cfg.max_streams; ++s)
+    if (!slot_used[s]) {
+      slot_used[s] = 1;
+      *slot = s;
+      host_offsets[s] = 0;
+      PTTS_CUDA_CHECK(cudaMemsetAsync(offsets + s, 0, sizeof(int), stream));
+      return stream_reset_decoder(s);
+    }
+  PTTS_FAIL(PTTS_ENOSLOT, "all %d stream slots in use", cfg.max_streams);
+}
+
+int Engine::stream_close(int slot) {
+  NEED_READY();
+  CHECK_SLOT(slot);
+  slot_used[slot] = 0;
+  return PTTS_OK;
+}
+
+// fresh Mimi state (tts_model.py:444) and BOS marker (tts_model.py:748-753)
+int Engine::stream_reset_decoder(int slot) {
+  NEED_READY();
+  CHECK_SLOT(slot);
+  host_mimi_offsets[slot] = 0;
+  PTTS_CUDA_CHECK(cudaMemsetAsync(mimi_offsets + slot, 0, sizeof(int), stream));
+  PTTS_CUDA_CHECK(cudaMemsetAsync(e_prev + (size_t)slot * cfg.mimi_d, 0, cfg.mimi_d * sizeof(float), stream));
+  for (int k = 0; k < hist_tab.count; ++k) {
+    const size_t bytes = (size_t)hist_tab.d[k].hist * hist_tab.d[k].C * act_size;
+    PTTS_CUDA_CHECK(cudaMemsetAsync((char*)hist_tab.d[k].state + slot * bytes, 0, bytes, stream));
+  }
+  PTTS_CUDA_CHECK(launch_fill_f32(prev_latent + (size_t)slot * cfg.ldim, NAN, cfg.ldim, stream));
+  return PTTS_OK;
+}
+
+int Engine::stream_fork(int src, int dst) {
+  NEED_READY();
+  CHECK_SLOT(src);
+  CHECK_SLOT(dst);
+  if (src == dst) return PTTS_OK;
+  const int P = host_offsets[src];
+  PTTS_CUDA_CHECK(launch_kv_fork(kv_flow, cfg.n_layers, src, dst, P, stream));
+  ++launches;
+  host_offsets[dst] = P;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(offsets + dst, offsets + src, sizeof(int), cudaMemcpyDeviceToDevice, stream));
+  return PTTS_OK;
+}
+
+int Engine::import_kv(int slot, int layer, const float* cache_any, int P) {
+  NEED_READY();
+  CHECK_SLOT(slot);
+  if (layer < 0 || layer >= cfg.n_layers || P < 0 || P > cfg.kv_capacity)
+    PTTS_FAIL(PTTS_EINVAL, "import_kv: layer %d / positions %d out of range", layer, P);
+  if (P == 0) return PTTS_OK;
+  const size_t elems = 2ull * P * cfg.d_model;
+  float* tmp = nullptr;
+  PTTS_CUDA_CHECK(cudaMallocAsync((void**)&tmp, elems * sizeof(float), stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(tmp, cache_any, elems * sizeof(float), cudaMemcpyDefault, stream));
+  PTTS_CUDA_CHECK(launch_kv_import(tmp, kv_flow, layer, slot, P, stream));
+  PTTS_CUDA_CHECK(cudaFreeAsync(tmp, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return PTTS_OK;
+}
+
+int Engine::export_kv(int slot, int layer, float* cache_any, int P) {
+  NEED_READY();
+  CHECK_SLOT(slot);
+  if (layer < 0 || layer >= cfg.n_layers || P < 0 || P > cfg.kv_capacity)
+    PTTS_FAIL(PTTS_EINVAL, "export_kv: layer %d / positions %d out of range", layer, P);
+  if (P == 0) return PTTS_OK;
+  const size_t elems = 2ull * P * cfg.d_model;
+  float* tmp = nullptr;
+  PTTS_CUDA_CHECK(cudaMallocAsync((void**)&tmp, elems * sizeof(float), stream));
+  PTTS_CUDA_CHECK(launch_kv_export(tmp, kv_flow, layer, slot, P, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(cache_any, tmp, elems * sizeof(float), cudaMemcpyDefault, stream));
+  PTTS_CUDA_CHECK(cudaFreeAsync(tmp, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return PTTS_OK;
+}
+
+int Engine::set_offset(int slot, int off) {
+  NEED_READY();
+  CHECK_SLOT(slot);
+  if (off < 0 || off > cfg.kv_capacity) PTTS_FAIL(PTTS_EINVAL, "offset %d out of range", off);
+  host_offsets[slot] = off;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(offsets + slot, &host_offsets[slot], sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return PTTS_OK;
+}
+
+int Engine::get_offset(int slot, int* off) {
+  NEED_READY();
+  CHECK_SLOT(slot);
+  int dev = -1;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(&dev, offsets + slot, sizeof(int), cudaMemcpyDeviceToHost, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  if (dev != host_offsets[slot]) PTTS_FAIL(PTTS_ESTATE, "offset mirror diverged (%d vs %d)", dev, host_offsets[slot]);
+  *off = dev;
+  return PTTS_OK;
+}
+
+int Engine::set_prev_latent(int slot, const float* latent_any) {
+  NEED_READY();
+  CHECK_SLOT(slot);
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(prev_latent + (size_t)slot * cfg.ldim, latent_any, cfg.ldim * sizeof(float),
+                                  cudaMemcpyDefault, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return PTTS_OK;
+}
+
+int Engine::check_slots(int n, const int* slots, bool need_decode_room) {
+  if (n < 1 || n > cfg.max_streams || !slots) PTTS_FAIL(PTTS_EINVAL, "bad stream count %d", n);
+  std::vector<char> seen(cfg.max_streams, 0);
+  for (int i = 0; i < n; ++i) {
+    CHECK_SLOT(slots[i]);
+    if (seen[slots[i]]) PTTS_FAIL(PTTS_EINVAL, "slot %d listed twice", slots[i]);
+    seen[slots[i]] = 1;
+    if (need_decode_room && host_offsets[slots[i]] + 1 > cfg.kv_capacity)
+      PTTS_FAIL(PTTS_ENOSLOT, "slot %d: KV capacity %d exhausted", slots[i], cfg.kv_capacity);
+  }
+  return PTTS_OK;
+}
+
+int Engine::upload_slots(int n, const int* slots) {
+  if ((int)cur_slots.size() == n && std::memcmp(cur_slots.data(), slots, n * sizeof(int)) == 0) return PTTS_OK;
+  int* hp = reinterpret_cast<int*>(h_pinned);
+  const int S = cfg.max_streams;
+  std::memcpy(hp, slots, n * sizeof(int));
+  for (int i = 0; i < S; ++i) {
+    hp[S + i] = i * cfg.upsample_stride;
+    hp[2 * S + i] = cfg.upsample_stride;
+  }
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(d_slot_ids, hp, n * sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(d_mimi_row_start, hp + S, S * sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(d_mimi_lens, hp + 2 * S, S * sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));  // h_pinned is reused
+  cur_slots.assign(slots, slots + n);
+  return PTTS_OK;
+}
+
+int Engine::prefill(int n, const int* slots, const int* lens, const float* embeds_any) {
+  NEED_READY();
+  int rc;
+  if ((rc = check_slots(n, slots, false)) != PTTS_OK) return rc;
+  if (!lens || !embeds_any) PTTS_FAIL(PTTS_EINVAL, "prefill: null argument");
+  int rows = 0;
+  std::vector<int> rs(n);
+  for (int i = 0; i < n; ++i) {
+    if (lens[i] < 1) PTTS_FAIL(PTTS_EINVAL, "prefill: stream %d has %d rows", i, lens[i]);
+    if (host_offsets[slots[i]] + lens[i] > cfg.kv_capacity)
+      PTTS_FAIL(PTTS_ENOSLOT, "slot %d: %d + %d positions exceed KV capacity %d", slots[i],
+                host_offsets[slots[i]], lens[i], cfg.kv_capacity);
+    rs[i] = rows;
+    rows += lens[i];
+  }
+  if (rows > max_rows) PTTS_FAIL(PTTS_EINVAL, "prefill: %d rows exceed max_prefill_rows %d", rows, max_rows);
+  if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(d_row_start, rs.data(), n * sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(d_lens, lens, n * sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(h, embeds_any, (size_t)rows * cfg.d_model * sizeof(float), cudaMemcpyDefault, stream));
+  for (int l = 0; l < cfg.n_layers; ++l) {
+    // rows == n would select the decode kernel, which is equivalent for len == 1
+    if ((rc = transformer_layer_common(flow_layers[l], h, rows, cfg.d_model, cfg.ffn, a_ln, qkv, attn_o, mid,
+                                       false, l, n)) != PTTS_OK)
+      return rc;
+  }
+  PTTS_CUDA_CHECK(launch_advance(offsets, d_slot_ids, d_lens, 0, n, stream));
+  ++launches;
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));  // rs / lens host buffers
+  for (int i = 0; i < n; ++i) host_offsets[slots[i]] += lens[i];
+  return PTTS_OK;
+}
+
+// one frame for the streams in d_slot_ids with noise in noise_buf; graph-replayed when enabled
+int Engine::frame(int n, int lsd, int audio) {
+  int rc;
+  if (!use_graphs) {
+    if ((rc = flow_sequence(n, lsd)) != PTTS_OK) return rc;
+    if (audio && (rc = mimi_sequence(n, x_lat)) != PTTS_OK) return rc;
+    return PTTS_OK;
+  }
+  GraphKey key{n, lsd, audio};
+  auto it = graphs.find(key);
+  if (it == graphs.end()) {
+    const long long before = launches;
+    cudaGraph_t graph = nullptr;
+    PTTS_CUDA_CHECK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+    rc = flow_sequence(n, lsd);
+    if (rc == PTTS_OK && audio) rc = mimi_sequence(n, x_lat);
+    cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+    if (rc != PTTS_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+    PTTS_CUDA_CHECK(ce);
+    GraphEntry ent;
+    ent.kernels = launches - before;
+    launches = before;
+    PTTS_CUDA_CHECK(cudaGraphInstantiate(&ent.exec, graph, 0));
+    cudaGraphDestroy(graph);
+    it = graphs.emplace(key, ent).first;
+  }
+  PTTS_CUDA_CHECK(cudaGraphLaunch(it->second.exec, stream));
+  launches += it->second.kernels;
+  return PTTS_OK;
+}
+
+int Engine::step(int n, const int* slots, const float* noise_any, int lsd, int audio, float* out_lat,
+                 float* out_eos, float* out_pcm) {
+  NEED_READY();
+  int rc;
+  if ((rc = check_slots(n, slots, true)) != PTTS_OK) return rc;
+  if (lsd < 1 || lsd > tcomb_rows) PTTS_FAIL(PTTS_EINVAL, "lsd_steps %d outside loaded flow.tcomb rows %d", lsd, tcomb_rows);
+  if (!noise_any) PTTS_FAIL(PTTS_EINVAL, "step: noise is required");
+  if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
+  const int Ld = cfg.ldim;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_any, (size_t)n * Ld * sizeof(float), cudaMemcpyDefault, stream));
+  if ((rc = frame(n, lsd, audio)) != PTTS_OK) return rc;
+  if (out_lat) PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat, x_lat, (size_t)n * Ld * sizeof(float), cudaMemcpyDefault, stream));
+  if (out_eos) PTTS_CUDA_CHECK(cudaMemcpyAsync(out_eos, eos_logit, (size_t)n * sizeof(float), cudaMemcpyDefault, stream));
+  if (out_pcm && audio) {
+    const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(out_pcm, pcm, n * fs * sizeof(float), cudaMemcpyDefault, stream));
+  }
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  for (int i = 0; i < n; ++i) {
+    host_offsets[slots[i]] += 1;
+    if (audio) host_mimi_offsets[slots[i]] += cfg.upsample_stride;
+  }
+  return PTTS_OK;
+}
+
+int Engine::mimi_decode(int n, const int* slots, const float* latents_any, float* out_pcm) {
+  NEED_READY();
+  int rc;
+  if ((rc = check_slots(n, slots, false)) != PTTS_OK) return rc;
+  if (!latents_any) PTTS_FAIL(PTTS_EINVAL, "mimi_decode: null latents");
+  if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(lat_in, latents_any, (size_t)n * cfg.ldim * sizeof(float), cudaMemcpyDefault, stream));
+  if ((rc = mimi_sequence(n, lat_in)) != PTTS_OK) return rc;
+  if (out_pcm) {
+    const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(out_pcm, pcm, n * fs * sizeof(float), cudaMemcpyDefault, stream));
+  }
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  for (int i = 0; i < n; ++i) host_mimi_offsets[slots[i]] += cfg.upsample_stride;
+  return PTTS_OK;
+}
+
+int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise_dev, int lsd,
+                       float* out_pcm_dev, float* out_lat_dev) {
+  NEED_READY();
+  int rc;
+  if ((rc = check_slots(n, slots, true)) != PTTS_OK) return rc;
+  if (lsd < 1 || lsd > tcomb_rows) PTTS_FAIL(PTTS_EINVAL, "lsd_steps %d outside loaded flow.tcomb rows %d", lsd, tcomb_rows);
+  if (n_frames < 1 || !noise_dev) PTTS_FAIL(PTTS_EINVAL, "run_frames: bad arguments");
+  for (int i = 0; i < n; ++i)
+    if (host_offsets[slots[i]] + n_frames > cfg.kv_capacity)
+      PTTS_FAIL(PTTS_ENOSLOT, "slot %d: %d frames exceed KV capacity", slots[i], n_frames);
+  if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
+  const int Ld = cfg.ldim;
+  const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
+  for (int f = 0; f < n_frames; ++f) {
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_dev + (size_t)f * n * Ld, (size_t)n * Ld * sizeof(float),
+                                    cudaMemcpyDeviceToDevice, stream));
+    if ((rc = frame(n, lsd, 1)) != PTTS_OK) return rc;
+    if (out_pcm_dev)
+      PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_dev + (size_t)f * fs, (size_t)n_frames * fs * sizeof(float), pcm,
+                                        fs * sizeof(float), fs * sizeof(float), n, cudaMemcpyDeviceToDevice, stream));
+    if (out_lat_dev)
+      PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat_dev + (size_t)f * n * Ld, x_lat, (size_t)n * Ld * sizeof(float),
+                                      cudaMemcpyDeviceToDevice, stream));
+  }
+  for (int i = 0; i < n; ++i) {
+    host_offsets[slots[i]] += n_frames;
+    host_mimi_offsets[slots[i]] += n_frames * cfg.upsample_stride;
+  }
+  return PTTS_OK;
+}
+
+int Engine::debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out) {
+  NEED_READY();
+  const std::string w(what ? what : "");
+  const int S = cfg.max_streams, U = cfg.upsample_stride;
+  struct Ent { const char* name; const void* p; int type; long long elems; };
+  const Ent tab[] = {
+      {"h", h, 0, (long long)max_rows * cfg.d_model},
+      {"qkv", qkv, 0, (long long)max_rows * 3 * cfg.d_model},
+      {"attn_o", attn_o, act_type, (long long)max_rows * cfg.d_model},
+      {"c_cond", c_cond, act_type, (long long)S * cfg.d_model},
+      {"eos_logit", eos_logit, 0, S},
+      {"x_lat", x_lat, 0, (long long)S * cfg.ldim},
+      {"mod", mod, 0, (long long)S * (cfg.flow_depth * 3 + 2) * cfg.flow_dim},
+      {"xm", xm, 0, (long long)S * U * cfg.mimi_d},
+      {"b_conv0", b_conv0, act_type, (long long)S * (cfg.kernel - 1 + U) * cfg.mimi_d},
+      {"b_tr0", b_tr[0], act_type, (long long)S * (1 + U) * cfg.mimi_d},
+      {"b_raw0", b_raw[0], act_type, (long long)S * U * cfg.ratios[0] * cfg.mimi_d / 2},
+      {"b_raw1", b_raw[1], act_type, (long long)S * U * cfg.ratios[0] * cfg.ratios[1] * cfg.mimi_d / 4},
+      {"b_raw2", b_raw[2], act_type, (long long)S * U * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2] * cfg.mimi_d / 8},
+      {"pcm", pcm, 0, (long long)S * U * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2]},
+  };
+  for (const Ent& e : tab) {
+    if (w != e.name) continue;
+    const long long n = std::min<long long>(e.elems, max_elems);
+    if (e.type == 0) {
+      PTTS_CUDA_CHECK(cudaMemcpyAsync(out_any, e.p, n * sizeof(float), cudaMemcpyDefault, stream));
+    } else {
+      float* tmp = nullptr;
+      PTTS_CUDA_CHECK(cudaMallocAsync((void**)&tmp, n * sizeof(float), stream));
+      PTTS_CUDA_CHECK(launch_bf16_to_f32((const bf16*)e.p, tmp, n, stream));
+      PTTS_CUDA_CHECK(cudaMemcpyAsync(out_any, tmp, n * sizeof(float), cudaMemcpyDefault, stream));
+      PTTS_CUDA_CHECK(cudaFreeAsync(tmp, stream));
+    }
+    PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+    if (n_out) *n_out = n;
+    return PTTS_OK;
+  }
+  PTTS_FAIL(PTTS_EINVAL, "debug_read: unknown buffer '%s'", w.c_str());
+}
+
+}  // namespace ptts

@@ -92,6 +92,7 @@ cudaError_t launch_last_conv(const void* buf, int buf_type, const float* w, cons
 // fp32 -> bf16 conversion (weights at load time), strided fill helpers
 cudaError_t launch_f32_to_bf16(const float* src, bf16* dst, long long n, cudaStream_t st);
 cudaError_t launch_fill_f32(float* dst, float v, long long n, cudaStream_t st);
+cudaError_t launch_bf16_to_f32(const bf16* src, float* dst, long long n, cudaStream_t st);
 
 // KV import/export between the reference layout cache[2,1,P,H,D] (fp32) and the engine layout
 cudaError_t launch_kv_import(const float* ref /*[2,P,H,D]*/, KvGeom kv, int layer, int slot, int P,

@@ -1,0 +1,166 @@
+// Mimi-decoder side non-GEMM kernels: latent de-normalisation + 1x1 projection + depthwise
+// x16 upsampling (tts_model.py:449-451, resample.py:41-48), streaming-conv history moves
+// (conv.py:108-112,155-162 restated as "previous input columns"), the final C->1 conv
+// (seanet.py:168-171) and small conversion helpers.
+#include "kernels.cuh"
+
+namespace ptts {
+
+// one CTA per stream, one thread per channel
+__global__ void __launch_bounds__(512)
+mimi_embed_kernel(const float* __restrict__ latents, const int* __restrict__ slot_ids,
+                  const float* __restrict__ emb_std, const float* __restrict__ emb_mean,
+                  const float* __restrict__ w_q, const float* __restrict__ w_up,
+                  float* __restrict__ e_prev, float* __restrict__ xm, int C, int ldim, int S) {
+  __shared__ float z[64];
+  const int i = blockIdx.x, slot = slot_ids[i];
+  if (threadIdx.x < ldim)
+    z[threadIdx.x] = latents[i * ldim + threadIdx.x] * emb_std[threadIdx.x] + emb_mean[threadIdx.x];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float* w = w_q + (long long)c * ldim;
+    float e = 0.0f;
+    for (int j = 0; j < ldim; ++j) e = fmaf(w[j], z[j], e);
+    const float ep = e_prev[(long long)slot * C + c];
+    e_prev[(long long)slot * C + c] = e;
+    const float* wu = w_up + (long long)c * 2 * S;
+    // out[t] = e * w[t] + e_prev * w[S + t]   (K = 2S transposed conv, stride S, depthwise)
+    for (int t = 0; t < S; ++t)
+      xm[((long long)i * S + t) * C + c] = e * wu[t] + ep * wu[S + t];
+  }
+}
+
+cudaError_t launch_mimi_embed(const float* latents, const int* slot_ids, const float* emb_std,
+                              const float* emb_mean, const float* w_q, const float* w_up,
+                              float* e_prev, float* xm, int n, int C, int ldim, int S, cudaStream_t st) {
+  if (ldim > 64) return cudaErrorInvalidValue;
+  mimi_embed_kernel<<<n, 512, 0, st>>>(latents, slot_ids, emb_std, emb_mean, w_q, w_up, e_prev, xm, C, ldim, S);
+  return cudaGetLastError();
+}
+
+template <typename TO>
+__global__ void stage_rows_kernel(const float* __restrict__ xm, TO* __restrict__ buf, int T, int C,
+                                  int hist, long long total4) {
+  const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= total4) return;
+  const long long e = q * 4;
+  const int c = (int)(e % C);
+  const long long r = e / C;  // i*T + t
+  const int t = (int)(r % T);
+  const long long i = r / T;
+  store4(buf + (i * (hist + T) + hist + t) * C + c, load4(xm + e));
+}
+
+cudaError_t launch_stage_rows(const float* xm, void* buf, int buf_type, int n, int T, int C, int hist,
+                              cudaStream_t st) {
+  const long long total4 = (long long)n * T * C / 4;
+  const int blocks = (int)((total4 + 255) / 256);
+  if (buf_type == 0) stage_rows_kernel<float><<<blocks, 256, 0, st>>>(xm, (float*)buf, T, C, hist, total4);
+  else stage_rows_kernel<bf16><<<blocks, 256, 0, st>>>(xm, (bf16*)buf, T, C, hist, total4);
+  return cudaGetLastError();
+}
+
+// grid (n, count); copies hist*C elements per (stream, conv)
+template <typename T, bool GATHER>
+__global__ void __launch_bounds__(128)
+hist_move_kernel(HistTable tab, const int* __restrict__ slot_ids) {
+  const HistDesc d = tab.d[blockIdx.y];
+  const int i = blockIdx.x, slot = slot_ids[i];
+  const int total = d.hist * d.C;
+  T* state = reinterpret_cast<T*>(d.state) + (long long)slot * total;
+  T* buf = reinterpret_cast<T*>(d.buf) + (long long)i * (d.hist + d.T) * d.C;
+  if (GATHER) {
+    for (int e = threadIdx.x * 4; e < total; e += blockDim.x * 4) store4(buf + e, load4(state + e));
+  } else {
+    const T* tail = buf + (long long)d.T * d.C;  // rows [T, T+hist) = last `hist` rows of data
+    for (int e = threadIdx.x * 4; e < total; e += blockDim.x * 4) store4(state + e, load4(tail + e));
+  }
+}
+
+cudaError_t launch_hist_gather(const HistTable& t, const int* slot_ids, int type, int n, cudaStream_t st) {
+  dim3 grid(n, t.count);
+  if (type == 0) hist_move_kernel<float, true><<<grid, 128, 0, st>>>(t, slot_ids);
+  else hist_move_kernel<bf16, true><<<grid, 128, 0, st>>>(t, slot_ids);
+  return cudaGetLastError();
+}
+cudaError_t launch_hist_scatter(const HistTable& t, const int* slot_ids, int type, int n, cudaStream_t st) {
+  dim3 grid(n, t.count);
+  if (type == 0) hist_move_kernel<float, false><<<grid, 128, 0, st>>>(t, slot_ids);
+  else hist_move_kernel<bf16, false><<<grid, 128, 0, st>>>(t, slot_ids);
+  return cudaGetLastError();
+}
+
+// final conv C -> 1: 128 outputs per CTA, the (128 + K - 1) x C input slab staged in smem
+// with a padded row (C + 1) so that thread t reading row t + k is bank-conflict free.
+template <typename T>
+__global__ void __launch_bounds__(128)
+last_conv_kernel(const T* __restrict__ buf, const float* __restrict__ w, const float* __restrict__ b,
+                 float* __restrict__ pcm, int Tn, int C, int K) {
+  extern __shared__ float sm[];
+  float* sw = sm;               // K*C
+  float* sx = sm + K * C;       // (128+K-1) * (C+1)
+  const int i = blockIdx.y, t0 = blockIdx.x * 128;
+  const int rows = min(128, Tn - t0) + K - 1;
+  for (int e = threadIdx.x; e < K * C; e += 128) sw[e] = w[e];
+  const T* src = buf + ((long long)i * (Tn + K - 1) + t0) * C;
+  for (int e = threadIdx.x * 4; e < rows * C; e += 128 * 4) {
+    const float4 v = load4(src + e);
+    const int r = e / C, c = e - r * C;
+    float* d = sx + r * (C + 1) + c;
+    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+  }
+  __syncthreads();
+  const int t = t0 + threadIdx.x;
+  if (t >= Tn) return;
+  float acc = b[0];
+  for (int k = 0; k < K; ++k) {
+    const float* xr = sx + (threadIdx.x + k) * (C + 1);
+    const float* wr = sw + k * C;
+    for (int c = 0; c < C; ++c) acc = fmaf(wr[c], xr[c], acc);
+  }
+  pcm[(long long)i * Tn + t] = acc;
+}
+
+cudaError_t launch_last_conv(const void* buf, int buf_type, const float* w, const float* b, float* pcm,
+                             int n, int T, int C, int K, cudaStream_t st) {
+  if (C % 4) return cudaErrorInvalidValue;
+  dim3 grid((T + 127) / 128, n);
+  const size_t smem = (size_t)(K * C + (128 + K - 1) * (C + 1)) * sizeof(float);
+  if (smem > 48 * 1024) return cudaErrorInvalidValue;
+  if (buf_type == 0) last_conv_kernel<float><<<grid, 128, smem, st>>>((const float*)buf, w, b, pcm, T, C, K);
+  else last_conv_kernel<bf16><<<grid, 128, smem, st>>>((const bf16*)buf, w, b, pcm, T, C, K);
+  return cudaGetLastError();
+}
+
+__global__ void f32_to_bf16_kernel(const float* __restrict__ s, bf16* __restrict__ d, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    d[i] = __float2bfloat16_rn(s[i]);
+}
+cudaError_t launch_f32_to_bf16(const float* src, bf16* dst, long long n, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  f32_to_bf16_kernel<<<(int)min(4096LL, (n + 255) / 256), 256, 0, st>>>(src, dst, n);
+  return cudaGetLastError();
+}
+__global__ void fill_f32_kernel(float* __restrict__ d, float v, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    d[i] = v;
+}
+cudaError_t launch_fill_f32(float* dst, float v, long long n, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  fill_f32_kernel<<<(int)min(4096LL, (n + 255) / 256), 256, 0, st>>>(dst, v, n);
+  return cudaGetLastError();
+}
+
+}  // namespace ptts
+
+namespace ptts {
+__global__ void bf16_to_f32_kernel(const bf16* __restrict__ s, float* __restrict__ d, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    d[i] = __bfloat162float(s[i]);
+}
+cudaError_t launch_bf16_to_f32(const bf16* src, float* dst, long long n, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  bf16_to_f32_kernel<<<(int)min(4096LL, (n + 255) / 256), 256, 0, st>>>(src, dst, n);
+  return cudaGetLastError();
+}
+}  // namespace ptts

@@ -1,0 +1,240 @@
+"""Python host side of the generation engine: owns a native engine handle, feeds it the
+reference-format state_dict and exposes prefill / step / decode on torch tensors.
+
+PyTorch is plumbing here (host/device buffers); all arithmetic of the generation path runs in
+the CUDA library behind include/pocket_tts_b200.h."""
+
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass
+
+import torch
+
+from . import _native as N
+
+
+@dataclass(frozen=True)
+class ModelConfig:
+    """Decode-path architecture (pocket_tts/config/*.yaml, utils/config.py:11-118)."""
+    n_layers: int = 6
+    d_model: int = 1024
+    n_heads: int = 16
+    ffn: int = 4096
+    ldim: int = 32
+    flow_dim: int = 512
+    flow_depth: int = 6
+    max_period: float = 10000.0
+    n_bins: int = 4000
+    insert_bos_before_voice: bool = True
+    mimi_d: int = 512
+    mimi_heads: int = 8
+    mimi_layers: int = 2
+    mimi_ffn: int = 2048
+    mimi_context: int = 250
+    n_filters: int = 64
+    ratios: tuple = (6, 5, 4)
+    kernel: int = 7
+    res_kernel: int = 3
+    last_kernel: int = 3
+    upsample_stride: int = 16
+    frame_rate: float = 12.5
+    sample_rate: int = 24000
+
+    @property
+    def frame_samples(self) -> int:
+        return int(self.sample_rate / self.frame_rate)
+
+
+def rope_freqs(head_dim: int, max_period: float) -> torch.Tensor:
+    """rope.py:28-29, evaluated exactly as the reference does (torch fp32)."""
+    ds = torch.arange(head_dim // 2, dtype=torch.float32)
+    return torch.exp(ds * (-math.log(max_period) * 2 / head_dim))
+
+
+def flow_time_table(sd: dict, lsd_steps: int) -> torch.Tensor:
+    """Input-independent constant of the flow head: (te0(i/n) + te1((i+1)/n)) / 2 for each LSD
+    step i (mlp.py:58-83,205-208 at the times of flow_lm.py:33-37).  Folded at load time."""
+    def te(idx: int, tau: float) -> torch.Tensor:
+        p = f"flow_lm.flow_net.time_embed.{idx}."
+        args = torch.tensor(float(tau), dtype=torch.float32) * sd[p + "freqs"].float()
+        emb = torch.cat([torch.cos(args), torch.sin(args)], dim=-1)
+        hid = torch.nn.functional.silu(emb @ sd[p + "mlp.0.weight"].float().t() + sd[p + "mlp.0.bias"].float())
+        hid = hid @ sd[p + "mlp.2.weight"].float().t() + sd[p + "mlp.2.bias"].float()
+        var = 1e-5 + hid.var(dim=-1, keepdim=True)  # mlp.py:20-25 (unbiased variance)
+        return hid * (sd[p + "mlp.3.alpha"].float() * torch.rsqrt(var))
+    rows = [(te(0, i / lsd_steps) + te(1, (i + 1) / lsd_steps)) / 2 for i in range(lsd_steps)]
+    return torch.stack(rows).contiguous()
+
+
+def _ptr(t: torch.Tensor | None):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _i32(values) -> "C.Array":
+    return (C.c_int32 * len(values))(*[int(v) for v in values])
+
+
+class GenerationEngine:
+    """One engine per GPU: weights, stream slots, frame step."""
+
+    def __init__(self, cfg: ModelConfig, state_dict: dict, *, max_streams: int = 64, kv_capacity: int = 1024,
+                 precision: str = "fp32", device: int = 0, lsd_steps: int = 1, max_prefill_rows: int = 4096):
+        self.cfg = cfg
+        self.lib = N.lib()
+        self.device = torch.device("cuda", device)
+        self.precision = precision
+        self.lsd_steps = lsd_steps
+        self.max_streams = max_streams
+        self.kv_capacity = kv_capacity
+        pc = N.PttsConfig()
+        for k in ("n_layers", "d_model", "n_heads", "ffn", "ldim", "flow_dim", "flow_depth", "mimi_d",
+                  "mimi_heads", "mimi_layers", "mimi_ffn", "mimi_context", "n_filters", "kernel",
+                  "res_kernel", "last_kernel", "upsample_stride"):
+            setattr(pc, k, int(getattr(cfg, k)))
+        pc.ratios = (C.c_int32 * 3)(*cfg.ratios)
+        pc.max_streams, pc.kv_capacity = max_streams, kv_capacity
+        pc.max_prefill_rows, pc.max_lsd_steps = max_prefill_rows, lsd_steps
+        pc.precision = {"fp32": N.PRECISION_FP32, "bf16": N.PRECISION_BF16}[precision]
+        pc.device = device
+        h = C.c_void_p()
+        N.check(self.lib.ptts_engine_create(C.byref(pc), C.byref(h)))
+        self._h = h
+        try:
+            self._load(state_dict)
+        except Exception:
+            self.close()
+            raise
+
+    # ---- weights
+    def _load_one(self, name: str, t: torch.Tensor) -> None:
+        t = t.detach().to("cpu", torch.float32).contiguous()
+        shape = (C.c_int64 * t.dim())(*t.shape)
+        N.check(self.lib.ptts_load_tensor(self._h, name.encode(), _ptr(t), shape, t.dim()))
+
+    def _load(self, sd: dict) -> None:
+        skip = ("flow_lm.conditioner.", "flow_lm.bos_before_voice", "flow_lm.speaker_proj_weight",
+                "flow_lm.flow_net.time_embed.")  # host-side only / folded into flow.tcomb
+        for name, t in sd.items():
+            if name.startswith(skip):
+                continue
+            self._load_one(name, t)
+        self._load_one("rope.freqs", rope_freqs(self.cfg.d_model // self.cfg.n_heads, self.cfg.max_period))
+        self._load_one("flow.tcomb", flow_time_table(sd, self.lsd_steps))
+        N.check(self.lib.ptts_finalize(self._h))
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self.lib.ptts_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- streams
+    def open_stream(self) -> int:
+        s = C.c_int32(-1)
+        N.check(self.lib.ptts_stream_open(self._h, C.byref(s)))
+        return s.value
+
+    def close_stream(self, slot: int) -> None:
+        N.check(self.lib.ptts_stream_close(self._h, slot))
+
+    def reset_decoder(self, slot: int) -> None:
+        N.check(self.lib.ptts_stream_reset_decoder(self._h, slot))
+
+    def fork(self, src: int, dst: int) -> None:
+        N.check(self.lib.ptts_stream_fork(self._h, src, dst))
+
+    def offset(self, slot: int) -> int:
+        o = C.c_int32(0)
+        N.check(self.lib.ptts_stream_get_offset(self._h, slot, C.byref(o)))
+        return o.value
+
+    def set_prev_latent(self, slot: int, latent: torch.Tensor) -> None:
+        t = latent.detach().to(torch.float32).contiguous()
+        N.check(self.lib.ptts_stream_set_prev_latent(self._h, slot, _ptr(t)))
+
+    def import_state(self, slot: int, model_state: dict) -> None:
+        """model_state in the reference format (transformer.py:46-57): per layer
+        {"offset": int64[1], "cache": float[2,1,T,H,D]}; positions >= offset are ignored."""
+        off = None
+        for i in range(self.cfg.n_layers):
+            st = model_state[f"transformer.layers.{i}.self_attn"]
+            o = int(st["offset"].view(-1)[0])
+            off = o if off is None else off
+            if o != off:
+                raise ValueError("model_state layers disagree on offset")
+            cache = st["cache"][:, 0, :o].detach().to(torch.float32).contiguous()
+            N.check(self.lib.ptts_stream_import_kv(self._h, slot, i, _ptr(cache), o))
+        N.check(self.lib.ptts_stream_set_offset(self._h, slot, off))
+
+    def export_state(self, slot: int) -> dict:
+        o = self.offset(slot)
+        out = {}
+        for i in range(self.cfg.n_layers):
+            cache = torch.empty(2, 1, o, self.cfg.n_heads, self.cfg.d_model // self.cfg.n_heads)
+            N.check(self.lib.ptts_stream_export_kv(self._h, slot, i, _ptr(cache), o))
+            out[f"transformer.layers.{i}.self_attn"] = {
+                "offset": torch.full((1,), o, dtype=torch.long), "cache": cache}
+        return out
+
+    # ---- compute
+    def prefill(self, slots, embeds: list) -> None:
+        """embeds[i]: [len_i, d_model] conditioning rows for stream slots[i]."""
+        lens = [int(e.shape[0]) for e in embeds]
+        flat = torch.cat([e.detach().to(torch.float32).reshape(-1, self.cfg.d_model) for e in embeds]).contiguous()
+        N.check(self.lib.ptts_prefill(self._h, len(slots), _i32(slots), _i32(lens), _ptr(flat)))
+
+    def step(self, slots, noise: torch.Tensor, *, lsd_steps: int | None = None, decode_audio: bool = True,
+             out_device: str = "cpu"):
+        """One frame.  Returns (latents [n,ldim], eos_logits [n], pcm [n,1920] | None)."""
+        n = len(slots)
+        noise = noise.detach().to(torch.float32).contiguous()
+        assert noise.shape == (n, self.cfg.ldim), noise.shape
+        dev = self.device if out_device == "cuda" else "cpu"
+        lat = torch.empty(n, self.cfg.ldim, dtype=torch.float32, device=dev)
+        eos = torch.empty(n, dtype=torch.float32, device=dev)
+        pcm = torch.empty(n, self.cfg.frame_samples, dtype=torch.float32, device=dev) if decode_audio else None
+        N.check(self.lib.ptts_step(self._h, n, _i32(slots), _ptr(noise), lsd_steps or self.lsd_steps,
+                                   1 if decode_audio else 0, _ptr(lat), _ptr(eos), _ptr(pcm)))
+        return lat, eos, pcm
+
+    def mimi_decode(self, slots, latents: torch.Tensor) -> torch.Tensor:
+        n = len(slots)
+        latents = latents.detach().to(torch.float32).contiguous()
+        pcm = torch.empty(n, self.cfg.frame_samples, dtype=torch.float32)
+        N.check(self.lib.ptts_mimi_decode(self._h, n, _i32(slots), _ptr(latents), _ptr(pcm)))
+        return pcm
+
+    def run_frames(self, slots, noise_dev: torch.Tensor, *, lsd_steps: int | None = None,
+                   out_pcm: torch.Tensor | None = None, out_latents: torch.Tensor | None = None) -> None:
+        """Device-resident loop: noise_dev [F, n, ldim] on the GPU; asynchronous."""
+        assert noise_dev.is_cuda and noise_dev.dtype == torch.float32 and noise_dev.is_contiguous()
+        F, n, _ = noise_dev.shape
+        N.check(self.lib.ptts_run_frames(self._h, n, _i32(slots), F, _ptr(noise_dev), lsd_steps or self.lsd_steps,
+                                         _ptr(out_pcm), _ptr(out_latents)))
+
+    def synchronize(self) -> None:
+        N.check(self.lib.ptts_synchronize(self._h))
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.ptts_launch_count(self._h))
+
+    @property
+    def cuda_stream(self) -> int:
+        return int(self.lib.ptts_stream_handle(self._h) or 0)
+
+    def set_graphs(self, enabled: bool) -> None:
+        N.check(self.lib.ptts_set_graphs(self._h, 1 if enabled else 0))
+
+    def debug_read(self, what: str, numel: int) -> torch.Tensor:
+        out = torch.empty(numel, dtype=torch.float32)
+        got = C.c_int64(0)
+        N.check(self.lib.ptts_debug_read(self._h, what.encode(), _ptr(out), numel, C.byref(got)))
+        return out[: got.value]

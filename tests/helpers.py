@@ -1,0 +1,42 @@
+"""Shared helpers for parity tests: build engines from the oracle's deterministic weights and
+drive engine and oracle with identical inputs."""
+from __future__ import annotations
+
+from pathlib import Path
+
+import numpy as np
+import torch
+
+from oracle import pocket_oracle as po
+
+GOLD = Path(__file__).parent / "golden"
+_WEIGHTS: dict = {}
+
+
+def weights(n_layers: int):
+    if n_layers not in _WEIGHTS:
+        _WEIGHTS[n_layers] = po.make_weights(po.ModelDims(n_layers=n_layers), seed=0)
+    return _WEIGHTS[n_layers]
+
+
+def make_engine(n_layers: int, *, max_streams=8, kv_capacity=256, precision="fp32", lsd_steps=1,
+                max_prefill_rows=512):
+    from pocket_tts_b200.engine import GenerationEngine, ModelConfig
+
+    cfg = ModelConfig(n_layers=n_layers)
+    return GenerationEngine(cfg, weights(n_layers), max_streams=max_streams, kv_capacity=kv_capacity,
+                            precision=precision, lsd_steps=lsd_steps, max_prefill_rows=max_prefill_rows)
+
+
+def load_case(name: str):
+    g = np.load(GOLD / f"{name}.npz")
+    ns = int(g["n_streams"])
+    case = dict(n_layers=int(g["n_layers"]), lsd=int(g["lsd_steps"]), G=int(g["G"]), ns=ns)
+    for k in ("cond", "tokens", "noise", "latents", "eos_logits", "pcm"):
+        case[k] = [torch.from_numpy(g[f"{k}_{i}"]) for i in range(ns)]
+    case["raw"] = g
+    return case
+
+
+def oracle_for(n_layers: int, lsd=1):
+    return po.Oracle(po.ModelDims(n_layers=n_layers), weights(n_layers), lsd_steps=lsd)

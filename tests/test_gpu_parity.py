@@ -1,0 +1,187 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against
+(a) the reference-generated golden fixtures and (b) the CPU oracle on the same seeded inputs.
+
+Tolerances are the north_star's: per-frame latents rel-L2 <= 1e-4 (fp32 mode), <= 2e-2 (bf16
+mode); waveform SNR >= 40 dB (fp32 mode)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import pocket_oracle as po
+from tests.helpers import load_case, make_engine, oracle_for, weights
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-4
+TOL_BF16 = 2e-2
+SNR_FP32 = 40.0
+
+
+def _prefill_streams(eng, orc, conds, toks):
+    slots = [eng.open_stream() for _ in conds]
+    voice = [orc.voice_conditioning(c[None])[0] for c in conds]
+    eng.prefill(slots, voice)                       # ragged voice prefill in one call
+    eng.prefill(slots, [orc.embed_tokens(t[None])[0] for t in toks])
+    return slots
+
+
+def _run_engine_case(eng, case, teacher=False):
+    orc = oracle_for(case["n_layers"], case["lsd"])
+    slots = _prefill_streams(eng, orc, case["cond"], case["tokens"])
+    ns, G = case["ns"], case["G"]
+    lat, logit, pcm = [], [], []
+    for g in range(G):
+        noise = torch.stack([case["noise"][i][g] for i in range(ns)])
+        if teacher and g > 0:
+            for i, s in enumerate(slots):
+                eng.set_prev_latent(s, case["latents"][i][g - 1])
+        l, e, p = eng.step(slots, noise, lsd_steps=case["lsd"])
+        lat.append(l); logit.append(e); pcm.append(p)
+    for s in slots:
+        eng.close_stream(s)
+    return torch.stack(lat), torch.stack(logit), torch.cat(pcm, dim=1)
+
+
+def _check_case(name, precision, teacher, tol, snr_min):
+    case = load_case(name)
+    eng = make_engine(case["n_layers"], precision=precision, lsd_steps=case["lsd"])
+    lat, logit, pcm = _run_engine_case(eng, case, teacher)
+    worst = 0.0
+    for i in range(case["ns"]):
+        for g in range(case["G"]):
+            e = po.rel_l2(lat[g, i], case["latents"][i][g])
+            worst = max(worst, e)
+        snr = po.snr_db(case["pcm"][i], pcm[i])
+        elog = float((logit[:, i] - case["eos_logits"][i]).abs().max())
+        print(f"{name}[{precision}{' tf' if teacher else ''}] stream {i}: worst frame latent rel-L2 "
+              f"{worst:.3e}  eos abs {elog:.3e}  pcm SNR {snr:.1f} dB")
+        if snr_min is not None:
+            assert snr >= snr_min, (name, i, snr)
+    assert worst <= tol, (name, worst)
+    eng.close()
+
+
+@pytest.mark.parametrize("name", ["gen_2l", "gen_2l_lsd2", "gen_english_6l", "gen_italian_24l"])
+def test_fp32_free_running_vs_reference_fixture(name):
+    _check_case(name, "fp32", teacher=False, tol=TOL_FP32, snr_min=SNR_FP32)
+
+
+@pytest.mark.parametrize("name", ["gen_2l", "gen_english_6l"])
+def test_fp32_teacher_forced_vs_reference_fixture(name):
+    _check_case(name, "fp32", teacher=True, tol=TOL_FP32, snr_min=None)
+
+
+@pytest.mark.parametrize("name", ["gen_2l", "gen_english_6l", "gen_italian_24l"])
+def test_bf16_teacher_forced_vs_reference_fixture(name):
+    _check_case(name, "bf16", teacher=True, tol=TOL_BF16, snr_min=None)
+
+
+def test_mimi_20_frames_vs_reference_fixture():
+    g = np.load("tests/golden/mimi_20f.npz")
+    eng = make_engine(1)
+    s = eng.open_stream()
+    lat = torch.from_numpy(g["latents"])
+    pcm = torch.cat([eng.mimi_decode([s], lat[i][None]) for i in range(lat.shape[0])], dim=1)[0]
+    snr = po.snr_db(torch.from_numpy(g["pcm"]), pcm)
+    print("mimi 20 frames (window 250 exercised) SNR", snr)
+    assert snr >= 80.0
+    eng.close()
+
+
+def test_voice_kv_export_matches_reference_cache():
+    case = load_case("gen_2l")
+    orc = oracle_for(2)
+    eng = make_engine(2)
+    s = eng.open_stream()
+    eng.prefill([s], [orc.voice_conditioning(case["cond"][0][None])[0]])
+    st = eng.export_state(s)
+    for li in (0, 1):
+        ref = torch.from_numpy(case["raw"][f"voice_kv_{li}"])  # [2,1,P,16,64]
+        got = st[f"transformer.layers.{li}.self_attn"]
+        assert int(got["offset"][0]) == ref.shape[2]
+        assert po.rel_l2(got["cache"], ref) < 1e-5
+    # import into a second slot and fork into a third: all three must continue identically
+    s2, s3 = eng.open_stream(), eng.open_stream()
+    eng.import_state(s2, st)
+    eng.fork(s, s3)
+    tok = orc.embed_tokens(case["tokens"][0][None])[0]
+    eng.prefill([s, s2, s3], [tok, tok, tok])
+    noise = case["noise"][0][0][None].repeat(3, 1)
+    lat, _, pcm = eng.step([s, s2, s3], noise)
+    assert torch.equal(lat[0], lat[1]) and torch.equal(lat[0], lat[2])
+    assert torch.equal(pcm[0], pcm[1]) and torch.equal(pcm[0], pcm[2])
+    assert po.rel_l2(lat[0], case["latents"][0][0]) <= TOL_FP32
+    eng.close()
+
+
+def test_graph_replay_is_bit_identical_to_eager():
+    case = load_case("gen_2l")
+    outs = []
+    for graphs in (False, True):
+        eng = make_engine(2)
+        eng.set_graphs(graphs)
+        outs.append(_run_engine_case(eng, case))
+        eng.close()
+    for a, b in zip(outs[0], outs[1]):
+        assert torch.equal(a, b)
+
+
+def test_batch_of_64_streams_vs_oracle_english_6l():
+    """BASELINE config 2 shape: english 6L, 64 concurrent streams, ragged voice lengths."""
+    torch.manual_seed(5)
+    B, G = 64, 3
+    orc = oracle_for(6)
+    dims = orc.d
+    P = [int(x) for x in torch.randint(4, 24, (B,))]
+    T = [int(x) for x in torch.randint(3, 12, (B,))]
+    conds = [torch.randn(p, dims.d_model) * 0.3 for p in P]
+    toks = [torch.randint(0, dims.n_bins, (t,)) for t in T]
+    noise = torch.randn(G, B, dims.ldim) * 0.7 ** 0.5
+    eng = make_engine(6, max_streams=B, kv_capacity=64, max_prefill_rows=2048)
+    slots = _prefill_streams(eng, orc, conds, toks)
+    # oracle, ragged batch
+    cb = torch.zeros(B, max(P) + 1, dims.d_model)
+    tb = torch.zeros(B, max(T), dims.d_model)
+    for i in range(B):
+        cb[i, : P[i] + 1] = orc.voice_conditioning(conds[i][None])[0]
+        tb[i, : T[i]] = orc.embed_tokens(toks[i][None])[0]
+    st = orc.new_flow_state(B, 8)
+    orc.prefill(st, cb, torch.tensor(P) + 1)
+    ref = orc.generate(st, tb, noise, text_lens=torch.tensor(T))
+    worst = 0.0
+    pcm = []
+    for g in range(G):
+        lat, _, p = eng.step(slots, noise[g])
+        pcm.append(p)
+        for i in range(B):
+            worst = max(worst, po.rel_l2(lat[i], ref["latents"][g, i]))
+    pcm = torch.cat(pcm, dim=1)
+    snr = min(po.snr_db(ref["pcm"][i], pcm[i]) for i in range(B))
+    print(f"64 streams english 6L: worst latent rel-L2 {worst:.3e}, min pcm SNR {snr:.1f} dB")
+    assert worst <= TOL_FP32 and snr >= SNR_FP32
+    eng.close()
+
+
+def test_error_conventions():
+    from pocket_tts_b200 import _native as N
+    from pocket_tts_b200.engine import GenerationEngine, ModelConfig
+
+    W = dict(weights(1))
+    bad = {k: v for k, v in W.items() if k != "flow_lm.out_norm.weight"}
+    with pytest.raises(N.NativeError) as ei:
+        GenerationEngine(ModelConfig(n_layers=1), bad, max_streams=2, kv_capacity=32)
+    assert "out_norm" in str(ei.value)
+    eng = make_engine(1, max_streams=2, kv_capacity=16)
+    a, b = eng.open_stream(), eng.open_stream()
+    with pytest.raises(N.NativeError) as ei:
+        eng.open_stream()
+    assert ei.value.code == N.PTTS_ENOSLOT
+    eng.close_stream(b)
+    with pytest.raises(N.NativeError):
+        eng.step([b], torch.zeros(1, 32))                   # closed slot
+    with pytest.raises(N.NativeError) as ei:
+        eng.prefill([a], [torch.zeros(17, 1024)])           # exceeds kv_capacity
+    assert ei.value.code == N.PTTS_ENOSLOT
+    with pytest.raises(N.NativeError):
+        eng.step([a, a], torch.zeros(2, 32))                # duplicate slot
+    eng.close()
