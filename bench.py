@@ -1,0 +1,355 @@
+"""bench.py — throughput of the Pocket TTS per-frame generation path on B200.
+
+Workload (BASELINE.json configs[1]): default english model (6-layer FlowLM), 64 concurrent
+streams per GPU, voice prefix 126 positions + 40 text tokens, bf16 mode.  One step = one 80 ms
+frame for every stream of the batch (FlowLM step + flow head + Mimi decode).
+metric = audio-seconds generated per wall-second (RTFx), aggregate over all GPUs.
+
+    python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+
+Under torchrun (N > 1) every rank drives its own GPU with its own 64 streams (streams shard,
+weights replicate, no data-path collective): weak scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+FRAME_S = 0.08
+STREAMS = 64
+VOICE_P, TEXT_T = 126, 40      # SURVEY.md 8(d) synthetic inputs
+PRESET, N_LAYERS = "english", 6
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for nm, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        busy = [s for s in sm if s > 0.5 * max(sm)] if sm else []
+        return {"sm_mhz": statistics.median(busy) if busy else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------- workload
+def synth_inputs(dims, B, G, seed_base=0):
+    import torch
+    g = torch.Generator().manual_seed(1 + seed_base)
+    tokens = torch.randint(0, dims.n_bins, (B, TEXT_T), generator=g)
+    voice = torch.randn(B, VOICE_P - 1, dims.d_model, generator=g) * 0.1
+    g2 = torch.Generator().manual_seed(2 + seed_base)
+    noise = torch.randn(G, B, dims.ldim, generator=g2) * (0.7 ** 0.5)
+    return tokens, voice, noise
+
+
+def algorithmic_bytes_per_step(dims, B, ctx_len, e):
+    """weights once + FlowLM KV read + Mimi KV window + conv state + I/O."""
+    w_elems = 95_582_018 if dims.n_layers == 6 else 322_074_434
+    kv_flow = B * dims.n_layers * 2 * dims.d_model * e * (ctx_len + 1)
+    kv_mimi = B * dims.mimi_layers * 2 * dims.mimi_d * e * (min(ctx_len * 16, 265) + 16)
+    state = B * 2 * 14_720 * e
+    io = B * (dims.ldim * 4 + dims.frame_samples * 4)
+    return w_elems * e + kv_flow + kv_mimi + state + io
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    from oracle import pocket_oracle as po           # weights generator + CPU baseline only
+    from pocket_tts_b200.engine import GenerationEngine, ModelConfig
+
+    torch.cuda.set_device(local_rank)
+    dims = po.PRESETS[PRESET]
+    B, K, Wm = STREAMS, args.steps, args.warmup
+    prec = args.precision
+    e_bytes = 2 if prec == "bf16" else 4
+    W = po.make_weights(dims, seed=0)
+    eng = GenerationEngine(ModelConfig(n_layers=dims.n_layers), W, max_streams=B,
+                           kv_capacity=VOICE_P + TEXT_T + Wm + K + 8, precision=prec, device=local_rank,
+                           max_prefill_rows=B * VOICE_P)
+    emb = W["flow_lm.conditioner.embed.weight"]
+    bos = W["flow_lm.bos_before_voice"][0]
+
+    def fresh_streams(seed_base):
+        tokens, voice, noise = synth_inputs(dims, B, Wm + K, seed_base + 1000 * rank)
+        slots = [eng.open_stream() for _ in range(B)]
+        eng.prefill(slots, [torch.cat([bos, voice[i]]) for i in range(B)])
+        eng.prefill(slots, [emb[tokens[i]] for i in range(B)])
+        return slots, noise
+
+    def close(slots):
+        for s in slots:
+            eng.close_stream(s)
+
+    dist = world > 1
+    if dist:
+        import torch.distributed as td
+        td.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist:
+            td.barrier()
+        torch.cuda.synchronize()
+
+    # ---------------- device-resident timed region (value) ----------------
+    slots, noise = fresh_streams(0)
+    noise_dev = noise.cuda()
+    stream = torch.cuda.ExternalStream(eng.cuda_stream)
+    pcm_dev = torch.empty(B, K * dims.frame_samples, device="cuda")
+    eng.run_frames(slots, noise_dev[:Wm].contiguous())          # warm-up (captures the graph)
+    eng.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    launches0 = eng.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    eng.run_frames(slots, noise_dev[Wm:].contiguous(), out_pcm=pcm_dev)
+    ev1.record(stream)
+    eng.synchronize()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop()
+    launches = eng.launch_count - launches0
+    assert bool(torch.isfinite(pcm_dev).all()), "non-finite PCM"
+    close(slots)
+
+    # ---------------- end-to-end through the host-buffer C-ABI call (e2e) ----------------
+    slots, noise = fresh_streams(1)
+    noise_pin = noise.pin_memory()
+    for g in range(Wm):
+        eng.step(slots, noise_pin[g])
+    barrier()
+    t0 = time.perf_counter()
+    for g in range(Wm, Wm + K):
+        lat, eos, pcm = eng.step(slots, noise_pin[g])          # H2D noise, D2H latents/eos/pcm, sync
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    close(slots)
+    h2d = B * dims.ldim * 4
+    d2h = B * (dims.ldim * 4 + 4 + dims.frame_samples * 4)
+
+    # ---------------- per-kernel CUDA-event pass (roofline of the dominant kernel) ----------------
+    prof = {}
+    if rank == 0:
+        slots, noise = fresh_streams(2)
+        eng.set_graphs(False)
+        for g in range(Wm):
+            eng.step(slots, noise[g])
+        eng.profile_begin()
+        PK = min(K, 32)
+        for g in range(Wm, Wm + PK):
+            eng.step(slots, noise[g])
+        prof = eng.profile_end()
+        eng.set_graphs(True)
+        close(slots)
+
+    if dist:
+        t = torch.tensor([ms, e2e_ms], device="cuda", dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if dist:
+            td.destroy_process_group()
+        return
+
+    audio_s = world * B * K * FRAME_S
+    value = audio_s / (ms / 1e3)
+    e2e_value = audio_s / (e2e_ms / 1e3)
+    # roofline: dominant kernel by summed event time
+    peaks = {}
+    pk = ROOT / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    total_prof = sum(v["total_ms"] for v in prof.values()) or 1.0
+    top = max(prof.items(), key=lambda kv: kv[1]["total_ms"]) if prof else (None, None)
+    roofline = None
+    if top[0]:
+        ctx_mid = VOICE_P + TEXT_T + Wm + min(K, 32) // 2
+        per_launch = kernel_algorithmic_bytes(top[0], dims, B, ctx_mid, e_bytes)
+        avg_ms = top[1]["total_ms"] / top[1]["count"]
+        ach = per_launch / (avg_ms / 1e3) / 1e9
+        roofline = {"kernel": top[0], "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak,
+                    "unit": "GB/s", "frac": round(ach / hbm_peak, 4), "traffic": None,
+                    "avg_launch_us": round(avg_ms * 1e3, 2), "share_of_step": round(top[1]["total_ms"] / total_prof, 3),
+                    "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback"}
+    ctx_avg = VOICE_P + TEXT_T + Wm + K / 2
+    step_bytes = algorithmic_bytes_per_step(dims, B, ctx_avg, e_bytes)
+    step_frac = step_bytes / (ms / K / 1e3) / 1e9 / hbm_peak
+
+    cpu = cpu_baseline(dims, W, sample_streams=8, frames=4)
+    line = {
+        "metric": "audio-sec generated per sec (RTFx), batched", "value": round(value, 1), "unit": "audio-s/s",
+        "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": round(ms / K, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": prec, "data": "synthetic",
+        "config": {"workload": f"default english model ({dims.n_layers}L FlowLM), {B} concurrent streams per GPU, "
+                               f"voice prefix {VOICE_P} + {TEXT_T} text tokens, lsd_steps 1, frame step = FlowLM + flow head + Mimi decode",
+                   "streams_per_gpu": B, "precision": prec, "parallelism": f"streams sharded x{world}, no collective",
+                   "l2_policy": "working set per step (weights + KV, >= 0.6 GB) exceeds the 126 MB L2; no flush"},
+        "e2e": {"value": round(e2e_value, 1), "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": round(e2e_ms / K, 4), "api": "ptts_step (host buffers) via pocket_tts_b200.GenerationEngine.step"},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+        "step_roofline": {"bound": "hbm", "algorithmic_bytes_per_step": int(step_bytes), "frac_of_hbm_peak": round(step_frac, 4)},
+        "cpu_baseline": cpu,
+        "kernel_ms_share": {k: round(v["total_ms"] / total_prof, 4) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["total_ms"])[:12]},
+    }
+    print(json.dumps(line), flush=True)
+    if dist:
+        td.destroy_process_group()
+
+
+def kernel_algorithmic_bytes(tag, dims, B, ctx, e):
+    """Algorithmic bytes one launch of `tag` must move (DESIGN.md kernel table)."""
+    d, ffn = dims.d_model, dims.ffn
+    if tag == "flow.attn_decode":
+        return B * 2 * d * e * (ctx + 1) + B * 3 * d * 4 + B * d * e
+    gemm = {"flow.qkv": (3 * d, d), "flow.out_proj": (d, d), "flow.ffn1": (ffn, d), "flow.ffn2": (d, ffn),
+            "mimi.qkv": (1536, 512), "mimi.out_proj": (512, 512), "mimi.ffn1": (2048, 512), "mimi.ffn2": (512, 2048)}
+    if tag in gemm:
+        N, K = gemm[tag]
+        rows = B * (16 if tag.startswith("mimi") else 1)
+        return N * K * e + rows * K * e + rows * N * 4
+    conv = {  # (rows per stream, K, N, extra outputs)
+        "seanet.conv0": (16, 3584, 512), "seanet.convtr0": (16, 1024, 1536), "seanet.res0.conv3": (96, 768, 128),
+        "seanet.res0.conv1": (96, 128, 256), "seanet.convtr1": (96, 512, 640), "seanet.res1.conv3": (480, 384, 64),
+        "seanet.res1.conv1": (480, 64, 128), "seanet.convtr2": (480, 256, 256), "seanet.res2.conv3": (1920, 192, 32),
+        "seanet.res2.conv1": (1920, 32, 64)}
+    if tag in conv:
+        T, K, N = conv[tag]
+        uniq_in = K // (7 if tag == "seanet.conv0" else (2 if "convtr" in tag else (3 if "conv3" in tag else 1)))
+        out_mult = 2 if "convtr" in tag else 1
+        res = N if "conv1" in tag else 0
+        return N * K * e + B * T * (uniq_in + out_mult * N + res) * e
+    return 0
+
+
+# --------------------------------------------------------------------------- CPU arm
+def cpu_baseline(dims, W, sample_streams=8, frames=4, threads=None):
+    """The CPU port of the reference path (oracle) on this box's host cores, bounded sample."""
+    import torch
+    from oracle import pocket_oracle as po
+    threads = threads or os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    orc = po.Oracle(dims, W)
+    tokens, voice, noise = synth_inputs(dims, sample_streams, frames + 1)
+    st = orc.new_flow_state(sample_streams, VOICE_P + TEXT_T + frames + 2)
+    with torch.no_grad():
+        orc.prefill(st, orc.voice_conditioning(voice))
+        orc.prefill(st, orc.embed_tokens(tokens))
+        mst = orc.new_mimi_state(sample_streams, frames + 1)
+        prev = torch.full((sample_streams, dims.ldim), float("nan"))
+        lat, _ = orc.flow_step(st, prev, noise[0]); orc.mimi_step(mst, lat)        # warm-up frame
+        t0 = time.perf_counter()
+        for g in range(1, frames + 1):
+            lat, _ = orc.flow_step(st, lat, noise[g])
+            orc.mimi_step(mst, lat)
+        dt = time.perf_counter() - t0
+    return {"value": round(sample_streams * frames * FRAME_S / dt, 2), "unit": "audio-s/s", "cores": threads,
+            "kind": "port", "sample": f"oracle (torch fp32 CPU restatement), {sample_streams} streams x {frames} frames "
+            f"at context {VOICE_P + TEXT_T}, {threads} torch threads"}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    import torch
+    from oracle import pocket_oracle as po
+    dims = po.PRESETS[PRESET]
+    W = po.make_weights(dims, seed=0)
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    Bs = 16   # bounded sample of the 64-stream workload per step
+    K, Wm = args.steps, args.warmup
+    orc = po.Oracle(dims, W)
+    tokens, voice, noise = synth_inputs(dims, Bs, Wm + K)
+    with torch.no_grad():
+        st = orc.new_flow_state(Bs, VOICE_P + TEXT_T + Wm + K + 2)
+        orc.prefill(st, orc.voice_conditioning(voice))
+        orc.prefill(st, orc.embed_tokens(tokens))
+        mst = orc.new_mimi_state(Bs, Wm + K)
+        lat = torch.full((Bs, dims.ldim), float("nan"))
+        for g in range(Wm):
+            lat, _ = orc.flow_step(st, lat, noise[g]); orc.mimi_step(mst, lat)
+        t0 = time.perf_counter()
+        for g in range(Wm, Wm + K):
+            lat, _ = orc.flow_step(st, lat, noise[g]); orc.mimi_step(mst, lat)
+        dt = time.perf_counter() - t0
+    value = Bs * K * FRAME_S / dt
+    sample = f"oracle port of the reference CPU path, {Bs} of the {STREAMS} streams per step, {threads} torch threads"
+    line = {"impl": "reference", "metric": "audio-sec generated per sec (RTFx), batched", "value": round(value, 2),
+            "unit": "audio-s/s", "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": round(dt / K * 1e3, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"default english model ({dims.n_layers}L FlowLM), {STREAMS} concurrent streams per GPU, "
+                                   f"voice prefix {VOICE_P} + {TEXT_T} text tokens (CPU arm: {Bs}-stream sample per step)"},
+            "cpu_baseline": {"value": round(value, 2), "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": round(value, 2), "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=96)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

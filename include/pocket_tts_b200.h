@@ -141,6 +141,12 @@ int ptts_set_graphs(ptts_engine* e, int32_t enabled);
 int ptts_debug_read(ptts_engine* e, const char* what, float* out_any, int64_t max_elems,
                     int64_t* n_out);
 
+/* Per-kernel timing with CUDA events on the engine stream (eager launches between begin and
+ * end; graph replay is bypassed by the caller with ptts_set_graphs(e, 0)).  profile_end writes a
+ * JSON object {"<kernel tag>": {"count": n, "total_ms": t}, ...} into json_out. */
+int ptts_profile_begin(ptts_engine* e);
+int ptts_profile_end(ptts_engine* e, char* json_out, int64_t capacity);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,8 @@ def load_library() -> C.CDLL:
         "ptts_stream_handle": (p, [p]),
         "ptts_set_graphs": (C.c_int, [p, i32]),
         "ptts_debug_read": (C.c_int, [p, C.c_char_p, f32p, i64, C.POINTER(i64)]),
+        "ptts_profile_begin": (C.c_int, [p]),
+        "ptts_profile_end": (C.c_int, [p, C.c_char_p, i64]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -140,4 +140,9 @@ int ptts_debug_read(ptts_engine* e, const char* what, float* out_any, int64_t ma
   API_BEGIN NEED(e) return e->impl->debug_read(what, out_any, max_elems, n_out); API_END
 }
 
+int ptts_profile_begin(ptts_engine* e) { API_BEGIN NEED(e) return e->impl->profile_begin(); API_END }
+int ptts_profile_end(ptts_engine* e, char* json_out, int64_t capacity) {
+  API_BEGIN NEED(e) return e->impl->profile_end(json_out, capacity); API_END
+}
+
 }  // extern "C"

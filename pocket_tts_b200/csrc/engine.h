@@ -87,6 +87,8 @@ class Engine {
   int run_frames(int n, const int* slots, int n_frames, const float* noise_dev, int lsd,
                  float* out_pcm_dev, float* out_lat_dev);
   int debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out);
+  int profile_begin();
+  int profile_end(char* json_out, int64_t cap);
 
   ptts_config cfg;
   cudaStream_t stream = nullptr;
@@ -101,8 +103,10 @@ class Engine {
   int make_mat(const std::string& name, int N, int K, Mat* m, bool want_b16 = true);
   int make_mat_from(const std::vector<float>& host, int N, int K, Mat* m, bool want_b16 = true);
   float* upload(const std::vector<float>& host);
-  int gemm(const void* A, bool a_is_act, RowMap amap, const Mat& W, int M, GemmEpilogue ep,
+  int gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, const Mat& W, int M, GemmEpilogue ep,
            bool out_is_act);
+  void prof_begin(const char* tag);
+  void prof_end();
   int transformer_layer_common(const LayerW& L, float* h, int rows, int d, int ffn, void* a,
                                float* qkv, void* ao, void* mid, bool mimi, int li, int n);
   int flow_sequence(int n, int lsd);
@@ -154,6 +158,12 @@ class Engine {
   void* b_last;                   // [n][2+1920][64]
   HistTable hist_tab{};
   int frame_T0 = 16;
+
+  // per-kernel CUDA-event profiling (eager mode only)
+  struct ProfRec { const char* tag; cudaEvent_t a, b; };
+  bool prof_on = false;
+  std::vector<ProfRec> prof_recs;
+  std::vector<cudaEvent_t> prof_pool;
 
   std::map<GraphKey, GraphEntry> graphs;
   std::vector<int> cur_slots;

@@ -289,6 +289,62 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
   return PTTS_OK;
 }
 
+// ---- per-kernel CUDA-event profiling: events are recorded on the engine stream around every
+// launch (eager mode), aggregated per tag at profile_end().
+void Engine::prof_begin(const char* tag) {
+  if (!prof_on) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(stream, &cs);
+  if (cs != cudaStreamCaptureStatusNone) return;
+  ProfRec r{tag, nullptr, nullptr};
+  cudaEventCreate(&r.a);
+  cudaEventCreate(&r.b);
+  cudaEventRecord(r.a, stream);
+  prof_recs.push_back(r);
+}
+void Engine::prof_end() {
+  if (!prof_on || prof_recs.empty() || prof_recs.back().b == nullptr) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  cudaStreamIsCapturing(stream, &cs);
+  if (cs != cudaStreamCaptureStatusNone) return;
+  cudaEventRecord(prof_recs.back().b, stream);
+}
+int Engine::profile_begin() {
+  for (auto& r : prof_recs) { cudaEventDestroy(r.a); cudaEventDestroy(r.b); }
+  prof_recs.clear();
+  prof_on = true;
+  return PTTS_OK;
+}
+int Engine::profile_end(char* json_out, int64_t cap) {
+  prof_on = false;
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  std::map<std::string, std::pair<long long, double>> agg;
+  for (auto& r : prof_recs) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.a, r.b) == cudaSuccess) {
+      auto& a = agg[r.tag];
+      a.first += 1;
+      a.second += ms;
+    }
+    cudaEventDestroy(r.a);
+    cudaEventDestroy(r.b);
+  }
+  prof_recs.clear();
+  std::string js = "{";
+  bool first = true;
+  for (auto& kv : agg) {
+    char b[256];
+    snprintf(b, sizeof b, "%s\"%s\": {\"count\": %lld, \"total_ms\": %.6f}", first ? "" : ", ", kv.first.c_str(),
+             kv.second.first, kv.second.second);
+    js += b;
+    first = false;
+  }
+  js += "}";
+  if (!json_out || (int64_t)js.size() + 1 > cap) PTTS_FAIL(PTTS_EINVAL, "profile_end: buffer too small (%zu needed)", js.size() + 1);
+  std::memcpy(json_out, js.c_str(), js.size() + 1);
+  return PTTS_OK;
+}
+
 int Engine::debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out) {
   NEED_READY();
   const std::string w(what ? what : "");

@@ -5,20 +5,24 @@
 
 namespace ptts {
 
-static const RowMap kPlain{0, 1 << 30, 1 << 30, 0};
+static const char* kTrTag[3] = {"seanet.convtr0", "seanet.convtr1", "seanet.convtr2"};
+static const char* kC3Tag[3] = {"seanet.res0.conv3", "seanet.res1.conv3", "seanet.res2.conv3"};
+static const char* kC1Tag[3] = {"seanet.res0.conv1", "seanet.res1.conv1", "seanet.res2.conv1"};
 static inline RowMap plain(int ld) { return RowMap{0, 1 << 30, 1 << 30, ld}; }
 static inline RowMap batched(long long bs, int rpb, int valid, int ld) { return RowMap{bs, rpb, valid, ld}; }
 
-#define LAUNCH(expr)            \
+#define LAUNCH(tag, expr)       \
   do {                          \
+    prof_begin(tag);            \
     PTTS_CUDA_CHECK(expr);      \
+    prof_end();                 \
     ++launches;                 \
   } while (0)
 
 // D = epilogue(A W^T).  a_is_act: A stored in the activation type (else fp32);
 // out_is_act: out / out2 / res stored in the activation type (else fp32).
-int Engine::gemm(const void* A, bool a_is_act, RowMap amap, const Mat& W, int M, GemmEpilogue ep,
-                 bool out_is_act) {
+int Engine::gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, const Mat& W, int M,
+                 GemmEpilogue ep, bool out_is_act) {
   GemmProblem p;
   p.A = A; p.a_map = amap; p.M = M; p.N = W.N; p.K = W.K; p.ep = ep;
   const int in_type = a_is_act ? act_type : 0;
@@ -30,7 +34,7 @@ int Engine::gemm(const void* A, bool a_is_act, RowMap amap, const Mat& W, int M,
     p.W = W.f32;
   }
   if (in_type == 0 && out_type == 1) PTTS_FAIL(PTTS_ESTATE, "unsupported GEMM type combination");
-  LAUNCH(gemm_simt_launch(p, in_type, out_type, stream));
+  LAUNCH(tag, gemm_simt_launch(p, in_type, out_type, stream));
   return PTTS_OK;
 }
 
@@ -39,34 +43,34 @@ int Engine::gemm(const void* A, bool a_is_act, RowMap amap, const Mat& W, int M,
 int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int d, int ffn, void* a,
                                      float* qkvb, void* ao, void* midb, bool mimi, int li, int n) {
   int rc;
-  LAUNCH(launch_ln_rows(hbuf, L.n1w, L.n1b, 1e-5f, a, act_type, rows, d, stream));
+  LAUNCH(mimi ? "mimi.ln" : "flow.ln", launch_ln_rows(hbuf, L.n1w, L.n1b, 1e-5f, a, act_type, rows, d, stream));
   {
     GemmEpilogue ep; ep.out = qkvb; ep.out_map = plain(3 * d);
-    if ((rc = gemm(a, true, plain(d), L.in_proj, rows, ep, false)) != PTTS_OK) return rc;
+    if ((rc = gemm(mimi ? "mimi.qkv" : "flow.qkv", a, true, plain(d), L.in_proj, rows, ep, false)) != PTTS_OK) return rc;
   }
   if (mimi) {
-    LAUNCH(launch_attn_chunk(qkvb, rope_freqs, mimi_offsets, d_slot_ids, d_mimi_row_start, d_mimi_lens,
+    LAUNCH("mimi.attn", launch_attn_chunk(qkvb, rope_freqs, mimi_offsets, d_slot_ids, d_mimi_row_start, d_mimi_lens,
                              kv_mimi, li, cfg.mimi_context, ao, act_type, n, stream));
   } else if (rows == n) {
-    LAUNCH(launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, kv_flow, li, ao, act_type, n, stream));
+    LAUNCH("flow.attn_decode", launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, kv_flow, li, ao, act_type, n, stream));
   } else {
-    LAUNCH(launch_attn_chunk(qkvb, rope_freqs, offsets, d_slot_ids, d_row_start, d_lens, kv_flow, li,
+    LAUNCH("flow.attn_prefill", launch_attn_chunk(qkvb, rope_freqs, offsets, d_slot_ids, d_row_start, d_lens, kv_flow, li,
                              INT_MAX / 2, ao, act_type, n, stream));
   }
   {
     GemmEpilogue ep; ep.out = hbuf; ep.out_map = plain(d); ep.res = hbuf; ep.res_map = plain(d);
     ep.colscale = L.ls1;
-    if ((rc = gemm(ao, true, plain(d), L.out_proj, rows, ep, false)) != PTTS_OK) return rc;
+    if ((rc = gemm(mimi ? "mimi.out_proj" : "flow.out_proj", ao, true, plain(d), L.out_proj, rows, ep, false)) != PTTS_OK) return rc;
   }
-  LAUNCH(launch_ln_rows(hbuf, L.n2w, L.n2b, 1e-5f, a, act_type, rows, d, stream));
+  LAUNCH(mimi ? "mimi.ln" : "flow.ln", launch_ln_rows(hbuf, L.n2w, L.n2b, 1e-5f, a, act_type, rows, d, stream));
   {
     GemmEpilogue ep; ep.out = midb; ep.out_map = plain(ffn); ep.act_pre = ACT_GELU;
-    if ((rc = gemm(a, true, plain(d), L.lin1, rows, ep, true)) != PTTS_OK) return rc;
+    if ((rc = gemm(mimi ? "mimi.ffn1" : "flow.ffn1", a, true, plain(d), L.lin1, rows, ep, true)) != PTTS_OK) return rc;
   }
   {
     GemmEpilogue ep; ep.out = hbuf; ep.out_map = plain(d); ep.res = hbuf; ep.res_map = plain(d);
     ep.colscale = L.ls2;
-    if ((rc = gemm(midb, true, plain(ffn), L.lin2, rows, ep, false)) != PTTS_OK) return rc;
+    if ((rc = gemm(mimi ? "mimi.ffn2" : "flow.ffn2", midb, true, plain(ffn), L.lin2, rows, ep, false)) != PTTS_OK) return rc;
   }
   return PTTS_OK;
 }
@@ -77,51 +81,51 @@ int Engine::flow_sequence(int n, int lsd) {
   const int D = c.d_model, F = c.flow_dim, Ld = c.ldim;
   const int modld = (c.flow_depth * 3 + 2) * F;
   int rc;
-  LAUNCH(launch_flow_embed(prev_latent, d_slot_ids, bos_emb, w_in, h, n, D, Ld, stream));
+  LAUNCH("flow.embed", launch_flow_embed(prev_latent, d_slot_ids, bos_emb, w_in, h, n, D, Ld, stream));
   for (int l = 0; l < c.n_layers; ++l)
     if ((rc = transformer_layer_common(flow_layers[l], h, n, D, c.ffn, a_ln, qkv, attn_o, mid, false, l, n)) != PTTS_OK)
       return rc;
-  LAUNCH(launch_final_norm_eos(h, out_norm_w, out_norm_b, 1e-5f, eos_w, eos_b, c_cond, act_type, eos_logit, n, D, stream));
-  LAUNCH(launch_advance(offsets, d_slot_ids, nullptr, 1, n, stream));
+  LAUNCH("flow.final_norm_eos", launch_final_norm_eos(h, out_norm_w, out_norm_b, 1e-5f, eos_w, eos_b, c_cond, act_type, eos_logit, n, D, stream));
+  LAUNCH("advance", launch_advance(offsets, d_slot_ids, nullptr, 1, n, stream));
   // LSD / Euler integration from the injected noise (flow_lm.py:32-40)
   PTTS_CUDA_CHECK(cudaMemcpyAsync(x_lat, noise_buf, (size_t)n * Ld * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   {
     GemmEpilogue ep; ep.bias = cond_b; ep.out = cemb; ep.out_map = plain(F);
-    if ((rc = gemm(c_cond, true, plain(D), cond_embed, n, ep, false)) != PTTS_OK) return rc;
+    if ((rc = gemm("head.cond_embed", c_cond, true, plain(D), cond_embed, n, ep, false)) != PTTS_OK) return rc;
   }
   for (int s = 0; s < lsd; ++s) {
-    LAUNCH(launch_silu_add(cemb, tcomb + (size_t)s * F, sy, act_type, n, F, stream));
+    LAUNCH("head.silu_add", launch_silu_add(cemb, tcomb + (size_t)s * F, sy, act_type, n, F, stream));
     {
       GemmEpilogue ep; ep.bias = mod_b; ep.out = mod; ep.out_map = plain(modld);
-      if ((rc = gemm(sy, true, plain(F), mod_all, n, ep, false)) != PTTS_OK) return rc;
+      if ((rc = gemm("head.adaln_mod", sy, true, plain(F), mod_all, n, ep, false)) != PTTS_OK) return rc;
     }
     {
       GemmEpilogue ep; ep.bias = inproj_b; ep.out = u; ep.out_map = plain(F);
-      if ((rc = gemm(x_lat, false, plain(Ld), input_proj, n, ep, false)) != PTTS_OK) return rc;
+      if ((rc = gemm("head.input_proj", x_lat, false, plain(Ld), input_proj, n, ep, false)) != PTTS_OK) return rc;
     }
     for (int j = 0; j < c.flow_depth; ++j) {
       const FlowBlockW& w = flow_blocks[j];
       const float* mj = mod + (size_t)j * 3 * F;  // shift | scale | gate  (mlp.py:108)
-      LAUNCH(launch_ln_modulate(u, w.lnw, w.lnb, mj, mj + F, modld, g, act_type, n, F, stream));
+      LAUNCH("head.ln_modulate", launch_ln_modulate(u, w.lnw, w.lnb, mj, mj + F, modld, g, act_type, n, F, stream));
       {
         GemmEpilogue ep; ep.bias = w.b0; ep.act_pre = ACT_SILU; ep.out = g1; ep.out_map = plain(F);
-        if ((rc = gemm(g, true, plain(F), w.mlp0, n, ep, true)) != PTTS_OK) return rc;
+        if ((rc = gemm("head.mlp0", g, true, plain(F), w.mlp0, n, ep, true)) != PTTS_OK) return rc;
       }
       {
         GemmEpilogue ep; ep.bias = w.b2; ep.gate = mj + 2 * F; ep.gate_ld = modld;
         ep.res = u; ep.res_map = plain(F); ep.out = u; ep.out_map = plain(F);
-        if ((rc = gemm(g1, true, plain(F), w.mlp2, n, ep, false)) != PTTS_OK) return rc;
+        if ((rc = gemm("head.mlp2", g1, true, plain(F), w.mlp2, n, ep, false)) != PTTS_OK) return rc;
       }
     }
     const float* mf = mod + (size_t)c.flow_depth * 3 * F;  // shift | scale  (mlp.py:128)
-    LAUNCH(launch_ln_modulate(u, nullptr, nullptr, mf, mf + F, modld, g, act_type, n, F, stream));
+    LAUNCH("head.ln_modulate", launch_ln_modulate(u, nullptr, nullptr, mf, mf + F, modld, g, act_type, n, F, stream));
     {
       GemmEpilogue ep; ep.bias = final_b; ep.alpha = 1.0f / (float)lsd;
       ep.res = x_lat; ep.res_map = plain(Ld); ep.out = x_lat; ep.out_map = plain(Ld);
-      if ((rc = gemm(g, true, plain(F), final_lin, n, ep, false)) != PTTS_OK) return rc;
+      if ((rc = gemm("head.final", g, true, plain(F), final_lin, n, ep, false)) != PTTS_OK) return rc;
     }
   }
-  LAUNCH(launch_commit_latent(x_lat, d_slot_ids, prev_latent, nullptr, n, Ld, stream));
+  LAUNCH("head.commit", launch_commit_latent(x_lat, d_slot_ids, prev_latent, nullptr, n, Ld, stream));
   return PTTS_OK;
 }
 
@@ -130,14 +134,14 @@ int Engine::mimi_sequence(int n, const float* latents) {
   const ptts_config& c = cfg;
   const int Md = c.mimi_d, U = c.upsample_stride;
   int rc;
-  LAUNCH(launch_mimi_embed(latents, d_slot_ids, emb_std, emb_mean, wq, wup, e_prev, xm, n, Md, c.ldim, U, stream));
+  LAUNCH("mimi.embed_upsample", launch_mimi_embed(latents, d_slot_ids, emb_std, emb_mean, wq, wup, e_prev, xm, n, Md, c.ldim, U, stream));
   for (int l = 0; l < c.mimi_layers; ++l)
     if ((rc = transformer_layer_common(mimi_layers[l], xm, n * U, Md, c.mimi_ffn, m_ln, mqkv, m_attn, m_mid, true, l, n)) != PTTS_OK)
       return rc;
-  LAUNCH(launch_advance(mimi_offsets, d_slot_ids, nullptr, U, n, stream));
-  LAUNCH(launch_hist_gather(hist_tab, d_slot_ids, act_type, n, stream));
+  LAUNCH("advance", launch_advance(mimi_offsets, d_slot_ids, nullptr, U, n, stream));
+  LAUNCH("seanet.hist_gather", launch_hist_gather(hist_tab, d_slot_ids, act_type, n, stream));
   const int h0 = c.kernel - 1;
-  LAUNCH(launch_stage_rows(xm, b_conv0, act_type, n, U, Md, h0, stream));
+  LAUNCH("seanet.stage", launch_stage_rows(xm, b_conv0, act_type, n, U, Md, h0, stream));
   const size_t es = act_size;
   auto off = [&](void* base, long long elems) { return (void*)((char*)base + elems * (long long)es); };
   int T = U, C = Md;
@@ -145,7 +149,7 @@ int Engine::mimi_sequence(int n, const float* latents) {
     const int rpb = h0 + T;
     GemmEpilogue ep; ep.bias = conv0_b; ep.act_post = ACT_ELU;
     ep.out = off(b_tr[0], 1LL * C); ep.out_map = batched((long long)(1 + T) * C, rpb, T, C);
-    if ((rc = gemm(b_conv0, true, batched((long long)rpb * C, rpb, T, C), conv0, n * rpb, ep, true)) != PTTS_OK) return rc;
+    if ((rc = gemm("seanet.conv0", b_conv0, true, batched((long long)rpb * C, rpb, T, C), conv0, n * rpb, ep, true)) != PTTS_OK) return rc;
   }
   for (int i = 0; i < 3; ++i) {
     const int r = c.ratios[i], T2 = T * r, C2 = C / 2, hc = C2 / 2, rk = c.res_kernel - 1;
@@ -154,13 +158,13 @@ int Engine::mimi_sequence(int n, const float* latents) {
       GemmEpilogue ep; ep.bias = stages[i].tr_b; ep.act_post = ACT_ELU;
       ep.out2 = b_raw[i]; ep.out2_map = batched((long long)T2 * C2, rpb, T, r * C2);
       ep.out = off(b_res[i], (long long)rk * C2); ep.out_map = batched((long long)(rk + T2) * C2, rpb, T, r * C2);
-      if ((rc = gemm(b_tr[i], true, batched((long long)rpb * C, rpb, T, C), stages[i].tr, n * rpb, ep, true)) != PTTS_OK) return rc;
+      if ((rc = gemm(kTrTag[i], b_tr[i], true, batched((long long)rpb * C, rpb, T, C), stages[i].tr, n * rpb, ep, true)) != PTTS_OK) return rc;
     }
     {  // ResBlock conv K3 C2 -> C2/2 on ELU(x), ELU on the way out (seanet.py:27-41)
       const int rpb = rk + T2;
       GemmEpilogue ep; ep.bias = stages[i].c3_b; ep.act_post = ACT_ELU;
       ep.out = b_hid[i]; ep.out_map = batched((long long)T2 * hc, rpb, T2, hc);
-      if ((rc = gemm(b_res[i], true, batched((long long)rpb * C2, rpb, T2, C2), stages[i].c3, n * rpb, ep, true)) != PTTS_OK) return rc;
+      if ((rc = gemm(kC3Tag[i], b_res[i], true, batched((long long)rpb * C2, rpb, T2, C2), stages[i].c3, n * rpb, ep, true)) != PTTS_OK) return rc;
     }
     {  // ResBlock conv K1 + skip, then the ELU that precedes the next layer
       const int nh = (i < 2) ? 1 : c.last_kernel - 1;
@@ -168,12 +172,12 @@ int Engine::mimi_sequence(int n, const float* latents) {
       GemmEpilogue ep; ep.bias = stages[i].c1_b; ep.act_post = ACT_ELU;
       ep.res = b_raw[i]; ep.res_map = batched((long long)T2 * C2, T2, T2, C2);
       ep.out = off(nxt, (long long)nh * C2); ep.out_map = batched((long long)(nh + T2) * C2, T2, T2, C2);
-      if ((rc = gemm(b_hid[i], true, batched((long long)T2 * hc, T2, T2, hc), stages[i].c1, n * T2, ep, true)) != PTTS_OK) return rc;
+      if ((rc = gemm(kC1Tag[i], b_hid[i], true, batched((long long)T2 * hc, T2, T2, hc), stages[i].c1, n * T2, ep, true)) != PTTS_OK) return rc;
     }
     T = T2; C = C2;
   }
-  LAUNCH(launch_last_conv(b_last, act_type, last_w, last_b, pcm, n, T, C, c.last_kernel, stream));
-  LAUNCH(launch_hist_scatter(hist_tab, d_slot_ids, act_type, n, stream));
+  LAUNCH("seanet.last_conv", launch_last_conv(b_last, act_type, last_w, last_b, pcm, n, T, C, c.last_kernel, stream));
+  LAUNCH("seanet.hist_scatter", launch_hist_scatter(hist_tab, d_slot_ids, act_type, n, stream));
   return PTTS_OK;
 }
 

@@ -233,6 +233,16 @@ class GenerationEngine:
     def set_graphs(self, enabled: bool) -> None:
         N.check(self.lib.ptts_set_graphs(self._h, 1 if enabled else 0))
 
+    def profile_begin(self) -> None:
+        N.check(self.lib.ptts_profile_begin(self._h))
+
+    def profile_end(self) -> dict:
+        import json
+
+        buf = C.create_string_buffer(1 << 16)
+        N.check(self.lib.ptts_profile_end(self._h, buf, len(buf)))
+        return json.loads(buf.value.decode())
+
     def debug_read(self, what: str, numel: int) -> torch.Tensor:
         out = torch.empty(numel, dtype=torch.float32)
         got = C.c_int64(0)
