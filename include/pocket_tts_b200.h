@@ -141,6 +141,14 @@ int ptts_set_graphs(ptts_engine* e, int32_t enabled);
 int ptts_debug_read(ptts_engine* e, const char* what, float* out_any, int64_t max_elems,
                     int64_t* n_out);
 
+/* Test hook: D[M,N] = A W^T on bf16-rounded operands through one GEMM back-end (0 = SIMT FFMA,
+ * 1 = tcgen05).  rows_per_batch <= 0: plain A [M, ld]; otherwise A is a stack of channels-last
+ * stream buffers with overlapping rows (row t of a buffer = K elements starting at t*ld) and only
+ * rows t < valid_rows of each buffer are written; other rows of out keep the 0xff fill. */
+int ptts_debug_gemm(ptts_engine* e, int32_t backend, int32_t M, int32_t N, int32_t K, int32_t ld,
+                    int32_t rows_per_batch, int32_t valid_rows, const float* a_host, int64_t a_elems,
+                    const float* w_host, float* out_host);
+
 /* Per-kernel timing with CUDA events on the engine stream (eager launches between begin and
  * end; graph replay is bypassed by the caller with ptts_set_graphs(e, 0)).  profile_end writes a
  * JSON object {"<kernel tag>": {"count": n, "total_ms": t}, ...} into json_out. */

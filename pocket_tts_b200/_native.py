@@ -69,6 +69,7 @@ def load_library() -> C.CDLL:
         "ptts_stream_handle": (p, [p]),
         "ptts_set_graphs": (C.c_int, [p, i32]),
         "ptts_debug_read": (C.c_int, [p, C.c_char_p, f32p, i64, C.POINTER(i64)]),
+        "ptts_debug_gemm": (C.c_int, [p, i32, i32, i32, i32, i32, i32, i32, f32p, i64, f32p, f32p]),
         "ptts_profile_begin": (C.c_int, [p]),
         "ptts_profile_end": (C.c_int, [p, C.c_char_p, i64]),
     }

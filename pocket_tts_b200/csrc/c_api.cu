@@ -140,6 +140,13 @@ int ptts_debug_read(ptts_engine* e, const char* what, float* out_any, int64_t ma
   API_BEGIN NEED(e) return e->impl->debug_read(what, out_any, max_elems, n_out); API_END
 }
 
+int ptts_debug_gemm(ptts_engine* e, int32_t backend, int32_t M, int32_t N, int32_t K, int32_t ld,
+                    int32_t rows_per_batch, int32_t valid_rows, const float* a_host, int64_t a_elems,
+                    const float* w_host, float* out_host) {
+  API_BEGIN NEED(e)
+  return e->impl->debug_gemm(backend, M, N, K, ld, rows_per_batch, valid_rows, a_host, a_elems, w_host, out_host);
+  API_END
+}
 int ptts_profile_begin(ptts_engine* e) { API_BEGIN NEED(e) return e->impl->profile_begin(); API_END }
 int ptts_profile_end(ptts_engine* e, char* json_out, int64_t capacity) {
   API_BEGIN NEED(e) return e->impl->profile_end(json_out, capacity); API_END

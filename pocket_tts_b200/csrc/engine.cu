@@ -3,6 +3,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace ptts {
@@ -45,6 +46,8 @@ int Engine::init() {
     PTTS_FAIL(PTTS_EINVAL, "unknown precision %d", c.precision);
   PTTS_CUDA_CHECK(cudaSetDevice(c.device));
   PTTS_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  PTTS_CUDA_CHECK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, c.device));
+  if (const char* f = getenv("PTTS_FORCE_SIMT")) use_tc = !(f[0] == '1');
   act_type = c.precision == PTTS_PRECISION_BF16 ? 1 : 0;
   act_size = act_type ? 2 : 4;
   const int S = c.max_streams;

@@ -87,6 +87,8 @@ class Engine {
   int run_frames(int n, const int* slots, int n_frames, const float* noise_dev, int lsd,
                  float* out_pcm_dev, float* out_lat_dev);
   int debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out);
+  int debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_batch, int valid_rows,
+                 const float* a_host, long long a_elems, const float* w_host, float* out_host);
   int profile_begin();
   int profile_end(char* json_out, int64_t cap);
 
@@ -94,6 +96,8 @@ class Engine {
   cudaStream_t stream = nullptr;
   long long launches = 0;
   bool use_graphs = true;
+  bool use_tc = true;   // bf16 mode: tcgen05 GEMMs (PTTS_FORCE_SIMT=1 disables)
+  int n_sms = 148;
 
  private:
   // ---- helpers

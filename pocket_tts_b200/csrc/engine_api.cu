@@ -289,6 +289,43 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
   return PTTS_OK;
 }
 
+// Debug/test entry: D = A W^T (+bias) on bf16-rounded operands through the selected back-end
+// (0 = SIMT, 1 = tcgen05).  A is [n_batches, rows_per_batch(+taps-1 rows), ld] with overlapping
+// rows of length K when ld < K (the convolution-as-GEMM addressing).
+int Engine::debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_batch, int valid_rows,
+                       const float* a_host, long long a_elems, const float* w_host, float* out_host) {
+  float *a32 = nullptr, *w32 = nullptr, *o = nullptr;
+  bf16 *a16 = nullptr, *w16 = nullptr;
+  PTTS_CUDA_CHECK(cudaMalloc(&a32, a_elems * 4 + 512));
+  PTTS_CUDA_CHECK(cudaMalloc(&a16, a_elems * 2 + 512));
+  PTTS_CUDA_CHECK(cudaMalloc(&w32, (size_t)N * K * 4));
+  PTTS_CUDA_CHECK(cudaMalloc(&w16, (size_t)N * K * 2));
+  PTTS_CUDA_CHECK(cudaMalloc(&o, (size_t)M * N * 4));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(a32, a_host, a_elems * 4, cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(w32, w_host, (size_t)N * K * 4, cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(launch_f32_to_bf16(a32, a16, a_elems, stream));
+  PTTS_CUDA_CHECK(launch_f32_to_bf16(w32, w16, (long long)N * K, stream));
+  PTTS_CUDA_CHECK(cudaMemsetAsync(o, 0xff, (size_t)M * N * 4, stream));
+  GemmProblem p;
+  p.A = a16; p.W = w16; p.M = M; p.N = N; p.K = K;
+  const bool plain_a = rows_per_batch <= 0;
+  p.a_map = plain_a ? RowMap{0, 1 << 30, 1 << 30, ld} : RowMap{(long long)rows_per_batch * ld, rows_per_batch, valid_rows, ld};
+  p.ep.out = o;
+  p.ep.out_map = plain_a ? RowMap{0, 1 << 30, 1 << 30, N} : RowMap{(long long)rows_per_batch * N, rows_per_batch, valid_rows, N};
+  cudaError_t ce;
+  if (backend == 1) {
+    const long long a_rows = plain_a ? M : (long long)M - (K / ld - 1);
+    ce = gemm_tc_launch(p, 0, a_rows, n_sms, stream);
+  } else {
+    ce = gemm_simt_launch(p, 1, 0, stream);
+  }
+  PTTS_CUDA_CHECK(ce);
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(out_host, o, (size_t)M * N * 4, cudaMemcpyDeviceToHost, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  cudaFree(a32); cudaFree(a16); cudaFree(w32); cudaFree(w16); cudaFree(o);
+  return PTTS_OK;
+}
+
 // ---- per-kernel CUDA-event profiling: events are recorded on the engine stream around every
 // launch (eager mode), aggregated per tag at profile_end().
 void Engine::prof_begin(const char* tag) {

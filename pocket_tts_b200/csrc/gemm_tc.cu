@@ -1,0 +1,379 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a (bf16 operands, fp32 accumulate in tensor memory).
+//
+//   D[m, n] = epilogue( sum_k A[m, k] * W[n, k] )
+//
+// Warp roles (192 threads): warp 0 = TMA producer (one elected lane), warp 1 = TMEM allocator
+// + tcgen05.mma issuer (one elected lane), warps 2..5 = epilogue (tcgen05.ld -> registers ->
+// fused epilogue -> global).  Operand tiles are [rows][64 bf16] = 128-byte rows in the
+// canonical K-major SWIZZLE_128B layout, written by TMA and read by the tensor core through
+// shared-memory matrix descriptors; a ring of `stages` buffers is handed back and forth with
+// mbarriers (full: TMA complete_tx, empty: tcgen05.commit).
+//
+// Two orientations:
+//   SWAP = false : UMMA M (128 TMEM lanes) = activation rows, UMMA N = BN weight rows.
+//                  Large-M problems (Mimi transformer, SEANet convolutions as overlapping-row
+//                  GEMMs: the A tensor map simply has row stride C_in < K).
+//   SWAP = true  : UMMA M = 128 weight rows, UMMA N = all streams (<= 256).  Skinny decode
+//                  GEMMs (M = number of streams): the weight matrix is streamed exactly once
+//                  and split along K over gridDim.z so that every SM pulls HBM; partial sums
+//                  are reduced with fp32 red.global.add into the residual stream.
+#include <cuda.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "gemm.cuh"
+
+namespace ptts {
+
+// --------------------------------------------------------------------------- PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem desc] * B[smem desc], bf16 x bf16 -> fp32
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 B apart
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);   // start address, 16-byte units
+  d |= (uint64_t)1 << 16;                   // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;         // stride byte offset between 8-row core groups
+  d |= (uint64_t)1 << 46;                   // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                   // SWIZZLE_128B
+  return d;
+}
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+constexpr int BM_TC = 128;   // TMEM lanes / UMMA M
+constexpr int BK_TC = 64;    // bf16 elements per 128-byte swizzle row
+constexpr int MAX_STAGES = 8;
+
+struct TcParams {
+  int M, N;            // logical output rows (activation rows) and features
+  int num_kb;          // K / 64
+  int kb_per_split;    // k-blocks handled by one blockIdx.z
+  int stages;
+  int atomic_out;      // SWAP split-K: red.add into `out` (fp32)
+};
+
+// scalar epilogue for the swapped orientation (thread = feature n, loop over streams m)
+template <typename TO>
+__device__ __forceinline__ void epilogue_scalar(const GemmEpilogue& ep, int m, int n, float acc, bool atomic_out) {
+  const int ob = m / ep.out_map.rows_per_batch, ot = m - ob * ep.out_map.rows_per_batch;
+  if (ot >= ep.out_map.valid_rows) return;
+  TO* o = reinterpret_cast<TO*>(ep.out) + ob * ep.out_map.batch_stride + (long long)ot * ep.out_map.ld + n;
+  float x = acc;
+  if (atomic_out) {  // partial sum of one K split; residual already lives in `out`; bias added by split 0
+    if (ep.bias && blockIdx.z == 0) x += ep.bias[n];
+    if (ep.gate) x *= ep.gate[(long long)m * ep.gate_ld + n];
+    if (ep.colscale) x *= ep.colscale[n];
+    x *= ep.alpha;
+    atomicAdd(reinterpret_cast<float*>(o), x);
+    return;
+  }
+  if (ep.bias) x += ep.bias[n];
+  x = apply_act(x, ep.act_pre);
+  if (ep.gate) x *= ep.gate[(long long)m * ep.gate_ld + n];
+  if (ep.colscale) x *= ep.colscale[n];
+  x *= ep.alpha;
+  if (ep.res) {
+    const int rb = m / ep.res_map.rows_per_batch, rt = m - rb * ep.res_map.rows_per_batch;
+    x += to_f(reinterpret_cast<const TO*>(ep.res)[rb * ep.res_map.batch_stride + (long long)rt * ep.res_map.ld + n]);
+  }
+  if (ep.out2) {
+    const int b2 = m / ep.out2_map.rows_per_batch, t2 = m - b2 * ep.out2_map.rows_per_batch;
+    reinterpret_cast<TO*>(ep.out2)[b2 * ep.out2_map.batch_stride + (long long)t2 * ep.out2_map.ld + n] = from_f<TO>(x);
+  }
+  *o = from_f<TO>(apply_act(x, ep.act_post));
+}
+
+template <int BN, bool SWAP, typename TO>
+__global__ void __launch_bounds__(192, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
+               TcParams P, GemmEpilogue ep) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // carve: [stages][A 16 KB][B BN*128 B] then barriers
+  constexpr uint32_t A_BYTES = BM_TC * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
+  __shared__ __align__(8) uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = blockIdx.x * BM_TC;   // UMMA-M operand row offset
+  const int col0 = blockIdx.y * BN;      // UMMA-N operand row offset
+  const int kb0 = blockIdx.z * P.kb_per_split;
+  const int nkb = min(P.kb_per_split, P.num_kb - kb0);
+  constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_row) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_col) : "memory");
+    for (int s = 0; s < P.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer =====
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % P.stages;
+        const uint32_t ph = (i / P.stages) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);   // first pass: fresh barrier, parity 1 passes immediately
+        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+        uint8_t* a = tiles + (size_t)s * STAGE_BYTES;
+        tma_load_2d(a, &tm_row, &full_bar[s], (kb0 + i) * BK_TC, row0);
+        tma_load_2d(a + A_BYTES, &tm_col, &full_bar[s], (kb0 + i) * BK_TC, col0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer =====
+      // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at bit 17, M>>4 at bit 24
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM_TC >> 4) << 24);
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % P.stages;
+        const uint32_t ph = (i / P.stages) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES);
+        const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + A_BYTES);
+#pragma unroll
+        for (int k = 0; k < BK_TC / 16; ++k) {
+          // advance 16 bf16 = 32 bytes inside the swizzled 128-byte row: +2 in 16-byte units
+          tc_mma_bf16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (i | k) != 0);
+        }
+        tc_commit(&empty_bar[s]);   // frees the smem stage when these MMAs retire
+      }
+      tc_commit(&tmem_full_bar);    // accumulator complete
+    }
+  } else {
+    // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4 =====
+    const int q = warp & 3;
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
+    const int r = row0 + q * 32 + lane;             // UMMA-M index owned by this thread
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    if (nkb > 0) {
+#pragma unroll 1
+      for (int c = 0; c < BN; c += 16) {
+        float v[16];
+        tmem_ld16(taddr + c, v);
+        if (!SWAP) {
+          // r = activation row m, columns = features
+          if (r < P.M) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+              const int n = col0 + c + j;
+              if (n < P.N) epilogue_store4<TO>(ep, r, n, P.N, v + j);
+            }
+          }
+        } else {
+          // r = feature n, columns = activation rows (streams)
+          if (r < P.N) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int m = col0 + c + j;
+              if (m < P.M) epilogue_scalar<TO>(ep, m, r, v[j], P.atomic_out != 0);
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+// --------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor map: inner dim K (contiguous), outer dim `rows` with stride `ld` elements
+// (ld < K is allowed: overlapping rows = streaming convolution windows), box = 64 x box_rows.
+static bool make_map(CUtensorMap* out, const void* base, long long rows, int K, long long ld, int box_rows) {
+  using Key = std::tuple<const void*, long long, int, long long, int>;
+  static std::map<Key, CUtensorMap> cache;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  Key key{base, rows, K, ld, box_rows};
+  auto it = cache.find(key);
+  if (it != cache.end()) { *out = it->second; return true; }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) return false;
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK_TC, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return false;
+  cache[key] = m;
+  *out = m;
+  return true;
+}
+
+template <int BN, bool SWAP, typename TO>
+static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, const TcParams& P, const GemmEpilogue& ep,
+                              dim3 grid, cudaStream_t st) {
+  const size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + 1024;
+  static bool attr_done = false;
+  auto kern = gemm_tc_kernel<BN, SWAP, TO>;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  kern<<<grid, 192, smem, st>>>(tr, tc, P, ep);
+  return cudaGetLastError();
+}
+
+static int pick_bn(int n) {
+  if (n <= 16) return 16;
+  if (n <= 32) return 32;
+  if (n <= 64) return 64;
+  if (n <= 128) return 128;
+  return 256;
+}
+
+// rows_alloc: number of addressable A rows (for the tensor-map extent; rows beyond are zero-filled)
+cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_alloc, int n_sms, cudaStream_t st) {
+  if (p.M <= 0 || p.N <= 0) return cudaSuccess;
+  if (p.K % BK_TC != 0) return cudaErrorInvalidValue;
+  const bool plain_a = p.a_map.rows_per_batch >= (1 << 30);
+  if (!plain_a && p.a_map.batch_stride != (long long)p.a_map.rows_per_batch * p.a_map.ld) return cudaErrorInvalidValue;
+  const bool swap = plain_a && p.M <= 256 && out_type == 0;
+  TcParams P{};
+  P.M = p.M; P.N = p.N; P.num_kb = p.K / BK_TC;
+  CUtensorMap ta, tw;
+  GemmEpilogue ep = p.ep;
+  if (swap) {
+    const int bn = pick_bn(p.M);
+    if (!make_map(&tw, p.W, p.N, p.K, p.K, BM_TC)) return cudaErrorUnknown;
+    if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, bn)) return cudaErrorUnknown;
+    const int tiles = (p.N + BM_TC - 1) / BM_TC;
+    // split K so that ~all SMs stream weights; only linear epilogues can be split
+    const bool linear = ep.act_pre == ACT_NONE && ep.act_post == ACT_NONE && ep.out2 == nullptr &&
+                        (ep.res == nullptr || ep.res == ep.out);
+    int splits = 1;
+    if (linear) {
+      splits = std::max(1, std::min(P.num_kb, n_sms / tiles));
+      while (splits > 1 && (P.num_kb + splits - 1) / splits < 2) --splits;
+    }
+    P.kb_per_split = (P.num_kb + splits - 1) / splits;
+    splits = (P.num_kb + P.kb_per_split - 1) / P.kb_per_split;
+    P.atomic_out = splits > 1;
+    if (P.atomic_out && ep.res == nullptr) {
+      // no residual to accumulate onto: clear the output first
+      if (ep.out_map.rows_per_batch < (1 << 30)) return cudaErrorInvalidValue;
+      cudaError_t e = cudaMemset2DAsync(ep.out, (size_t)ep.out_map.ld * 4, 0, (size_t)p.N * 4, p.M, st);
+      if (e != cudaSuccess) return e;
+    }
+    P.stages = std::max(1, std::min(P.kb_per_split, std::min(6, (196 * 1024) / (BM_TC * 128 + bn * 128))));
+    dim3 grid(tiles, 1, splits);
+    switch (bn) {
+      case 16: return launch_cfg<16, true, float>(tw, ta, P, ep, grid, st);
+      case 32: return launch_cfg<32, true, float>(tw, ta, P, ep, grid, st);
+      case 64: return launch_cfg<64, true, float>(tw, ta, P, ep, grid, st);
+      case 128: return launch_cfg<128, true, float>(tw, ta, P, ep, grid, st);
+      default: return launch_cfg<256, true, float>(tw, ta, P, ep, grid, st);
+    }
+  }
+  const int bn = pick_bn(p.N);
+  if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
+  if (!make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
+  P.kb_per_split = P.num_kb;
+  P.atomic_out = 0;
+  P.stages = std::max(1, std::min(P.num_kb, std::min(6, (196 * 1024) / (BM_TC * 128 + bn * 128))));
+  dim3 grid((p.M + BM_TC - 1) / BM_TC, (p.N + bn - 1) / bn, 1);
+#define TC_CASE(BNV)                                                                          \
+  case BNV:                                                                                   \
+    return out_type == 0 ? launch_cfg<BNV, false, float>(ta, tw, P, ep, grid, st)             \
+                         : launch_cfg<BNV, false, bf16>(ta, tw, P, ep, grid, st);
+  switch (bn) {
+    TC_CASE(16) TC_CASE(32) TC_CASE(64) TC_CASE(128)
+    default: return out_type == 0 ? launch_cfg<256, false, float>(ta, tw, P, ep, grid, st)
+                                  : launch_cfg<256, false, bf16>(ta, tw, P, ep, grid, st);
+  }
+#undef TC_CASE
+}
+
+}  // namespace ptts

@@ -233,6 +233,15 @@ class GenerationEngine:
     def set_graphs(self, enabled: bool) -> None:
         N.check(self.lib.ptts_set_graphs(self._h, 1 if enabled else 0))
 
+    def debug_gemm(self, backend: int, a: torch.Tensor, w: torch.Tensor, *, M: int, K: int, ld: int,
+                   rows_per_batch: int = 0, valid_rows: int = 0) -> torch.Tensor:
+        a = a.detach().to(torch.float32).contiguous()
+        w = w.detach().to(torch.float32).contiguous()
+        out = torch.empty(M, w.shape[0], dtype=torch.float32)
+        N.check(self.lib.ptts_debug_gemm(self._h, backend, M, w.shape[0], K, ld, rows_per_batch, valid_rows,
+                                         _ptr(a), a.numel(), _ptr(w), _ptr(out)))
+        return out
+
     def profile_begin(self) -> None:
         N.check(self.lib.ptts_profile_begin(self._h))
 
