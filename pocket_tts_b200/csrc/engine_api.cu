@@ -320,6 +320,7 @@ int Engine::debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_ba
     ce = gemm_simt_launch(p, 1, 0, stream);
   }
   PTTS_CUDA_CHECK(ce);
+  if (backend == 1) { PTTS_CUDA_CHECK(cudaStreamSynchronize(stream)); tc_trace_dump("debug_gemm"); }
   PTTS_CUDA_CHECK(cudaMemcpyAsync(out_host, o, (size_t)M * N * 4, cudaMemcpyDeviceToHost, stream));
   PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
   cudaFree(a32); cudaFree(a16); cudaFree(w32); cudaFree(w16); cudaFree(o);

@@ -34,9 +34,10 @@ int Engine::gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, con
     p.W = W.f32;
   }
   if (in_type == 0 && out_type == 1) PTTS_FAIL(PTTS_ESTATE, "unsupported GEMM type combination");
-  if (in_type == 1 && use_tc && (p.K % 64) == 0) {
+  const bool plain_a = amap.rows_per_batch >= (1 << 30);
+  const bool skinny = plain_a && M <= 256 && ep.out_map.rows_per_batch >= (1 << 30);
+  if (in_type == 1 && use_tc && (p.K % 64) == 0 && (skinny || p.N % 32 == 0 || p.N == 16)) {
     // tcgen05 path: A rows addressable through the (possibly overlapping-row) tensor map
-    const bool plain_a = amap.rows_per_batch >= (1 << 30);
     const long long a_rows = plain_a ? M : (long long)M - (p.K / amap.ld - 1);
     LAUNCH(tag, gemm_tc_launch(p, out_type, a_rows, n_sms, stream));
     return PTTS_OK;

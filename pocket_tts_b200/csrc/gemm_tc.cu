@@ -19,6 +19,8 @@
 //                  are reduced with fp32 red.global.add into the residual stream.
 #include <cuda.h>
 
+#include <cstdio>
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -80,18 +82,6 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
   return d;
 }
 
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-
 constexpr int BM_TC = 128;   // TMEM lanes / UMMA M
 constexpr int BK_TC = 64;    // bf16 elements per 128-byte swizzle row
 constexpr int MAX_STAGES = 8;
@@ -102,41 +92,200 @@ struct TcParams {
   int kb_per_split;    // k-blocks handled by one blockIdx.z
   int stages;
   int atomic_out;      // SWAP split-K: red.add into `out` (fp32)
+  long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
 };
+#define TC_TRACE(slot) do { if (P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) P.trace[slot] = clock64(); } while (0)
 
-// scalar epilogue for the swapped orientation (thread = feature n, loop over streams m)
-template <typename TO>
-__device__ __forceinline__ void epilogue_scalar(const GemmEpilogue& ep, int m, int n, float acc, bool atomic_out) {
-  const int ob = m / ep.out_map.rows_per_batch, ot = m - ob * ep.out_map.rows_per_batch;
-  if (ot >= ep.out_map.valid_rows) return;
-  TO* o = reinterpret_cast<TO*>(ep.out) + ob * ep.out_map.batch_stride + (long long)ot * ep.out_map.ld + n;
-  float x = acc;
-  if (atomic_out) {  // partial sum of one K split; residual already lives in `out`; bias added by split 0
-    if (ep.bias && blockIdx.z == 0) x += ep.bias[n];
-    if (ep.gate) x *= ep.gate[(long long)m * ep.gate_ld + n];
-    if (ep.colscale) x *= ep.colscale[n];
-    x *= ep.alpha;
-    atomicAdd(reinterpret_cast<float*>(o), x);
-    return;
-  }
-  if (ep.bias) x += ep.bias[n];
-  x = apply_act(x, ep.act_pre);
-  if (ep.gate) x *= ep.gate[(long long)m * ep.gate_ld + n];
-  if (ep.colscale) x *= ep.colscale[n];
-  x *= ep.alpha;
-  if (ep.res) {
-    const int rb = m / ep.res_map.rows_per_batch, rt = m - rb * ep.res_map.rows_per_batch;
-    x += to_f(reinterpret_cast<const TO*>(ep.res)[rb * ep.res_map.batch_stride + (long long)rt * ep.res_map.ld + n]);
-  }
-  if (ep.out2) {
-    const int b2 = m / ep.out2_map.rows_per_batch, t2 = m - b2 * ep.out2_map.rows_per_batch;
-    reinterpret_cast<TO*>(ep.out2)[b2 * ep.out2_map.batch_stride + (long long)t2 * ep.out2_map.ld + n] = from_f<TO>(x);
-  }
-  *o = from_f<TO>(apply_act(x, ep.act_post));
+// ---- TMEM -> registers: CH consecutive fp32 columns of this thread's lane
+template <int CH> __device__ __forceinline__ void tmem_ld(uint32_t taddr, float* v);
+template <> __device__ __forceinline__ void tmem_ld<16>(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+template <> __device__ __forceinline__ void tmem_ld<32>(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// CH contiguous elements of a row <-> registers, 16-byte vector accesses
+template <int CH> __device__ __forceinline__ void row_load(const float* p, float* v) {
+#pragma unroll
+  for (int j = 0; j < CH; j += 4) { const float4 t = *reinterpret_cast<const float4*>(p + j); v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w; }
+}
+template <int CH> __device__ __forceinline__ void row_load(const bf16* p, float* v) {
+#pragma unroll
+  for (int j = 0; j < CH; j += 8) {
+    const uint4 t = *reinterpret_cast<const uint4*>(p + j);
+    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[q]));
+      v[j + 2 * q] = f.x; v[j + 2 * q + 1] = f.y;
+    }
+  }
+}
+template <int CH> __device__ __forceinline__ void row_store(float* p, const float* v) {
+#pragma unroll
+  for (int j = 0; j < CH; j += 4) *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+}
+template <int CH> __device__ __forceinline__ void row_store(bf16* p, const float* v) {
+#pragma unroll
+  for (int j = 0; j < CH; j += 8) {
+    uint32_t w[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const __nv_bfloat162 b = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
+      w[q] = *reinterpret_cast<const uint32_t*>(&b);
+    }
+    *reinterpret_cast<uint4*>(p + j) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+template <int CH> __device__ __forceinline__ void act_inplace(float* v, int act) {
+  if (act == ACT_NONE) return;
+  if (act == ACT_GELU) {
+#pragma unroll
+    for (int j = 0; j < CH; ++j) v[j] = gelu_erf(v[j]);
+  } else if (act == ACT_SILU) {
+#pragma unroll
+    for (int j = 0; j < CH; ++j) v[j] = silu_f(v[j]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < CH; ++j) v[j] = elu_f(v[j]);
+  }
+}
+
+// Row-major epilogue (SWAP = false): this thread owns output row r, columns come from TMEM.
+template <int BN, typename TO>
+__device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, const TcParams& P, uint32_t taddr, int r,
+                                              int col0, int half) {
+  constexpr int CH = BN >= 32 ? 32 : 16;
+  constexpr int NCH = BN / CH;
+  bool valid = r < P.M;
+  TO* orow = nullptr;
+  const TO* rrow = nullptr;
+  TO* o2row = nullptr;
+  if (valid) {
+    const int ob = r / ep.out_map.rows_per_batch, ot = r - ob * ep.out_map.rows_per_batch;
+    valid = ot < ep.out_map.valid_rows;
+    orow = reinterpret_cast<TO*>(ep.out) + ob * ep.out_map.batch_stride + (long long)ot * ep.out_map.ld;
+    if (ep.res) {
+      const int rb = r / ep.res_map.rows_per_batch, rt = r - rb * ep.res_map.rows_per_batch;
+      rrow = reinterpret_cast<const TO*>(ep.res) + rb * ep.res_map.batch_stride + (long long)rt * ep.res_map.ld;
+    }
+    if (ep.out2) {
+      const int b2 = r / ep.out2_map.rows_per_batch, t2 = r - b2 * ep.out2_map.rows_per_batch;
+      o2row = reinterpret_cast<TO*>(ep.out2) + b2 * ep.out2_map.batch_stride + (long long)t2 * ep.out2_map.ld;
+    }
+  }
+  const float* grow = ep.gate ? ep.gate + (long long)r * ep.gate_ld : nullptr;
+#pragma unroll 1
+  for (int ci = half; ci < NCH; ci += 2) {
+    const int c = ci * CH, n0 = col0 + c;
+    if (n0 >= P.N) break;   // uniform
+    float v[CH];
+    tmem_ld<CH>(taddr + c, v);   // warp-collective: executed by every lane
+    if (valid) {
+      float t[CH];
+      if (ep.bias) {
+        row_load<CH>(ep.bias + n0, t);
+#pragma unroll
+        for (int j = 0; j < CH; ++j) v[j] += t[j];
+      }
+      act_inplace<CH>(v, ep.act_pre);
+      if (grow) {
+        row_load<CH>(grow + n0, t);
+#pragma unroll
+        for (int j = 0; j < CH; ++j) v[j] *= t[j];
+      }
+      if (ep.colscale) {
+        row_load<CH>(ep.colscale + n0, t);
+#pragma unroll
+        for (int j = 0; j < CH; ++j) v[j] *= t[j];
+      }
+      if (ep.alpha != 1.0f) {
+#pragma unroll
+        for (int j = 0; j < CH; ++j) v[j] *= ep.alpha;
+      }
+      if (rrow) {
+        row_load<CH>(rrow + n0, t);
+#pragma unroll
+        for (int j = 0; j < CH; ++j) v[j] += t[j];
+      }
+      if (o2row) row_store<CH>(o2row + n0, v);
+      act_inplace<CH>(v, ep.act_post);
+      row_store<CH>(orow + n0, v);
+    }
+  }
+}
+
+// Swapped epilogue (SWAP = true): this thread owns feature n, TMEM columns are streams m.
+// out / res / out2 / gate are plain row-major [M, ld] here (checked on the host).
+template <int BN, typename TO>
+__device__ __forceinline__ void epilogue_cols(const GemmEpilogue& ep, const TcParams& P, uint32_t taddr, int n,
+                                              int m_base, int half) {
+  constexpr int CH = BN >= 32 ? 32 : 16;
+  constexpr int NCH = BN / CH;
+  const bool n_ok = n < P.N;
+  const bool atomic = P.atomic_out != 0;
+  const float bias = (ep.bias && n_ok && (!atomic || blockIdx.z == 0)) ? ep.bias[n] : 0.0f;
+  const float scale = ep.alpha * ((ep.colscale && n_ok) ? ep.colscale[n] : 1.0f);
+  TO* out = reinterpret_cast<TO*>(ep.out) + n;
+  const TO* res = ep.res ? reinterpret_cast<const TO*>(ep.res) + n : nullptr;
+  TO* out2 = ep.out2 ? reinterpret_cast<TO*>(ep.out2) + n : nullptr;
+  const float* gate = ep.gate ? ep.gate + n : nullptr;
+#pragma unroll 1
+  for (int ci = half; ci < NCH; ci += 2) {
+    const int c = ci * CH, m0 = m_base + c;
+    if (m0 >= P.M) break;   // uniform
+    float v[CH];
+    tmem_ld<CH>(taddr + c, v);
+    if (n_ok) {
+      const int cnt = min(CH, P.M - m0);
+#pragma unroll
+      for (int j = 0; j < CH; ++j) v[j] += bias;
+      if (!atomic) act_inplace<CH>(v, ep.act_pre);
+#pragma unroll
+      for (int j = 0; j < CH; ++j) {
+        if (j < cnt) {
+          const long long m = m0 + j;
+          float x = v[j];
+          if (gate) x *= gate[m * ep.gate_ld];
+          x *= scale;
+          TO* o = out + m * ep.out_map.ld;
+          if (atomic) {
+            atomicAdd(reinterpret_cast<float*>(o), x);
+          } else {
+            if (res) x += to_f(res[m * ep.res_map.ld]);
+            if (out2) out2[m * ep.out2_map.ld] = from_f<TO>(x);
+            *o = from_f<TO>(apply_act(x, ep.act_post));
+          }
+        }
+      }
+    }
+  }
+}
+
+constexpr int TC_THREADS = 64 + 256;   // producer warp, MMA warp, 8 epilogue warps
+
 template <int BN, bool SWAP, typename TO>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
                TcParams P, GemmEpilogue ep) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -170,30 +319,34 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_smem;
+  if (warp == 2) TC_TRACE(0);
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ===== TMA producer =====
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % P.stages;
-        const uint32_t ph = (i / P.stages) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);   // first pass: fresh barrier, parity 1 passes immediately
+    // ===== TMA producer: the whole warp walks the ring, one lane issues =====
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % P.stages;
+      const uint32_t ph = (i / P.stages) & 1;
+      mbar_wait(&empty_bar[s], ph ^ 1);   // first pass: fresh barrier, parity 1 passes immediately
+      TC_TRACE(8 + i * 4 + 0);
+      if (lane == 0) {
         mbar_expect_tx(&full_bar[s], STAGE_BYTES);
         uint8_t* a = tiles + (size_t)s * STAGE_BYTES;
         tma_load_2d(a, &tm_row, &full_bar[s], (kb0 + i) * BK_TC, row0);
         tma_load_2d(a + A_BYTES, &tm_col, &full_bar[s], (kb0 + i) * BK_TC, col0);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ===== MMA issuer =====
-      // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at bit 17, M>>4 at bit 24
-      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM_TC >> 4) << 24);
-      for (int i = 0; i < nkb; ++i) {
-        const int s = i % P.stages;
-        const uint32_t ph = (i / P.stages) & 1;
-        mbar_wait(&full_bar[s], ph);
-        tc_fence_after();
+    // ===== MMA issuer: whole warp waits, one lane issues =====
+    // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at bit 17, M>>4 at bit 24
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM_TC >> 4) << 24);
+    for (int i = 0; i < nkb; ++i) {
+      const int s = i % P.stages;
+      const uint32_t ph = (i / P.stages) & 1;
+      mbar_wait(&full_bar[s], ph);
+      tc_fence_after();
+      TC_TRACE(8 + i * 4 + 1);
+      if (lane == 0) {
         const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES);
         const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + A_BYTES);
 #pragma unroll
@@ -202,43 +355,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
           tc_mma_bf16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (i | k) != 0);
         }
         tc_commit(&empty_bar[s]);   // frees the smem stage when these MMAs retire
+        if (i == nkb - 1) tc_commit(&tmem_full_bar);    // accumulator complete
       }
-      tc_commit(&tmem_full_bar);    // accumulator complete
+      TC_TRACE(8 + i * 4 + 2);
+      __syncwarp();
     }
+    if (nkb == 0 && lane == 0) tc_commit(&tmem_full_bar);
   } else {
-    // ===== epilogue warps 2..5: TMEM lane quarter = warp % 4 =====
-    const int q = warp & 3;
+    // ===== epilogue warps 2..9: TMEM lane quarter = warp % 4, two warps share a quarter and
+    // split its column chunks =====
+    const int q = warp & 3, half = (warp - 2) >> 2;
+    if (warp == 2) TC_TRACE(1);
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
+    if (warp == 2) TC_TRACE(2);
     const int r = row0 + q * 32 + lane;             // UMMA-M index owned by this thread
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
     if (nkb > 0) {
-#pragma unroll 1
-      for (int c = 0; c < BN; c += 16) {
-        float v[16];
-        tmem_ld16(taddr + c, v);
-        if (!SWAP) {
-          // r = activation row m, columns = features
-          if (r < P.M) {
-#pragma unroll
-            for (int j = 0; j < 16; j += 4) {
-              const int n = col0 + c + j;
-              if (n < P.N) epilogue_store4<TO>(ep, r, n, P.N, v + j);
-            }
-          }
-        } else {
-          // r = feature n, columns = activation rows (streams)
-          if (r < P.N) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              const int m = col0 + c + j;
-              if (m < P.M) epilogue_scalar<TO>(ep, m, r, v[j], P.atomic_out != 0);
-            }
-          }
-        }
-      }
+      if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half);
+      else epilogue_rows<BN, TO>(ep, P, taddr, r, col0, half);
     }
     tc_fence_before();
+    if (warp == 2) TC_TRACE(3);
   }
   __syncthreads();
   if (warp == 1) {
@@ -302,8 +440,30 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  kern<<<grid, 192, smem, st>>>(tr, tc, P, ep);
+  kern<<<grid, TC_THREADS, smem, st>>>(tr, tc, P, ep);
   return cudaGetLastError();
+}
+
+// debug trace (PTTS_TC_TRACE=1): 8 + 4*kb slots of clock64 stamps, dumped by tc_trace_dump()
+static long long* g_trace = nullptr;
+static long long* tc_trace_buffer() {
+  static int enabled = -1;
+  if (enabled < 0) { const char* e = getenv("PTTS_TC_TRACE"); enabled = (e && e[0] == '1') ? 1 : 0; }
+  if (!enabled) return nullptr;
+  if (!g_trace) { cudaMalloc(&g_trace, 1024 * sizeof(long long)); }
+  cudaMemset(g_trace, 0, 1024 * sizeof(long long));
+  return g_trace;
+}
+void tc_trace_dump(const char* what) {
+  if (!g_trace) return;
+  long long h[1024];
+  cudaDeviceSynchronize();
+  cudaMemcpy(h, g_trace, sizeof h, cudaMemcpyDeviceToHost);
+  const long long t0 = h[0];
+  fprintf(stderr, "[tc trace %s] epi: wait_begin %lld tmem_full %lld epi_done %lld\n", what, h[1] - t0, h[2] - t0, h[3] - t0);
+  for (int i = 0; i < 64 && h[8 + i * 4 + 1]; ++i)
+    fprintf(stderr, "  kb %2d: producer_got_empty %7lld  mma_got_full %7lld  mma_issued %7lld\n", i, h[8 + i * 4] - t0,
+            h[8 + i * 4 + 1] - t0, h[8 + i * 4 + 2] - t0);
 }
 
 static int pick_bn(int n) {
@@ -320,9 +480,13 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   if (p.K % BK_TC != 0) return cudaErrorInvalidValue;
   const bool plain_a = p.a_map.rows_per_batch >= (1 << 30);
   if (!plain_a && p.a_map.batch_stride != (long long)p.a_map.rows_per_batch * p.a_map.ld) return cudaErrorInvalidValue;
-  const bool swap = plain_a && p.M <= 256 && out_type == 0;
+  const bool plain_out = p.ep.out_map.rows_per_batch >= (1 << 30) && p.ep.res_map.rows_per_batch >= (1 << 30) &&
+                         p.ep.out2_map.rows_per_batch >= (1 << 30);
+  const bool swap = plain_a && plain_out && p.M <= 256;
+  if (!swap && p.N % 32 != 0 && p.N != 16) return cudaErrorInvalidValue;   // row-major epilogue works in 32-column chunks
   TcParams P{};
   P.M = p.M; P.N = p.N; P.num_kb = p.K / BK_TC;
+  P.trace = tc_trace_buffer();
   CUtensorMap ta, tw;
   GemmEpilogue ep = p.ep;
   if (swap) {
@@ -331,7 +495,7 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, bn)) return cudaErrorUnknown;
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
     // split K so that ~all SMs stream weights; only linear epilogues can be split
-    const bool linear = ep.act_pre == ACT_NONE && ep.act_post == ACT_NONE && ep.out2 == nullptr &&
+    const bool linear = out_type == 0 && ep.act_pre == ACT_NONE && ep.act_post == ACT_NONE && ep.out2 == nullptr &&
                         (ep.res == nullptr || ep.res == ep.out);
     int splits = 1;
     if (linear) {
@@ -349,15 +513,21 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     }
     P.stages = std::max(1, std::min(P.kb_per_split, std::min(6, (196 * 1024) / (BM_TC * 128 + bn * 128))));
     dim3 grid(tiles, 1, splits);
+#define TC_CASE(BNV)                                                                          \
+  case BNV:                                                                                   \
+    return out_type == 0 ? launch_cfg<BNV, true, float>(tw, ta, P, ep, grid, st)              \
+                         : launch_cfg<BNV, true, bf16>(tw, ta, P, ep, grid, st);
     switch (bn) {
-      case 16: return launch_cfg<16, true, float>(tw, ta, P, ep, grid, st);
-      case 32: return launch_cfg<32, true, float>(tw, ta, P, ep, grid, st);
-      case 64: return launch_cfg<64, true, float>(tw, ta, P, ep, grid, st);
-      case 128: return launch_cfg<128, true, float>(tw, ta, P, ep, grid, st);
-      default: return launch_cfg<256, true, float>(tw, ta, P, ep, grid, st);
+      TC_CASE(16) TC_CASE(32) TC_CASE(64) TC_CASE(128)
+      default: return out_type == 0 ? launch_cfg<256, true, float>(tw, ta, P, ep, grid, st)
+                                    : launch_cfg<256, true, bf16>(tw, ta, P, ep, grid, st);
     }
+#undef TC_CASE
   }
-  const int bn = pick_bn(p.N);
+  // row-major: largest BN that still gives every SM a CTA (weights re-read from L2, not HBM)
+  int bn = pick_bn(p.N);
+  const int tiles_m = (p.M + BM_TC - 1) / BM_TC;
+  while (bn > 32 && tiles_m * ((p.N + bn - 1) / bn) < n_sms) bn >>= 1;
   if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
   if (!make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
   P.kb_per_split = P.num_kb;
