@@ -91,7 +91,8 @@ struct TcParams {
   int num_kb;          // K / 64
   int kb_per_split;    // k-blocks handled by one blockIdx.z
   int stages;
-  int atomic_out;      // SWAP split-K: red.add into `out` (fp32)
+  int atomic_out;      // (unused) SWAP split-K by atomics
+  int cluster;         // SWAP split-K: CTAs per cluster along z (partials reduced through DSMEM)
   long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
 };
 #define TC_TRACE(slot) do { if (P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) P.trace[slot] = clock64(); } while (0)
@@ -282,6 +283,78 @@ __device__ __forceinline__ void epilogue_cols(const GemmEpilogue& ep, const TcPa
   }
 }
 
+// ---- thread-block-cluster helpers (split-K partial sums are exchanged through DSMEM)
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ float4 dsmem_ld4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float4 ld4f(const float* p) { return *reinterpret_cast<const float4*>(p); }
+
+// Swapped orientation, split-K over a cluster of S CTAs (phase 1): dump this CTA's partial
+// accumulator tile to its own shared memory as part[m][f] (f = feature within the 128-row tile).
+template <int BN>
+__device__ __forceinline__ void partial_to_smem(const TcParams& P, uint32_t taddr, float* part, int f, int half) {
+  constexpr int CH = BN >= 32 ? 32 : 16;
+  constexpr int NCH = BN / CH;
+#pragma unroll 1
+  for (int ci = half; ci < NCH; ci += 2) {
+    const int c = ci * CH;
+    if (c >= P.M) break;   // uniform: no streams in this chunk
+    float v[CH];
+    tmem_ld<CH>(taddr + c, v);
+#pragma unroll
+    for (int j = 0; j < CH; ++j) part[(c + j) * BM_TC + f] = v[j];   // lanes -> consecutive f: conflict free
+  }
+}
+
+// Phase 2: CTA `rank` of the cluster owns features [rank*F, rank*F+F) of the tile (F = 128/S),
+// sums the S partial tiles in a fixed order (deterministic, unlike atomics) reading its peers'
+// shared memory, and applies the full epilogue with row-contiguous 16-byte accesses.
+template <typename TO>
+__device__ __forceinline__ void epilogue_cluster(const GemmEpilogue& ep, const TcParams& P, const float* part,
+                                                 int S, int rank, int row0, int et) {
+  const int F = BM_TC / S, FV = F >> 2;
+  const int fv = et % FV, mstep = 256 / FV;
+  const int fl = rank * F + fv * 4;   // feature within the tile
+  const int n = row0 + fl;
+  if (n >= P.N) return;
+  const uint32_t base = smem_u32(part) + (uint32_t)fl * 4u;
+  float4 bias = make_float4(0.f, 0.f, 0.f, 0.f), cs = make_float4(1.f, 1.f, 1.f, 1.f);
+  if (ep.bias) bias = ld4f(ep.bias + n);
+  if (ep.colscale) cs = ld4f(ep.colscale + n);
+  cs.x *= ep.alpha; cs.y *= ep.alpha; cs.z *= ep.alpha; cs.w *= ep.alpha;
+  for (int m = et / FV; m < P.M; m += mstep) {
+    float v[4] = {bias.x, bias.y, bias.z, bias.w};
+    for (int s = 0; s < S; ++s) {
+      const float4 t = dsmem_ld4(dsmem_addr(base, (uint32_t)s) + (uint32_t)m * (BM_TC * 4u));
+      v[0] += t.x; v[1] += t.y; v[2] += t.z; v[3] += t.w;
+    }
+    act_inplace<4>(v, ep.act_pre);
+    if (ep.gate) {
+      const float4 g = ld4f(ep.gate + (long long)m * ep.gate_ld + n);
+      v[0] *= g.x; v[1] *= g.y; v[2] *= g.z; v[3] *= g.w;
+    }
+    v[0] *= cs.x; v[1] *= cs.y; v[2] *= cs.z; v[3] *= cs.w;
+    if (ep.res) {
+      const float4 r4 = load4(reinterpret_cast<const TO*>(ep.res) + (long long)m * ep.res_map.ld + n);
+      v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
+    }
+    if (ep.out2) store4(reinterpret_cast<TO*>(ep.out2) + (long long)m * ep.out2_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
+    act_inplace<4>(v, ep.act_post);
+    store4(reinterpret_cast<TO*>(ep.out) + (long long)m * ep.out_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
+  }
+}
+
 constexpr int TC_THREADS = 64 + 256;   // producer warp, MMA warp, 8 epilogue warps
 
 template <int BN, bool SWAP, typename TO>
@@ -371,12 +444,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     if (warp == 2) TC_TRACE(2);
     const int r = row0 + q * 32 + lane;             // UMMA-M index owned by this thread
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    if (nkb > 0) {
+    if (SWAP && P.cluster > 1) {
+      partial_to_smem<BN>(P, taddr, reinterpret_cast<float*>(tiles), q * 32 + lane, half);
+    } else if (nkb > 0) {
       if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half);
       else epilogue_rows<BN, TO>(ep, P, taddr, r, col0, half);
     }
     tc_fence_before();
     if (warp == 2) TC_TRACE(3);
+  }
+  if (SWAP && P.cluster > 1) {
+    // split-K reduction across the cluster through distributed shared memory
+    cluster_sync_all();                       // every CTA's partial tile is in its smem
+    if (warp >= 2)
+      epilogue_cluster<TO>(ep, P, reinterpret_cast<const float*>(tiles), P.cluster, (int)blockIdx.z, row0,
+                           (int)threadIdx.x - 64);
+    cluster_sync_all();                       // peers finished reading this CTA's smem
   }
   __syncthreads();
   if (warp == 1) {
@@ -432,7 +515,9 @@ static bool make_map(CUtensorMap* out, const void* base, long long rows, int K, 
 template <int BN, bool SWAP, typename TO>
 static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, const TcParams& P, const GemmEpilogue& ep,
                               dim3 grid, cudaStream_t st) {
-  const size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + 1024;
+  size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128);
+  if (SWAP && P.cluster > 1) smem = std::max(smem, (size_t)BN * BM_TC * sizeof(float));   // partial tile part[m][f]
+  smem += 1024;
   static bool attr_done = false;
   auto kern = gemm_tc_kernel<BN, SWAP, TO>;
   if (!attr_done) {
@@ -440,8 +525,19 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  kern<<<grid, TC_THREADS, smem, st>>>(tr, tc, P, ep);
-  return cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(TC_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = (SWAP && P.cluster > 1) ? P.cluster : 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, tr, tc, P, ep);
 }
 
 // debug trace (PTTS_TC_TRACE=1): 8 + 4*kb slots of clock64 stamps, dumped by tc_trace_dump()
@@ -494,23 +590,15 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     if (!make_map(&tw, p.W, p.N, p.K, p.K, BM_TC)) return cudaErrorUnknown;
     if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, bn)) return cudaErrorUnknown;
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
-    // split K so that ~all SMs stream weights; only linear epilogues can be split
-    const bool linear = out_type == 0 && ep.act_pre == ACT_NONE && ep.act_post == ACT_NONE && ep.out2 == nullptr &&
-                        (ep.res == nullptr || ep.res == ep.out);
+    // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix;
+    // the partial tiles are reduced through distributed shared memory in a fixed order.
     int splits = 1;
-    if (linear) {
-      splits = std::max(1, std::min(P.num_kb, n_sms / tiles));
-      while (splits > 1 && (P.num_kb + splits - 1) / splits < 2) --splits;
-    }
+    while (splits < 8 && splits * 2 <= P.num_kb && tiles * splits * 2 <= n_sms) splits *= 2;
+    if (p.N % 4 != 0) splits = 1;   // the cluster epilogue works on 4-feature vectors
     P.kb_per_split = (P.num_kb + splits - 1) / splits;
-    splits = (P.num_kb + P.kb_per_split - 1) / P.kb_per_split;
-    P.atomic_out = splits > 1;
-    if (P.atomic_out && ep.res == nullptr) {
-      // no residual to accumulate onto: clear the output first
-      if (ep.out_map.rows_per_batch < (1 << 30)) return cudaErrorInvalidValue;
-      cudaError_t e = cudaMemset2DAsync(ep.out, (size_t)ep.out_map.ld * 4, 0, (size_t)p.N * 4, p.M, st);
-      if (e != cudaSuccess) return e;
-    }
+    if ((P.num_kb + P.kb_per_split - 1) / P.kb_per_split != splits) { splits = 1; P.kb_per_split = P.num_kb; }
+    P.atomic_out = 0;
+    P.cluster = splits;
     P.stages = std::max(1, std::min(P.kb_per_split, std::min(6, (196 * 1024) / (BM_TC * 128 + bn * 128))));
     dim3 grid(tiles, 1, splits);
 #define TC_CASE(BNV)                                                                          \
