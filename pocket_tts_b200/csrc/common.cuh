@@ -61,6 +61,12 @@ __device__ __forceinline__ void store2(bf16* p, float2 v) {
   *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(v.x, v.y);
 }
 
+// ---- programmatic dependent launch: `pdl_wait` blocks until the previous kernel of the stream has
+// completed and its writes are visible (a no-op when launched without the attribute); every kernel
+// of the frame step calls it before its first dependent global access.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- reductions
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -315,7 +315,7 @@ int Engine::debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_ba
   cudaError_t ce;
   if (backend == 1) {
     const long long a_rows = plain_a ? M : (long long)M - (K / ld - 1);
-    ce = gemm_tc_launch(p, 0, a_rows, n_sms, stream);
+    ce = gemm_tc_launch(p, 0, a_rows, n_sms, false, stream);
   } else {
     ce = gemm_simt_launch(p, 1, 0, stream);
   }

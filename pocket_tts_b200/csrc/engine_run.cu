@@ -39,7 +39,7 @@ int Engine::gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, con
   if (in_type == 1 && use_tc && (p.K % 64) == 0 && (skinny || p.N % 32 == 0 || p.N == 16)) {
     // tcgen05 path: A rows addressable through the (possibly overlapping-row) tensor map
     const long long a_rows = plain_a ? M : (long long)M - (p.K / amap.ld - 1);
-    LAUNCH(tag, gemm_tc_launch(p, out_type, a_rows, n_sms, stream));
+    LAUNCH(tag, gemm_tc_launch(p, out_type, a_rows, n_sms, false, stream));
     return PTTS_OK;
   }
   LAUNCH(tag, gemm_simt_launch(p, in_type, out_type, stream));

@@ -39,7 +39,8 @@ struct GemmProblem {
 cudaError_t gemm_simt_launch(const GemmProblem& p, int in_type, int out_type, cudaStream_t st);
 // bf16 x bf16 -> fp32 on tcgen05 tensor cores (operands via TMA); a_rows_alloc = addressable A rows
 void tc_trace_dump(const char* what);
-cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_alloc, int n_sms, cudaStream_t st);
+cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_alloc, int n_sms, bool pdl,
+                           cudaStream_t st);
 
 // shared epilogue math (used by both back-ends): returns v (pre act_post)
 template <typename TO>

@@ -2,23 +2,31 @@
 //
 //   D[m, n] = epilogue( sum_k A[m, k] * W[n, k] )
 //
-// Warp roles (192 threads): warp 0 = TMA producer (one elected lane), warp 1 = TMEM allocator
-// + tcgen05.mma issuer (one elected lane), warps 2..5 = epilogue (tcgen05.ld -> registers ->
-// fused epilogue -> global).  Operand tiles are [rows][64 bf16] = 128-byte rows in the
-// canonical K-major SWIZZLE_128B layout, written by TMA and read by the tensor core through
-// shared-memory matrix descriptors; a ring of `stages` buffers is handed back and forth with
-// mbarriers (full: TMA complete_tx, empty: tcgen05.commit).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + tcgen05.mma issuer
+// (both walk their loops as whole warps, one lane issues), warps 2..9 = epilogue (tcgen05.ld ->
+// registers -> fused epilogue -> global; two warps per TMEM lane quarter).  Operand tiles are
+// [rows][64 bf16] = 128-byte rows in the canonical K-major SWIZZLE_128B layout, written by TMA and
+// read by the tensor core through shared-memory matrix descriptors; a ring of `stages` buffers is
+// handed back and forth with mbarriers (full: TMA complete_tx, empty: tcgen05.commit).
 //
 // Two orientations:
 //   SWAP = false : UMMA M (128 TMEM lanes) = activation rows, UMMA N = BN weight rows.
 //                  Large-M problems (Mimi transformer, SEANet convolutions as overlapping-row
 //                  GEMMs: the A tensor map simply has row stride C_in < K).
 //   SWAP = true  : UMMA M = 128 weight rows, UMMA N = all streams (<= 256).  Skinny decode
-//                  GEMMs (M = number of streams): the weight matrix is streamed exactly once
-//                  and split along K over gridDim.z so that every SM pulls HBM; partial sums
-//                  are reduced with fp32 red.global.add into the residual stream.
+//                  GEMMs (M = number of streams): the weight matrix is streamed exactly once,
+//                  split along K over a thread-block cluster (gridDim.z = cluster size S) so that
+//                  many SMs pull HBM.  Every CTA pushes its partial accumulator tile into its
+//                  peers' shared memory (st.shared::cluster), CTA r owning features
+//                  [r*128/S, (r+1)*128/S): one cluster barrier, then each CTA sums the S slabs in
+//                  a fixed order (bit-stable, no atomics, no memset) and runs the full epilogue.
+//
+// Weight tiles do not depend on the previous kernel of the frame step, so the producer issues
+// them before `griddepcontrol.wait`: with programmatic dependent launch the weight stream of
+// GEMM i+1 starts while GEMM i is still in its epilogue.
 #include <cuda.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <map>
@@ -82,16 +90,30 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
   return d;
 }
 
+// ---- thread-block-cluster helpers
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void dsmem_st(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float4 ld4f(const float* p) { return *reinterpret_cast<const float4*>(p); }
+
 constexpr int BM_TC = 128;   // TMEM lanes / UMMA M
 constexpr int BK_TC = 64;    // bf16 elements per 128-byte swizzle row
 constexpr int MAX_STAGES = 8;
+constexpr int TC_THREADS = 64 + 256;   // producer warp, MMA warp, 8 epilogue warps
 
 struct TcParams {
   int M, N;            // logical output rows (activation rows) and features
   int num_kb;          // K / 64
   int kb_per_split;    // k-blocks handled by one blockIdx.z
   int stages;
-  int atomic_out;      // (unused) SWAP split-K by atomics
   int cluster;         // SWAP split-K: CTAs per cluster along z (partials reduced through DSMEM)
   long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
 };
@@ -158,17 +180,22 @@ template <int CH> __device__ __forceinline__ void row_store(bf16* p, const float
     *reinterpret_cast<uint4*>(p + j) = make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
+// out-of-line activations: the inlined erff / expm1f bodies, unrolled 32x per variant, made each
+// kernel ~10k SASS instructions; cold instruction fetch then dominated the short decode GEMMs.
+__device__ __noinline__ float gelu_call(float x) { return gelu_erf(x); }
+__device__ __noinline__ float silu_call(float x) { return silu_f(x); }
+__device__ __noinline__ float elu_call(float x) { return elu_f(x); }
 template <int CH> __device__ __forceinline__ void act_inplace(float* v, int act) {
   if (act == ACT_NONE) return;
   if (act == ACT_GELU) {
 #pragma unroll
-    for (int j = 0; j < CH; ++j) v[j] = gelu_erf(v[j]);
+    for (int j = 0; j < CH; ++j) v[j] = gelu_call(v[j]);
   } else if (act == ACT_SILU) {
 #pragma unroll
-    for (int j = 0; j < CH; ++j) v[j] = silu_f(v[j]);
+    for (int j = 0; j < CH; ++j) v[j] = silu_call(v[j]);
   } else {
 #pragma unroll
-    for (int j = 0; j < CH; ++j) v[j] = elu_f(v[j]);
+    for (int j = 0; j < CH; ++j) v[j] = elu_call(v[j]);
   }
 }
 
@@ -236,16 +263,15 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, const TcPa
   }
 }
 
-// Swapped epilogue (SWAP = true): this thread owns feature n, TMEM columns are streams m.
-// out / res / out2 / gate are plain row-major [M, ld] here (checked on the host).
+// Swapped epilogue without split-K (cluster == 1): this thread owns feature n, TMEM columns are
+// streams m.  out / res / out2 / gate are plain row-major [M, ld] (checked on the host).
 template <int BN, typename TO>
 __device__ __forceinline__ void epilogue_cols(const GemmEpilogue& ep, const TcParams& P, uint32_t taddr, int n,
                                               int m_base, int half) {
   constexpr int CH = BN >= 32 ? 32 : 16;
   constexpr int NCH = BN / CH;
   const bool n_ok = n < P.N;
-  const bool atomic = P.atomic_out != 0;
-  const float bias = (ep.bias && n_ok && (!atomic || blockIdx.z == 0)) ? ep.bias[n] : 0.0f;
+  const float bias = (ep.bias && n_ok) ? ep.bias[n] : 0.0f;
   const float scale = ep.alpha * ((ep.colscale && n_ok) ? ep.colscale[n] : 1.0f);
   TO* out = reinterpret_cast<TO*>(ep.out) + n;
   const TO* res = ep.res ? reinterpret_cast<const TO*>(ep.res) + n : nullptr;
@@ -261,7 +287,7 @@ __device__ __forceinline__ void epilogue_cols(const GemmEpilogue& ep, const TcPa
       const int cnt = min(CH, P.M - m0);
 #pragma unroll
       for (int j = 0; j < CH; ++j) v[j] += bias;
-      if (!atomic) act_inplace<CH>(v, ep.act_pre);
+      act_inplace<CH>(v, ep.act_pre);
 #pragma unroll
       for (int j = 0; j < CH; ++j) {
         if (j < cnt) {
@@ -269,74 +295,63 @@ __device__ __forceinline__ void epilogue_cols(const GemmEpilogue& ep, const TcPa
           float x = v[j];
           if (gate) x *= gate[m * ep.gate_ld];
           x *= scale;
-          TO* o = out + m * ep.out_map.ld;
-          if (atomic) {
-            atomicAdd(reinterpret_cast<float*>(o), x);
-          } else {
-            if (res) x += to_f(res[m * ep.res_map.ld]);
-            if (out2) out2[m * ep.out2_map.ld] = from_f<TO>(x);
-            *o = from_f<TO>(apply_act(x, ep.act_post));
-          }
+          if (res) x += to_f(res[m * ep.res_map.ld]);
+          v[j] = x;
+          if (out2) out2[m * ep.out2_map.ld] = from_f<TO>(x);
         }
       }
+      act_inplace<CH>(v, ep.act_post);
+#pragma unroll
+      for (int j = 0; j < CH; ++j)
+        if (j < cnt) out[(long long)(m0 + j) * ep.out_map.ld] = from_f<TO>(v[j]);
     }
   }
 }
 
-// ---- thread-block-cluster helpers (split-K partial sums are exchanged through DSMEM)
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ float4 dsmem_ld4(uint32_t addr) {
-  float4 v;
-  asm volatile("ld.shared::cluster.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ float4 ld4f(const float* p) { return *reinterpret_cast<const float4*>(p); }
-
-// Swapped orientation, split-K over a cluster of S CTAs (phase 1): dump this CTA's partial
-// accumulator tile to its own shared memory as part[m][f] (f = feature within the 128-row tile).
+// Swapped orientation, split-K over a cluster of S CTAs.  Slab layout in every CTA's shared
+// memory: slab[s][m][f'] (s = sending rank, m = stream < BN, f' < F = 128/S owned features).
+// Phase 1 (push): the thread holding feature f = owner*F + f' of this CTA's partial tile stores its
+// 32 stream values into the owner's slab[rank].  Lanes hold consecutive f', so a warp store covers
+// 128/F owners with F*4-byte contiguous segments.
 template <int BN>
-__device__ __forceinline__ void partial_to_smem(const TcParams& P, uint32_t taddr, float* part, int f, int half) {
+__device__ __forceinline__ void partial_push(const TcParams& P, uint32_t taddr, const float* slab, int S, int rank,
+                                             int f, int half) {
   constexpr int CH = BN >= 32 ? 32 : 16;
   constexpr int NCH = BN / CH;
+  const int F = BM_TC / S;
+  const int owner = f / F, fo = f - owner * F;
+  const uint32_t dst0 = dsmem_addr(smem_u32(slab) + (uint32_t)((rank * BN) * F + fo) * 4u, (uint32_t)owner);
+  const uint32_t mstride = (uint32_t)F * 4u;
 #pragma unroll 1
   for (int ci = half; ci < NCH; ci += 2) {
     const int c = ci * CH;
     if (c >= P.M) break;   // uniform: no streams in this chunk
     float v[CH];
     tmem_ld<CH>(taddr + c, v);
+    const uint32_t dst = dst0 + (uint32_t)c * mstride;
 #pragma unroll
-    for (int j = 0; j < CH; ++j) part[(c + j) * BM_TC + f] = v[j];   // lanes -> consecutive f: conflict free
+    for (int j = 0; j < CH; ++j) dsmem_st(dst + (uint32_t)j * mstride, v[j]);
   }
 }
 
-// Phase 2: CTA `rank` of the cluster owns features [rank*F, rank*F+F) of the tile (F = 128/S),
-// sums the S partial tiles in a fixed order (deterministic, unlike atomics) reading its peers'
-// shared memory, and applies the full epilogue with row-contiguous 16-byte accesses.
-template <typename TO>
-__device__ __forceinline__ void epilogue_cluster(const GemmEpilogue& ep, const TcParams& P, const float* part,
-                                                 int S, int rank, int row0, int et) {
+// Phase 2 (after the cluster barrier): sum the S slabs of this CTA in rank order and run the full
+// epilogue on features [rank*F, rank*F + F) of the tile with row-contiguous 16-byte accesses.
+template <int BN, typename TO>
+__device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcParams& P, const float* slab, int S,
+                                               int rank, int row0, int et) {
   const int F = BM_TC / S, FV = F >> 2;
   const int fv = et % FV, mstep = 256 / FV;
-  const int fl = rank * F + fv * 4;   // feature within the tile
-  const int n = row0 + fl;
+  const int n = row0 + rank * F + fv * 4;
   if (n >= P.N) return;
-  const uint32_t base = smem_u32(part) + (uint32_t)fl * 4u;
   float4 bias = make_float4(0.f, 0.f, 0.f, 0.f), cs = make_float4(1.f, 1.f, 1.f, 1.f);
   if (ep.bias) bias = ld4f(ep.bias + n);
   if (ep.colscale) cs = ld4f(ep.colscale + n);
   cs.x *= ep.alpha; cs.y *= ep.alpha; cs.z *= ep.alpha; cs.w *= ep.alpha;
+  const float* src = slab + fv * 4;
   for (int m = et / FV; m < P.M; m += mstep) {
     float v[4] = {bias.x, bias.y, bias.z, bias.w};
     for (int s = 0; s < S; ++s) {
-      const float4 t = dsmem_ld4(dsmem_addr(base, (uint32_t)s) + (uint32_t)m * (BM_TC * 4u));
+      const float4 t = ld4f(src + (s * BN + m) * F);
       v[0] += t.x; v[1] += t.y; v[2] += t.z; v[3] += t.w;
     }
     act_inplace<4>(v, ep.act_pre);
@@ -355,27 +370,35 @@ __device__ __forceinline__ void epilogue_cluster(const GemmEpilogue& ep, const T
   }
 }
 
-constexpr int TC_THREADS = 64 + 256;   // producer warp, MMA warp, 8 epilogue warps
-
 template <int BN, bool SWAP, typename TO>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
                TcParams P, GemmEpilogue ep) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // carve: [stages][A 16 KB][B BN*128 B] then barriers
+  // carve: [stages][A 16 KB][B BN*128 B] | slab (cluster split-K only)
   constexpr uint32_t A_BYTES = BM_TC * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  float* slab = reinterpret_cast<float*>(tiles + (size_t)P.stages * STAGE_BYTES);
   __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 2) TC_TRACE(4);
+  pdl_launch_dependents();               // the next kernel may start its own prologue / weight stream
   const int row0 = blockIdx.x * BM_TC;   // UMMA-M operand row offset
   const int col0 = blockIdx.y * BN;      // UMMA-N operand row offset
   const int kb0 = blockIdx.z * P.kb_per_split;
   const int nkb = min(P.kb_per_split, P.num_kb - kb0);
+  const int n_pre = min(P.stages, nkb);  // stages filled before the set-up barrier
   constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+  const bool clustered = SWAP && P.cluster > 1;
+  // weights are the UMMA-M operand in the swapped orientation, the UMMA-N operand otherwise
+  const CUtensorMap* tm_w = SWAP ? &tm_row : &tm_col;
+  const CUtensorMap* tm_a = SWAP ? &tm_col : &tm_row;
+  const int w_row = SWAP ? row0 : col0, a_row = SWAP ? col0 : row0;
+  const uint32_t w_off = SWAP ? 0u : A_BYTES, a_off = SWAP ? A_BYTES : 0u;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_row) : "memory");
@@ -383,6 +406,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     for (int s = 0; s < P.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(&tmem_full_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // first ring pass: weight tiles first (independent of the previous kernel), then, once the
+    // previous kernel's results are visible, the activation tiles of the same stages
+    for (int i = 0; i < n_pre; ++i) {
+      mbar_expect_tx(&full_bar[i], STAGE_BYTES);
+      tma_load_2d(tiles + (size_t)i * STAGE_BYTES + w_off, tm_w, &full_bar[i], (kb0 + i) * BK_TC, w_row);
+    }
+    pdl_wait();
+    for (int i = 0; i < n_pre; ++i)
+      tma_load_2d(tiles + (size_t)i * STAGE_BYTES + a_off, tm_a, &full_bar[i], (kb0 + i) * BK_TC, a_row);
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "n"(TMEM_COLS) : "memory");
@@ -391,24 +423,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();                            // everything below may read the previous kernel's outputs
+  if (clustered) cluster_arrive_relaxed();   // "this CTA runs": peers may write its slabs after the matching wait
   const uint32_t tmem_base = tmem_base_smem;
   if (warp == 2) TC_TRACE(0);
 
   if (warp == 0) {
     // ===== TMA producer: the whole warp walks the ring, one lane issues =====
-    for (int i = 0; i < nkb; ++i) {
+    for (int i = n_pre; i < nkb; ++i) {
       const int s = i % P.stages;
       const uint32_t ph = (i / P.stages) & 1;
-      mbar_wait(&empty_bar[s], ph ^ 1);   // first pass: fresh barrier, parity 1 passes immediately
+      mbar_wait(&empty_bar[s], ph ^ 1);
       TC_TRACE(8 + i * 4 + 0);
       if (lane == 0) {
         mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-        uint8_t* a = tiles + (size_t)s * STAGE_BYTES;
-        tma_load_2d(a, &tm_row, &full_bar[s], (kb0 + i) * BK_TC, row0);
-        tma_load_2d(a + A_BYTES, &tm_col, &full_bar[s], (kb0 + i) * BK_TC, col0);
+        uint8_t* st = tiles + (size_t)s * STAGE_BYTES;
+        tma_load_2d(st + w_off, tm_w, &full_bar[s], (kb0 + i) * BK_TC, w_row);
+        tma_load_2d(st + a_off, tm_a, &full_bar[s], (kb0 + i) * BK_TC, a_row);
       }
       __syncwarp();
     }
+    if (clustered) cluster_wait_acquire();
   } else if (warp == 1) {
     // ===== MMA issuer: whole warp waits, one lane issues =====
     // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at bit 17, M>>4 at bit 24
@@ -434,6 +469,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
       __syncwarp();
     }
     if (nkb == 0 && lane == 0) tc_commit(&tmem_full_bar);
+    if (clustered) cluster_wait_acquire();
   } else {
     // ===== epilogue warps 2..9: TMEM lane quarter = warp % 4, two warps share a quarter and
     // split its column chunks =====
@@ -444,8 +480,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     if (warp == 2) TC_TRACE(2);
     const int r = row0 + q * 32 + lane;             // UMMA-M index owned by this thread
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    if (SWAP && P.cluster > 1) {
-      partial_to_smem<BN>(P, taddr, reinterpret_cast<float*>(tiles), q * 32 + lane, half);
+    if (clustered) {
+      cluster_wait_acquire();                        // every peer CTA has started
+      partial_push<BN>(P, taddr, slab, P.cluster, (int)blockIdx.z, q * 32 + lane, half);
     } else if (nkb > 0) {
       if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half);
       else epilogue_rows<BN, TO>(ep, P, taddr, r, col0, half);
@@ -453,13 +490,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     tc_fence_before();
     if (warp == 2) TC_TRACE(3);
   }
-  if (SWAP && P.cluster > 1) {
-    // split-K reduction across the cluster through distributed shared memory
-    cluster_sync_all();                       // every CTA's partial tile is in its smem
-    if (warp >= 2)
-      epilogue_cluster<TO>(ep, P, reinterpret_cast<const float*>(tiles), P.cluster, (int)blockIdx.z, row0,
-                           (int)threadIdx.x - 64);
-    cluster_sync_all();                       // peers finished reading this CTA's smem
+  if (clustered) {
+    cluster_arrive_release();                 // this CTA's pushes are done ...
+    cluster_wait_acquire();                   // ... and so are everybody else's into this CTA
+    if (warp == 2) TC_TRACE(5);
+    if (warp >= 2) epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64);
+    if (warp == 2) TC_TRACE(6);
   }
   __syncthreads();
   if (warp == 1) {
@@ -512,16 +548,17 @@ static bool make_map(CUtensorMap* out, const void* base, long long rows, int K, 
   return true;
 }
 
+constexpr size_t TC_SMEM_LIMIT = 225 * 1024;
+
 template <int BN, bool SWAP, typename TO>
 static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, const TcParams& P, const GemmEpilogue& ep,
-                              dim3 grid, cudaStream_t st) {
-  size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128);
-  if (SWAP && P.cluster > 1) smem = std::max(smem, (size_t)BN * BM_TC * sizeof(float));   // partial tile part[m][f]
-  smem += 1024;
+                              dim3 grid, bool pdl, cudaStream_t st) {
+  const bool clustered = SWAP && P.cluster > 1;
+  const size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + (clustered ? (size_t)BN * BM_TC * sizeof(float) : 0) + 1024;
   static bool attr_done = false;
   auto kern = gemm_tc_kernel<BN, SWAP, TO>;
   if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_LIMIT + 1024);
     if (e != cudaSuccess) return e;
     attr_done = true;
   }
@@ -530,13 +567,22 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
   cfg.blockDim = dim3(TC_THREADS, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 1;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = (SWAP && P.cluster > 1) ? P.cluster : 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (clustered) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 1;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = P.cluster;
+    ++na;
+  }
+  if (pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = na;
   return cudaLaunchKernelEx(&cfg, kern, tr, tc, P, ep);
 }
 
@@ -556,7 +602,8 @@ void tc_trace_dump(const char* what) {
   cudaDeviceSynchronize();
   cudaMemcpy(h, g_trace, sizeof h, cudaMemcpyDeviceToHost);
   const long long t0 = h[0];
-  fprintf(stderr, "[tc trace %s] epi: wait_begin %lld tmem_full %lld epi_done %lld\n", what, h[1] - t0, h[2] - t0, h[3] - t0);
+  fprintf(stderr, "[tc trace %s] kernel_start %lld | setup_done 0 | tmem_full %lld epi/push_done %lld | cluster_barrier %lld slab_epilogue_done %lld\n",
+          what, h[4] - t0, h[2] - t0, h[3] - t0, h[5] ? h[5] - t0 : 0, h[6] ? h[6] - t0 : 0);
   for (int i = 0; i < 64 && h[8 + i * 4 + 1]; ++i)
     fprintf(stderr, "  kb %2d: producer_got_empty %7lld  mma_got_full %7lld  mma_issued %7lld\n", i, h[8 + i * 4] - t0,
             h[8 + i * 4 + 1] - t0, h[8 + i * 4 + 2] - t0);
@@ -570,8 +617,9 @@ static int pick_bn(int n) {
   return 256;
 }
 
-// rows_alloc: number of addressable A rows (for the tensor-map extent; rows beyond are zero-filled)
-cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_alloc, int n_sms, cudaStream_t st) {
+// a_rows_alloc: number of addressable A rows (for the tensor-map extent; rows beyond are zero-filled)
+cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_alloc, int n_sms, bool pdl,
+                           cudaStream_t st) {
   if (p.M <= 0 || p.N <= 0) return cudaSuccess;
   if (p.K % BK_TC != 0) return cudaErrorInvalidValue;
   const bool plain_a = p.a_map.rows_per_batch >= (1 << 30);
@@ -582,6 +630,7 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   if (!swap && p.N % 32 != 0 && p.N != 16) return cudaErrorInvalidValue;   // row-major epilogue works in 32-column chunks
   TcParams P{};
   P.M = p.M; P.N = p.N; P.num_kb = p.K / BK_TC;
+  P.cluster = 1;
   P.trace = tc_trace_buffer();
   CUtensorMap ta, tw;
   GemmEpilogue ep = p.ep;
@@ -590,25 +639,24 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     if (!make_map(&tw, p.W, p.N, p.K, p.K, BM_TC)) return cudaErrorUnknown;
     if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, bn)) return cudaErrorUnknown;
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
-    // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix;
-    // the partial tiles are reduced through distributed shared memory in a fixed order.
+    // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix
     int splits = 1;
     while (splits < 8 && splits * 2 <= P.num_kb && tiles * splits * 2 <= n_sms) splits *= 2;
-    if (p.N % 4 != 0) splits = 1;   // the cluster epilogue works on 4-feature vectors
+    if (p.N % 4 != 0) splits = 1;   // the slab epilogue works on 4-feature vectors
     P.kb_per_split = (P.num_kb + splits - 1) / splits;
     if ((P.num_kb + P.kb_per_split - 1) / P.kb_per_split != splits) { splits = 1; P.kb_per_split = P.num_kb; }
-    P.atomic_out = 0;
     P.cluster = splits;
-    P.stages = std::max(1, std::min(P.kb_per_split, std::min(6, (196 * 1024) / (BM_TC * 128 + bn * 128))));
+    const size_t stage = (size_t)(BM_TC + bn) * 128, slab = splits > 1 ? (size_t)bn * BM_TC * sizeof(float) : 0;
+    P.stages = (int)std::max<size_t>(1, std::min<size_t>(std::min(P.kb_per_split, 6), (TC_SMEM_LIMIT - slab) / stage));
     dim3 grid(tiles, 1, splits);
 #define TC_CASE(BNV)                                                                          \
   case BNV:                                                                                   \
-    return out_type == 0 ? launch_cfg<BNV, true, float>(tw, ta, P, ep, grid, st)              \
-                         : launch_cfg<BNV, true, bf16>(tw, ta, P, ep, grid, st);
+    return out_type == 0 ? launch_cfg<BNV, true, float>(tw, ta, P, ep, grid, pdl, st)         \
+                         : launch_cfg<BNV, true, bf16>(tw, ta, P, ep, grid, pdl, st);
     switch (bn) {
       TC_CASE(16) TC_CASE(32) TC_CASE(64) TC_CASE(128)
-      default: return out_type == 0 ? launch_cfg<256, true, float>(tw, ta, P, ep, grid, st)
-                                    : launch_cfg<256, true, bf16>(tw, ta, P, ep, grid, st);
+      default: return out_type == 0 ? launch_cfg<256, true, float>(tw, ta, P, ep, grid, pdl, st)
+                                    : launch_cfg<256, true, bf16>(tw, ta, P, ep, grid, pdl, st);
     }
 #undef TC_CASE
   }
@@ -619,17 +667,16 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
   if (!make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
   P.kb_per_split = P.num_kb;
-  P.atomic_out = 0;
-  P.stages = std::max(1, std::min(P.num_kb, std::min(6, (196 * 1024) / (BM_TC * 128 + bn * 128))));
-  dim3 grid((p.M + BM_TC - 1) / BM_TC, (p.N + bn - 1) / bn, 1);
+  P.stages = (int)std::max<size_t>(1, std::min<size_t>(std::min(P.num_kb, 6), TC_SMEM_LIMIT / ((size_t)(BM_TC + bn) * 128)));
+  dim3 grid(tiles_m, (p.N + bn - 1) / bn, 1);
 #define TC_CASE(BNV)                                                                          \
   case BNV:                                                                                   \
-    return out_type == 0 ? launch_cfg<BNV, false, float>(ta, tw, P, ep, grid, st)             \
-                         : launch_cfg<BNV, false, bf16>(ta, tw, P, ep, grid, st);
+    return out_type == 0 ? launch_cfg<BNV, false, float>(ta, tw, P, ep, grid, pdl, st)        \
+                         : launch_cfg<BNV, false, bf16>(ta, tw, P, ep, grid, pdl, st);
   switch (bn) {
     TC_CASE(16) TC_CASE(32) TC_CASE(64) TC_CASE(128)
-    default: return out_type == 0 ? launch_cfg<256, false, float>(ta, tw, P, ep, grid, st)
-                                  : launch_cfg<256, false, bf16>(ta, tw, P, ep, grid, st);
+    default: return out_type == 0 ? launch_cfg<256, false, float>(ta, tw, P, ep, grid, pdl, st)
+                                  : launch_cfg<256, false, bf16>(ta, tw, P, ep, grid, pdl, st);
   }
 #undef TC_CASE
 }
