@@ -82,6 +82,8 @@ __global__ void __launch_bounds__(128)
 attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs,
                    const int* __restrict__ offsets, const int* __restrict__ slot_ids, KvGeom g,
                    int layer, TO* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int NW = 4;
   __shared__ float sm_m[NW], sm_l[NW];
   __shared__ float2 sm_acc[NW][32];
@@ -138,11 +140,11 @@ cudaError_t launch_attn_decode(const float* qkv, const float* rope_freqs, const 
   if (kv.D != 64) return cudaErrorInvalidValue;
   dim3 grid(kv.H, n);
   if (kv.type == 0 && out_type == 0)
-    attn_decode_kernel<float, float><<<grid, 128, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out);
+    launch_k(attn_decode_kernel<float, float>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out);
   else if (kv.type == 1 && out_type == 1)
-    attn_decode_kernel<bf16, bf16><<<grid, 128, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+    launch_k(attn_decode_kernel<bf16, bf16>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
   else if (kv.type == 0 && out_type == 1)
-    attn_decode_kernel<float, bf16><<<grid, 128, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+    launch_k(attn_decode_kernel<float, bf16>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
   else
     return cudaErrorInvalidValue;
   return cudaGetLastError();
@@ -159,6 +161,8 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
                   const int* __restrict__ offsets, const int* __restrict__ slot_ids,
                   const int* __restrict__ row_start, const int* __restrict__ lens, KvGeom g, int layer,
                   int context, TO* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int NW = 8;
   const int h = blockIdx.x, i = blockIdx.y;
   const int slot = slot_ids[i];
@@ -214,13 +218,166 @@ cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* of
   if (kv.ring && (kv.cap & (kv.cap - 1))) return cudaErrorInvalidValue;
   dim3 grid(kv.H, n);
   if (kv.type == 0 && out_type == 0)
-    attn_chunk_kernel<float, float><<<grid, 256, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (float*)out);
+    launch_k(attn_chunk_kernel<float, float>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (float*)out);
   else if (kv.type == 1 && out_type == 1)
-    attn_chunk_kernel<bf16, bf16><<<grid, 256, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
+    launch_k(attn_chunk_kernel<bf16, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
   else if (kv.type == 0 && out_type == 1)
-    attn_chunk_kernel<float, bf16><<<grid, 256, 0, st>>>(qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
+    launch_k(attn_chunk_kernel<float, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
   else
     return cudaErrorInvalidValue;
+  return cudaGetLastError();
+}
+
+// =====================================================================================
+// window: Mimi decoder attention, T (<= 16) new tokens per stream per frame, sliding window
+// `context` over a ring cache (transformer.py:22-29, mimi_transformer.py:140-150).
+// grid (H, n), 256 threads.  The <= context+T-1 keys/values a frame can see are staged ONCE in
+// shared memory (padded rows: conflict-free both when lanes own keys and when lanes own dims);
+// scores: lanes own keys (no shuffles in the dot products), PV: lanes own dim pairs.
+// =====================================================================================
+template <typename TK> struct KvWords;
+template <> struct KvWords<bf16> { static constexpr int ROW = 32, LD = 33; };    // 64 bf16 = 32 words (+1 pad)
+template <> struct KvWords<float> { static constexpr int ROW = 64, LD = 65; };
+
+__device__ __forceinline__ float2 kv_word_pair(const uint32_t* row, int c, bf16) {   // dims 2c, 2c+1
+  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(row + c));
+}
+__device__ __forceinline__ float2 kv_word_pair(const uint32_t* row, int c, float) {
+  return make_float2(__uint_as_float(row[2 * c]), __uint_as_float(row[2 * c + 1]));
+}
+
+template <typename TK, typename TO>
+__global__ void __launch_bounds__(256)
+attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs, const int* __restrict__ offsets,
+                   const int* __restrict__ slot_ids, KvGeom g, int layer, int context, int T, int maxw,
+                   TO* __restrict__ out) {
+  constexpr int NW = 8, TQ = 16, NKL = 9;   // warps, max queries, max keys per lane (maxw <= 288)
+  constexpr int LD = KvWords<TK>::LD, ROWW = KvWords<TK>::ROW;
+  extern __shared__ __align__(16) uint32_t smw[];
+  uint32_t* Ks = smw;
+  uint32_t* Vs = Ks + maxw * LD;
+  float* Ps = reinterpret_cast<float*>(Vs + maxw * LD);   // [TQ][maxw]
+  float* Qs = Ps + TQ * maxw;                              // [TQ][64]
+  const int h = blockIdx.x, i = blockIdx.y;
+  const int slot = slot_ids[i];
+  const int off = offsets[slot];
+  const int r0 = i * T;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int d_model = g.H * 64;
+  const float fr = freqs[lane];
+
+  // phase 1: RoPE, append rotated k / v to the ring, keep rotated q in shared memory
+  for (int t = w; t < T; t += NW) {
+    const float* row = qkv + (long long)(r0 + t) * 3 * d_model + h * 64 + 2 * lane;
+    const float pos = (float)(off + t);
+    const float2 q = rope_pair(load2(row), pos, fr);
+    Qs[t * 64 + 2 * lane] = q.x;
+    Qs[t * 64 + 2 * lane + 1] = q.y;
+    const float2 k = rope_pair(load2(row + d_model), pos, fr);
+    const float2 v = load2(row + 2 * d_model);
+    store2(kv_row<TK>(g, layer, slot, 0, h, off + t) + 2 * lane, k);
+    store2(kv_row<TK>(g, layer, slot, 1, h, off + t) + 2 * lane, v);
+  }
+  __syncthreads();
+
+  // phase 2: stage the visible window [lo, off+T-1] (including the rows just written)
+  const int lo = max(0, off - context + 1);
+  const int W = off + T - lo;
+  for (int j = w; j < W; j += NW) {
+    const TK* kr = kv_row<TK>(g, layer, slot, 0, h, lo + j);
+    const TK* vr = kv_row<TK>(g, layer, slot, 1, h, lo + j);
+    if (sizeof(TK) == 2) {
+      Ks[j * LD + lane] = reinterpret_cast<const uint32_t*>(kr)[lane];
+      Vs[j * LD + lane] = reinterpret_cast<const uint32_t*>(vr)[lane];
+    } else {
+      const uint2 kk = reinterpret_cast<const uint2*>(kr)[lane], vv = reinterpret_cast<const uint2*>(vr)[lane];
+      Ks[j * LD + 2 * lane] = kk.x; Ks[j * LD + 2 * lane + 1] = kk.y;
+      Vs[j * LD + 2 * lane] = vv.x; Vs[j * LD + 2 * lane + 1] = vv.y;
+    }
+  }
+  __syncthreads();
+
+  // phase 3: one warp per query
+  for (int t = w; t < T; t += NW) {
+    const int pq = off + t;
+    const int jlo = max(0, pq - context + 1) - lo, jhi = pq - lo;   // inclusive key range in the window
+    float q[64];
+#pragma unroll
+    for (int c = 0; c < 64; c += 4) {
+      const float4 t4 = *reinterpret_cast<const float4*>(Qs + t * 64 + c);
+      q[c] = t4.x; q[c + 1] = t4.y; q[c + 2] = t4.z; q[c + 3] = t4.w;
+    }
+    float sc[NKL];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int u = 0; u < NKL; ++u) {
+      const int j = jlo + lane + 32 * u;
+      float a = -INFINITY;
+      if (j <= jhi) {
+        const uint32_t* kr = Ks + j * LD;
+        float acc = 0.0f;
+#pragma unroll
+        for (int c = 0; c < 32; ++c) {
+          const float2 kk = kv_word_pair(kr, c, TK());
+          acc = fmaf(q[2 * c], kk.x, acc);
+          acc = fmaf(q[2 * c + 1], kk.y, acc);
+        }
+        a = acc * 0.125f;
+      }
+      sc[u] = a;
+      mx = fmaxf(mx, a);
+    }
+    mx = warp_max(mx);
+    float l = 0.0f;
+#pragma unroll
+    for (int u = 0; u < NKL; ++u) {
+      const int j = jlo + lane + 32 * u;
+      if (j <= jhi) {
+        const float p = expf(sc[u] - mx);
+        l += p;
+        Ps[t * maxw + j] = p;
+      }
+    }
+    l = warp_sum(l);
+    __syncwarp();
+    float2 acc = make_float2(0.f, 0.f);
+    const float* pr = Ps + t * maxw;
+    for (int j = jlo; j <= jhi; ++j) {
+      const float p = pr[j];
+      const float2 vv = kv_word_pair(Vs + j * LD, lane, TK());
+      acc.x = fmaf(p, vv.x, acc.x);
+      acc.y = fmaf(p, vv.y, acc.y);
+    }
+    const float inv = 1.0f / l;
+    store2(out + (long long)(r0 + t) * d_model + h * 64 + 2 * lane, make_float2(acc.x * inv, acc.y * inv));
+  }
+}
+
+cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets, const int* slot_ids,
+                               KvGeom kv, int layer, int context, int T, void* out, int out_type, int n,
+                               cudaStream_t st) {
+  if (kv.D != 64 || !kv.ring || (kv.cap & (kv.cap - 1)) || T < 1 || T > 16) return cudaErrorInvalidValue;
+  const int maxw = ((context + T - 1 + 7) / 8) * 8;
+  if (maxw > 288 || maxw > kv.cap) return cudaErrorInvalidValue;
+  dim3 grid(kv.H, n);
+  const int ld = kv.type == 1 ? KvWords<bf16>::LD : KvWords<float>::LD;
+  const size_t smem = ((size_t)2 * maxw * ld + (size_t)16 * maxw + 16 * 64) * 4;
+#define WIN_CASE(TKT, TOT)                                                                                        \
+  do {                                                                                                            \
+    static bool attr = false;                                                                                     \
+    if (!attr) {                                                                                                  \
+      cudaError_t e = cudaFuncSetAttribute(attn_window_kernel<TKT, TOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
+      if (e != cudaSuccess) return e;                                                                             \
+      attr = true;                                                                                                \
+    }                                                                                                             \
+    launch_k(attn_window_kernel<TKT, TOT>, grid, 256, smem, st, qkv, rope_freqs, offsets, slot_ids, kv, layer,    \
+             context, T, maxw, (TOT*)out);                                                                        \
+  } while (0)
+  if (kv.type == 0 && out_type == 0) WIN_CASE(float, float);
+  else if (kv.type == 1 && out_type == 1) WIN_CASE(bf16, bf16);
+  else if (kv.type == 0 && out_type == 1) WIN_CASE(float, bf16);
+  else return cudaErrorInvalidValue;
+#undef WIN_CASE
   return cudaGetLastError();
 }
 
@@ -230,6 +387,8 @@ cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* of
 // =====================================================================================
 template <typename TK>
 __global__ void kv_import_kernel(const float* __restrict__ ref, KvGeom g, int layer, int slot, int P) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long total = 2LL * P * g.H * g.D;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -243,6 +402,8 @@ __global__ void kv_import_kernel(const float* __restrict__ ref, KvGeom g, int la
 }
 template <typename TK>
 __global__ void kv_export_kernel(float* __restrict__ ref, KvGeom g, int layer, int slot, int P) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long total = 2LL * P * g.H * g.D;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -256,6 +417,8 @@ __global__ void kv_export_kernel(float* __restrict__ ref, KvGeom g, int layer, i
 }
 template <typename TK>
 __global__ void kv_fork_kernel(KvGeom g, int n_layers, int src, int dst, int P) {
+  pdl_launch_dependents();
+  pdl_wait();
   // copy positions [0,P) of every (layer, kv, head): P*D contiguous elements each
   const int seg = blockIdx.x;  // layer*2*H + kv*H + h
   const int h = seg % g.H, kv = (seg / g.H) % 2, layer = seg / (2 * g.H);
@@ -268,22 +431,22 @@ __global__ void kv_fork_kernel(KvGeom g, int n_layers, int src, int dst, int P) 
 cudaError_t launch_kv_import(const float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st) {
   if (P <= 0) return cudaSuccess;
   const int blocks = (int)min(1024LL, (2LL * P * kv.H * kv.D + 255) / 256);
-  if (kv.type == 0) kv_import_kernel<float><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
-  else kv_import_kernel<bf16><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
+  if (kv.type == 0) launch_k(kv_import_kernel<float>, blocks, 256, 0, st, ref, kv, layer, slot, P);
+  else launch_k(kv_import_kernel<bf16>, blocks, 256, 0, st, ref, kv, layer, slot, P);
   return cudaGetLastError();
 }
 cudaError_t launch_kv_export(float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st) {
   if (P <= 0) return cudaSuccess;
   const int blocks = (int)min(1024LL, (2LL * P * kv.H * kv.D + 255) / 256);
-  if (kv.type == 0) kv_export_kernel<float><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
-  else kv_export_kernel<bf16><<<blocks, 256, 0, st>>>(ref, kv, layer, slot, P);
+  if (kv.type == 0) launch_k(kv_export_kernel<float>, blocks, 256, 0, st, ref, kv, layer, slot, P);
+  else launch_k(kv_export_kernel<bf16>, blocks, 256, 0, st, ref, kv, layer, slot, P);
   return cudaGetLastError();
 }
 cudaError_t launch_kv_fork(KvGeom kv, int n_layers, int src, int dst, int P, cudaStream_t st) {
   if (P <= 0) return cudaSuccess;
   const int blocks = n_layers * 2 * kv.H;
-  if (kv.type == 0) kv_fork_kernel<float><<<blocks, 256, 0, st>>>(kv, n_layers, src, dst, P);
-  else kv_fork_kernel<bf16><<<blocks, 256, 0, st>>>(kv, n_layers, src, dst, P);
+  if (kv.type == 0) launch_k(kv_fork_kernel<float>, blocks, 256, 0, st, kv, n_layers, src, dst, P);
+  else launch_k(kv_fork_kernel<bf16>, blocks, 256, 0, st, kv, n_layers, src, dst, P);
   return cudaGetLastError();
 }
 

@@ -100,6 +100,29 @@ struct RowMap {
   int ld;                  // elements between consecutive rows
 };
 
+// ---- host-side launch helper: every kernel of the frame step is launched with the programmatic
+// stream serialization attribute (PTTS_PDL=0 disables) so that its prologue overlaps the tail of
+// the previous kernel; kernels call pdl_wait() before their first dependent access.
+bool pdl_enabled();
+// Every kernel asks for the same (maximum) shared-memory carveout: alternating carveouts between
+// consecutive kernels makes the SMs drain and repartition L1/shared memory at every boundary.
+void prefer_max_smem_carveout(const void* kern);
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  prefer_max_smem_carveout(reinterpret_cast<const void*>(kern));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 }  // namespace ptts
 
 // ---- host-side error plumbing

@@ -17,6 +17,19 @@ void set_error_cuda(cudaError_t e, const char* expr, const char* file, int line)
   g_err = buf;
 }
 const char* get_error() { return g_err.c_str(); }
+void prefer_max_smem_carveout(const void* kern) {
+  static std::map<const void*, int> done;
+  static int on = -1;
+  if (on < 0) { const char* e = getenv("PTTS_CARVEOUT"); on = (e && e[0] == '1') ? 1 : 0; }
+  if (!on || done.count(kern)) return;
+  cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  done[kern] = 1;
+}
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("PTTS_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
 
 Engine::~Engine() {
   for (auto& kv : graphs)

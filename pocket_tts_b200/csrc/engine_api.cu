@@ -3,6 +3,7 @@
 
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 
 namespace ptts {
 
@@ -274,7 +275,9 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
   for (int f = 0; f < n_frames; ++f) {
     PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_dev + (size_t)f * n * Ld, (size_t)n * Ld * sizeof(float),
                                     cudaMemcpyDeviceToDevice, stream));
-    if ((rc = frame(n, lsd, 1)) != PTTS_OK) return rc;
+    static const int part = [] { const char* e = getenv("PTTS_PROFILE_PART"); return e ? atoi(e) : 0; }();  // 1: FlowLM+head only, 2: Mimi only (profiling)
+    if (part == 2) { if ((rc = mimi_sequence(n, x_lat)) != PTTS_OK) return rc; }
+    else if ((rc = frame(n, lsd, part == 1 ? 0 : 1)) != PTTS_OK) return rc;
     if (out_pcm_dev)
       PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_dev + (size_t)f * fs, (size_t)n_frames * fs * sizeof(float), pcm,
                                         fs * sizeof(float), fs * sizeof(float), n, cudaMemcpyDeviceToDevice, stream));
@@ -315,7 +318,7 @@ int Engine::debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_ba
   cudaError_t ce;
   if (backend == 1) {
     const long long a_rows = plain_a ? M : (long long)M - (K / ld - 1);
-    ce = gemm_tc_launch(p, 0, a_rows, n_sms, false, stream);
+    ce = gemm_tc_launch(p, 0, a_rows, n_sms, pdl_enabled(), stream);
   } else {
     ce = gemm_simt_launch(p, 1, 0, stream);
   }

@@ -39,7 +39,7 @@ int Engine::gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, con
   if (in_type == 1 && use_tc && (p.K % 64) == 0 && (skinny || p.N % 32 == 0 || p.N == 16)) {
     // tcgen05 path: A rows addressable through the (possibly overlapping-row) tensor map
     const long long a_rows = plain_a ? M : (long long)M - (p.K / amap.ld - 1);
-    LAUNCH(tag, gemm_tc_launch(p, out_type, a_rows, n_sms, false, stream));
+    LAUNCH(tag, gemm_tc_launch(p, out_type, a_rows, n_sms, pdl_enabled(), stream));
     return PTTS_OK;
   }
   LAUNCH(tag, gemm_simt_launch(p, in_type, out_type, stream));
@@ -57,8 +57,8 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
     if ((rc = gemm(mimi ? "mimi.qkv" : "flow.qkv", a, true, plain(d), L.in_proj, rows, ep, false)) != PTTS_OK) return rc;
   }
   if (mimi) {
-    LAUNCH("mimi.attn", launch_attn_chunk(qkvb, rope_freqs, mimi_offsets, d_slot_ids, d_mimi_row_start, d_mimi_lens,
-                             kv_mimi, li, cfg.mimi_context, ao, act_type, n, stream));
+    LAUNCH("mimi.attn", launch_attn_window(qkvb, rope_freqs, mimi_offsets, d_slot_ids, kv_mimi, li, cfg.mimi_context,
+                                           cfg.upsample_stride, ao, act_type, n, stream));
   } else if (rows == n) {
     LAUNCH("flow.attn_decode", launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, kv_flow, li, ao, act_type, n, stream));
   } else {

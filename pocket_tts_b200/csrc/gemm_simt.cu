@@ -11,6 +11,8 @@ template <typename TA, typename TO, int BM, int BN>
 __global__ void __launch_bounds__(256)
 gemm_simt_kernel(const TA* __restrict__ A, RowMap amap, const TA* __restrict__ W, int M, int N, int K,
                  GemmEpilogue ep) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int BK = 16;
   constexpr int TX = BN / 4;          // threads along N
   constexpr int LA = (BM * 4 + 255) / 256;  // float4 loads of A per thread per k-tile
@@ -121,13 +123,13 @@ static cudaError_t launch_typed(const GemmProblem& p, cudaStream_t st) {
   const TA* W = reinterpret_cast<const TA*>(p.W);
   if (p.N <= 32) {
     dim3 grid((p.N + 31) / 32, (p.M + 127) / 128);
-    gemm_simt_kernel<TA, TO, 128, 32><<<grid, 256, 0, st>>>(A, p.a_map, W, p.M, p.N, p.K, p.ep);
+    launch_k(gemm_simt_kernel<TA, TO, 128, 32>, grid, 256, 0, st, A, p.a_map, W, p.M, p.N, p.K, p.ep);
   } else if (p.M <= 32) {
     dim3 grid((p.N + 127) / 128, (p.M + 31) / 32);
-    gemm_simt_kernel<TA, TO, 32, 128><<<grid, 256, 0, st>>>(A, p.a_map, W, p.M, p.N, p.K, p.ep);
+    launch_k(gemm_simt_kernel<TA, TO, 32, 128>, grid, 256, 0, st, A, p.a_map, W, p.M, p.N, p.K, p.ep);
   } else {
     dim3 grid((p.N + 63) / 64, (p.M + 63) / 64);
-    gemm_simt_kernel<TA, TO, 64, 64><<<grid, 256, 0, st>>>(A, p.a_map, W, p.M, p.N, p.K, p.ep);
+    launch_k(gemm_simt_kernel<TA, TO, 64, 64>, grid, 256, 0, st, A, p.a_map, W, p.M, p.N, p.K, p.ep);
   }
   return cudaGetLastError();
 }

@@ -180,11 +180,27 @@ template <int CH> __device__ __forceinline__ void row_store(bf16* p, const float
     *reinterpret_cast<uint4*>(p + j) = make_uint4(w[0], w[1], w[2], w[3]);
   }
 }
-// out-of-line activations: the inlined erff / expm1f bodies, unrolled 32x per variant, made each
-// kernel ~10k SASS instructions; cold instruction fetch then dominated the short decode GEMMs.
-__device__ __noinline__ float gelu_call(float x) { return gelu_erf(x); }
-__device__ __noinline__ float silu_call(float x) { return silu_f(x); }
-__device__ __noinline__ float elu_call(float x) { return elu_f(x); }
+// Activations of the bf16 mode: results are rounded to bf16 (or feed a bf16 GEMM operand), so the
+// short forms below (absolute error <= 2e-7) are exact to the storage precision while keeping the
+// unrolled epilogue small (the libm erff / expm1f bodies made each kernel ~10k SASS instructions and
+// cold instruction fetch dominated the short decode GEMMs).  The fp32 parity mode never comes here.
+__device__ __forceinline__ float gelu_call(float x) {
+  // erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7)
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  const float e = 1.0f - p * t * __expf(-z * z);
+  return 0.5f * x * (1.0f + copysignf(e, x));
+}
+__device__ __forceinline__ float silu_call(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float elu_call(float x) {
+  const float small = x * fmaf(x, fmaf(x, fmaf(x, fmaf(x, 0.0083333333f, 0.041666667f), 0.16666667f), 0.5f), 1.0f);
+  const float big = __expf(x) - 1.0f;
+  return x > 0.0f ? x : (x > -0.125f ? small : big);
+}
 template <int CH> __device__ __forceinline__ void act_inplace(float* v, int act) {
   if (act == ACT_NONE) return;
   if (act == ACT_GELU) {
@@ -560,6 +576,7 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_LIMIT + 1024);
     if (e != cudaSuccess) return e;
+    prefer_max_smem_carveout(reinterpret_cast<const void*>(kern));
     attr_done = true;
   }
   cudaLaunchConfig_t cfg{};

@@ -12,6 +12,8 @@ __global__ void __launch_bounds__(256)
 flow_embed_kernel(const float* __restrict__ prev, const int* __restrict__ slot_ids,
                   const float* __restrict__ bos, const float* __restrict__ w_in,
                   float* __restrict__ h, int d, int ldim) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float seq[64];
   const int i = blockIdx.x, slot = slot_ids[i];
   if (threadIdx.x < ldim) {
@@ -36,7 +38,7 @@ flow_embed_kernel(const float* __restrict__ prev, const int* __restrict__ slot_i
 cudaError_t launch_flow_embed(const float* prev_latent, const int* slot_ids, const float* bos,
                               const float* w_in, float* h, int n, int d, int ldim, cudaStream_t st) {
   if (ldim > 64 || ldim % 4) return cudaErrorInvalidValue;
-  flow_embed_kernel<<<n, 256, 0, st>>>(prev_latent, slot_ids, bos, w_in, h, d, ldim);
+  launch_k(flow_embed_kernel, n, 256, 0, st, prev_latent, slot_ids, bos, w_in, h, d, ldim);
   return cudaGetLastError();
 }
 
@@ -48,6 +50,8 @@ template <typename TO, int VPT>
 __global__ void __launch_bounds__(128)
 ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                float eps, TO* __restrict__ y, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float scratch[33];
   const long long row = blockIdx.x;
   const float* xr = x + row * d;
@@ -89,8 +93,8 @@ cudaError_t launch_ln_rows(const float* x, const float* w, const float* b, float
                            int y_type, int rows, int d, cudaStream_t st) {
   if (rows <= 0) return cudaSuccess;
   if (d % 4 || d > 1024) return cudaErrorInvalidValue;
-  if (y_type == 0) ln_rows_kernel<float, 2><<<rows, 128, 0, st>>>(x, w, b, eps, (float*)y, d);
-  else ln_rows_kernel<bf16, 2><<<rows, 128, 0, st>>>(x, w, b, eps, (bf16*)y, d);
+  if (y_type == 0) launch_k(ln_rows_kernel<float, 2>, rows, 128, 0, st, x, w, b, eps, (float*)y, d);
+  else launch_k(ln_rows_kernel<bf16, 2>, rows, 128, 0, st, x, w, b, eps, (bf16*)y, d);
   return cudaGetLastError();
 }
 
@@ -103,6 +107,8 @@ final_norm_eos_kernel(const float* __restrict__ h, const float* __restrict__ w,
                       const float* __restrict__ b, float eps, const float* __restrict__ w_eos,
                       const float* __restrict__ b_eos, TO* __restrict__ c,
                       float* __restrict__ eos_logit, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float scratch[33];
   const long long row = blockIdx.x;
   const float* xr = h + row * d;
@@ -149,9 +155,9 @@ cudaError_t launch_final_norm_eos(const float* h, const float* w, const float* b
                                   float* eos_logit, int n, int d, cudaStream_t st) {
   if (d % 4 || d > 1024) return cudaErrorInvalidValue;
   if (c_type == 0)
-    final_norm_eos_kernel<float><<<n, 128, 0, st>>>(h, w, b, eps, w_eos, b_eos, (float*)c, eos_logit, d);
+    launch_k(final_norm_eos_kernel<float>, n, 128, 0, st, h, w, b, eps, w_eos, b_eos, (float*)c, eos_logit, d);
   else
-    final_norm_eos_kernel<bf16><<<n, 128, 0, st>>>(h, w, b, eps, w_eos, b_eos, (bf16*)c, eos_logit, d);
+    launch_k(final_norm_eos_kernel<bf16>, n, 128, 0, st, h, w, b, eps, w_eos, b_eos, (bf16*)c, eos_logit, d);
   return cudaGetLastError();
 }
 
@@ -161,6 +167,8 @@ cudaError_t launch_final_norm_eos(const float* h, const float* w, const float* b
 template <typename TO>
 __global__ void silu_add_kernel(const float* __restrict__ cemb, const float* __restrict__ trow,
                                 TO* __restrict__ sy, long long total, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i >= total) return;
   const int c = (int)(i % d);
@@ -172,8 +180,8 @@ cudaError_t launch_silu_add(const float* cemb, const float* tcomb_row, void* sy,
                             int d, cudaStream_t st) {
   const long long total = (long long)n * d;
   const int blocks = (int)((total / 4 + 255) / 256);
-  if (sy_type == 0) silu_add_kernel<float><<<blocks, 256, 0, st>>>(cemb, tcomb_row, (float*)sy, total, d);
-  else silu_add_kernel<bf16><<<blocks, 256, 0, st>>>(cemb, tcomb_row, (bf16*)sy, total, d);
+  if (sy_type == 0) launch_k(silu_add_kernel<float>, blocks, 256, 0, st, cemb, tcomb_row, (float*)sy, total, d);
+  else launch_k(silu_add_kernel<bf16>, blocks, 256, 0, st, cemb, tcomb_row, (bf16*)sy, total, d);
   return cudaGetLastError();
 }
 
@@ -184,6 +192,8 @@ __global__ void __launch_bounds__(128)
 ln_modulate_kernel(const float* __restrict__ u, const float* __restrict__ w,
                    const float* __restrict__ b, const float* __restrict__ shift,
                    const float* __restrict__ scale, int mod_ld, TO* __restrict__ g, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float scratch[33];
   const long long row = blockIdx.x;
   const int c = threadIdx.x * 4;
@@ -212,14 +222,16 @@ cudaError_t launch_ln_modulate(const float* u, const float* w, const float* b, c
                                cudaStream_t st) {
   if (d > 512 || d % 4) return cudaErrorInvalidValue;
   if (g_type == 0)
-    ln_modulate_kernel<float><<<n, 128, 0, st>>>(u, w, b, shift, scale, mod_ld, (float*)g, d);
+    launch_k(ln_modulate_kernel<float>, n, 128, 0, st, u, w, b, shift, scale, mod_ld, (float*)g, d);
   else
-    ln_modulate_kernel<bf16><<<n, 128, 0, st>>>(u, w, b, shift, scale, mod_ld, (bf16*)g, d);
+    launch_k(ln_modulate_kernel<bf16>, n, 128, 0, st, u, w, b, shift, scale, mod_ld, (bf16*)g, d);
   return cudaGetLastError();
 }
 
 __global__ void commit_latent_kernel(const float* __restrict__ x, const int* __restrict__ slot_ids,
                                      float* __restrict__ prev, float* __restrict__ out, int n, int ldim) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n * ldim) return;
   const int i = idx / ldim, j = idx - i * ldim;
@@ -230,19 +242,21 @@ __global__ void commit_latent_kernel(const float* __restrict__ x, const int* __r
 
 cudaError_t launch_commit_latent(const float* x, const int* slot_ids, float* prev_latent, float* out,
                                  int n, int ldim, cudaStream_t st) {
-  commit_latent_kernel<<<(n * ldim + 255) / 256, 256, 0, st>>>(x, slot_ids, prev_latent, out, n, ldim);
+  launch_k(commit_latent_kernel, (n * ldim + 255) / 256, 256, 0, st, x, slot_ids, prev_latent, out, n, ldim);
   return cudaGetLastError();
 }
 
 __global__ void advance_kernel(int* __restrict__ offsets, const int* __restrict__ slot_ids,
                                const int* __restrict__ inc, int const_inc, int n) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) offsets[slot_ids[i]] += inc ? inc[i] : const_inc;
 }
 
 cudaError_t launch_advance(int* offsets, const int* slot_ids, const int* inc, int const_inc, int n,
                            cudaStream_t st) {
-  advance_kernel<<<(n + 127) / 128, 128, 0, st>>>(offsets, slot_ids, inc, const_inc, n);
+  launch_k(advance_kernel, (n + 127) / 128, 128, 0, st, offsets, slot_ids, inc, const_inc, n);
   return cudaGetLastError();
 }
 

@@ -36,6 +36,12 @@ cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* of
                               const int* slot_ids, const int* row_start, const int* lens, KvGeom kv,
                               int layer, int context, void* out, int out_type, int n, cudaStream_t st);
 
+// Mimi decoder attention: exactly T (<= 16) new tokens per stream (rows i*T.. of qkv), sliding
+// window `context` over the ring cache; the visible window is staged once in shared memory.
+cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets,
+                               const int* slot_ids, KvGeom kv, int layer, int context, int T, void* out,
+                               int out_type, int n, cudaStream_t st);
+
 // offsets[slot_ids[i]] += inc[i] (inc == nullptr: += const_inc)
 cudaError_t launch_advance(int* offsets, const int* slot_ids, const int* inc, int const_inc, int n,
                            cudaStream_t st);

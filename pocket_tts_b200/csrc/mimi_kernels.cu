@@ -6,41 +6,59 @@
 
 namespace ptts {
 
-// one CTA per stream, one thread per channel
-__global__ void __launch_bounds__(512)
+// grid (n, C/128): one thread per channel; every weight row a thread needs (32 + 32 floats) is
+// fetched with 16-byte loads up front so the loads are in flight together
+__global__ void __launch_bounds__(128)
 mimi_embed_kernel(const float* __restrict__ latents, const int* __restrict__ slot_ids,
                   const float* __restrict__ emb_std, const float* __restrict__ emb_mean,
                   const float* __restrict__ w_q, const float* __restrict__ w_up,
                   float* __restrict__ e_prev, float* __restrict__ xm, int C, int ldim, int S) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float z[64];
   const int i = blockIdx.x, slot = slot_ids[i];
   if (threadIdx.x < ldim)
     z[threadIdx.x] = latents[i * ldim + threadIdx.x] * emb_std[threadIdx.x] + emb_mean[threadIdx.x];
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float* w = w_q + (long long)c * ldim;
-    float e = 0.0f;
-    for (int j = 0; j < ldim; ++j) e = fmaf(w[j], z[j], e);
-    const float ep = e_prev[(long long)slot * C + c];
-    e_prev[(long long)slot * C + c] = e;
-    const float* wu = w_up + (long long)c * 2 * S;
-    // out[t] = e * w[t] + e_prev * w[S + t]   (K = 2S transposed conv, stride S, depthwise)
-    for (int t = 0; t < S; ++t)
-      xm[((long long)i * S + t) * C + c] = e * wu[t] + ep * wu[S + t];
+  const int c = blockIdx.y * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float* w = w_q + (long long)c * ldim;
+  float e = 0.0f;
+  for (int j = 0; j < ldim; j += 4) {
+    const float4 wv = load4(w + j);
+    e = fmaf(wv.x, z[j], e);
+    e = fmaf(wv.y, z[j + 1], e);
+    e = fmaf(wv.z, z[j + 2], e);
+    e = fmaf(wv.w, z[j + 3], e);
+  }
+  const float ep = e_prev[(long long)slot * C + c];
+  e_prev[(long long)slot * C + c] = e;
+  const float* wu = w_up + (long long)c * 2 * S;
+  // out[t] = e * w[t] + e_prev * w[S + t]   (K = 2S transposed conv, stride S, depthwise)
+  for (int t = 0; t < S; t += 4) {
+    const float4 a = load4(wu + t), b = load4(wu + S + t);
+    float* o = xm + ((long long)i * S + t) * C + c;
+    o[0] = e * a.x + ep * b.x;
+    o[C] = e * a.y + ep * b.y;
+    o[2 * C] = e * a.z + ep * b.z;
+    o[3 * C] = e * a.w + ep * b.w;
   }
 }
 
 cudaError_t launch_mimi_embed(const float* latents, const int* slot_ids, const float* emb_std,
                               const float* emb_mean, const float* w_q, const float* w_up,
                               float* e_prev, float* xm, int n, int C, int ldim, int S, cudaStream_t st) {
-  if (ldim > 64) return cudaErrorInvalidValue;
-  mimi_embed_kernel<<<n, 512, 0, st>>>(latents, slot_ids, emb_std, emb_mean, w_q, w_up, e_prev, xm, C, ldim, S);
+  if (ldim > 64 || ldim % 4 || S % 4) return cudaErrorInvalidValue;
+  launch_k(mimi_embed_kernel, dim3(n, (C + 127) / 128), 128, 0, st, latents, slot_ids, emb_std, emb_mean, w_q, w_up,
+           e_prev, xm, C, ldim, S);
   return cudaGetLastError();
 }
 
 template <typename TO>
 __global__ void stage_rows_kernel(const float* __restrict__ xm, TO* __restrict__ buf, int T, int C,
                                   int hist, long long total4) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= total4) return;
   const long long e = q * 4;
@@ -55,8 +73,8 @@ cudaError_t launch_stage_rows(const float* xm, void* buf, int buf_type, int n, i
                               cudaStream_t st) {
   const long long total4 = (long long)n * T * C / 4;
   const int blocks = (int)((total4 + 255) / 256);
-  if (buf_type == 0) stage_rows_kernel<float><<<blocks, 256, 0, st>>>(xm, (float*)buf, T, C, hist, total4);
-  else stage_rows_kernel<bf16><<<blocks, 256, 0, st>>>(xm, (bf16*)buf, T, C, hist, total4);
+  if (buf_type == 0) launch_k(stage_rows_kernel<float>, blocks, 256, 0, st, xm, (float*)buf, T, C, hist, total4);
+  else launch_k(stage_rows_kernel<bf16>, blocks, 256, 0, st, xm, (bf16*)buf, T, C, hist, total4);
   return cudaGetLastError();
 }
 
@@ -64,6 +82,8 @@ cudaError_t launch_stage_rows(const float* xm, void* buf, int buf_type, int n, i
 template <typename T, bool GATHER>
 __global__ void __launch_bounds__(128)
 hist_move_kernel(HistTable tab, const int* __restrict__ slot_ids) {
+  pdl_launch_dependents();
+  pdl_wait();
   const HistDesc d = tab.d[blockIdx.y];
   const int i = blockIdx.x, slot = slot_ids[i];
   const int total = d.hist * d.C;
@@ -79,14 +99,14 @@ hist_move_kernel(HistTable tab, const int* __restrict__ slot_ids) {
 
 cudaError_t launch_hist_gather(const HistTable& t, const int* slot_ids, int type, int n, cudaStream_t st) {
   dim3 grid(n, t.count);
-  if (type == 0) hist_move_kernel<float, true><<<grid, 128, 0, st>>>(t, slot_ids);
-  else hist_move_kernel<bf16, true><<<grid, 128, 0, st>>>(t, slot_ids);
+  if (type == 0) launch_k(hist_move_kernel<float, true>, grid, 128, 0, st, t, slot_ids);
+  else launch_k(hist_move_kernel<bf16, true>, grid, 128, 0, st, t, slot_ids);
   return cudaGetLastError();
 }
 cudaError_t launch_hist_scatter(const HistTable& t, const int* slot_ids, int type, int n, cudaStream_t st) {
   dim3 grid(n, t.count);
-  if (type == 0) hist_move_kernel<float, false><<<grid, 128, 0, st>>>(t, slot_ids);
-  else hist_move_kernel<bf16, false><<<grid, 128, 0, st>>>(t, slot_ids);
+  if (type == 0) launch_k(hist_move_kernel<float, false>, grid, 128, 0, st, t, slot_ids);
+  else launch_k(hist_move_kernel<bf16, false>, grid, 128, 0, st, t, slot_ids);
   return cudaGetLastError();
 }
 
@@ -96,6 +116,8 @@ template <typename T>
 __global__ void __launch_bounds__(128)
 last_conv_kernel(const T* __restrict__ buf, const float* __restrict__ w, const float* __restrict__ b,
                  float* __restrict__ pcm, int Tn, int C, int K) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float sm[];
   float* sw = sm;               // K*C
   float* sx = sm + K * C;       // (128+K-1) * (C+1)
@@ -127,27 +149,31 @@ cudaError_t launch_last_conv(const void* buf, int buf_type, const float* w, cons
   dim3 grid((T + 127) / 128, n);
   const size_t smem = (size_t)(K * C + (128 + K - 1) * (C + 1)) * sizeof(float);
   if (smem > 48 * 1024) return cudaErrorInvalidValue;
-  if (buf_type == 0) last_conv_kernel<float><<<grid, 128, smem, st>>>((const float*)buf, w, b, pcm, T, C, K);
-  else last_conv_kernel<bf16><<<grid, 128, smem, st>>>((const bf16*)buf, w, b, pcm, T, C, K);
+  if (buf_type == 0) launch_k(last_conv_kernel<float>, grid, 128, smem, st, (const float*)buf, w, b, pcm, T, C, K);
+  else launch_k(last_conv_kernel<bf16>, grid, 128, smem, st, (const bf16*)buf, w, b, pcm, T, C, K);
   return cudaGetLastError();
 }
 
 __global__ void f32_to_bf16_kernel(const float* __restrict__ s, bf16* __restrict__ d, long long n) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     d[i] = __float2bfloat16_rn(s[i]);
 }
 cudaError_t launch_f32_to_bf16(const float* src, bf16* dst, long long n, cudaStream_t st) {
   if (n <= 0) return cudaSuccess;
-  f32_to_bf16_kernel<<<(int)min(4096LL, (n + 255) / 256), 256, 0, st>>>(src, dst, n);
+  launch_k(f32_to_bf16_kernel, (int)min(4096LL, (n + 255) / 256), 256, 0, st, src, dst, n);
   return cudaGetLastError();
 }
 __global__ void fill_f32_kernel(float* __restrict__ d, float v, long long n) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     d[i] = v;
 }
 cudaError_t launch_fill_f32(float* dst, float v, long long n, cudaStream_t st) {
   if (n <= 0) return cudaSuccess;
-  fill_f32_kernel<<<(int)min(4096LL, (n + 255) / 256), 256, 0, st>>>(dst, v, n);
+  launch_k(fill_f32_kernel, (int)min(4096LL, (n + 255) / 256), 256, 0, st, dst, v, n);
   return cudaGetLastError();
 }
 
@@ -155,12 +181,14 @@ cudaError_t launch_fill_f32(float* dst, float v, long long n, cudaStream_t st) {
 
 namespace ptts {
 __global__ void bf16_to_f32_kernel(const bf16* __restrict__ s, float* __restrict__ d, long long n) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     d[i] = __bfloat162float(s[i]);
 }
 cudaError_t launch_bf16_to_f32(const bf16* src, float* dst, long long n, cudaStream_t st) {
   if (n <= 0) return cudaSuccess;
-  bf16_to_f32_kernel<<<(int)min(4096LL, (n + 255) / 256), 256, 0, st>>>(src, dst, n);
+  launch_k(bf16_to_f32_kernel, (int)min(4096LL, (n + 255) / 256), 256, 0, st, src, dst, n);
   return cudaGetLastError();
 }
 }  // namespace ptts
