@@ -137,7 +137,7 @@ int Engine::init() {
     b_raw[i] = act_alloc((size_t)S * T2 * C2);
     b_res[i] = act_alloc((size_t)S * (c.res_kernel - 1 + T2) * C2);
     add_hist(b_res[i], c.res_kernel - 1, T2, C2);
-    b_hid[i] = act_alloc((size_t)S * T2 * hc);
+    b_hid[i] = act_alloc((size_t)S * T2 * hid_width(hc));
     T = T2; C = C2;
   }
   b_last = act_alloc((size_t)S * (c.last_kernel - 1 + T) * C);

@@ -117,6 +117,8 @@ class Engine {
   int mimi_sequence(int n, const float* latents);
   int frame(int n, int lsd, int audio);  // eager or graph
   void* act_alloc(size_t elems);
+  // ResBlock hidden width as stored (bf16 mode pads to a multiple of 64 channels)
+  int hid_width(int hc) const { return act_type == 1 ? ((hc + 63) / 64) * 64 : hc; }
 
   bool ready = false;
   int act_type = 0;  // 0 fp32, 1 bf16

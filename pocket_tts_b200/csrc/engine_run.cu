@@ -160,7 +160,7 @@ int Engine::mimi_sequence(int n, const float* latents) {
     if ((rc = gemm("seanet.conv0", b_conv0, true, batched((long long)rpb * C, rpb, T, C), conv0, n * rpb, ep, true)) != PTTS_OK) return rc;
   }
   for (int i = 0; i < 3; ++i) {
-    const int r = c.ratios[i], T2 = T * r, C2 = C / 2, hc = C2 / 2, rk = c.res_kernel - 1;
+    const int r = c.ratios[i], T2 = T * r, C2 = C / 2, hc = hid_width(C2 / 2), rk = c.res_kernel - 1;
     {  // ConvTranspose1d K=2r (seanet.py:147-152): raw -> b_raw (residual), ELU(raw) -> b_res
       const int rpb = 1 + T;
       GemmEpilogue ep; ep.bias = stages[i].tr_b; ep.act_post = ACT_ELU;

@@ -2,6 +2,8 @@
 //  into device weights, re-laying convolutions out as GEMM operands.
 #include "engine.h"
 
+#include <algorithm>
+
 namespace ptts {
 
 // Conv1d weight [C_out, C_in, K] -> GEMM weight [C_out, K*C_in] (k-major, channels-last rows)
@@ -162,9 +164,23 @@ int Engine::finalize() {
     if (!w3 || !w1) return PTTS_EINVAL;
     if (w3->shape != std::vector<int64_t>{hc, C2, c.res_kernel} || w1->shape != std::vector<int64_t>{C2, hc, 1})
       PTTS_FAIL(PTTS_EINVAL, "bad resblock shapes at %s", pr.c_str());
-    if ((rc = make_mat_from(conv_to_gemm(*w3), hc, c.res_kernel * C2, &stages[i].c3)) != PTTS_OK) return rc;
-    if ((rc = make_mat_from(conv_to_gemm(*w1), C2, hc, &stages[i].c1)) != PTTS_OK) return rc;
-    GETV(stages[i].c3_b, pr + "1.conv.bias", hc);
+    // bf16 mode: the hidden width is zero-padded to a multiple of 64 channels so that the 1x1 conv's
+    // reduction dim fills a 128-byte swizzle row (tcgen05 path); padded channels stay exactly 0:
+    // zero weight rows + zero bias -> ELU(0) = 0 -> multiplied by zero weight columns.
+    const int hp = hid_width(hc);
+    {
+      std::vector<float> g3 = conv_to_gemm(*w3), g1 = conv_to_gemm(*w1);
+      const int k3 = c.res_kernel * C2;
+      std::vector<float> p3((size_t)hp * k3, 0.0f), p1((size_t)C2 * hp, 0.0f), b3(hp, 0.0f);
+      for (int o = 0; o < hc; ++o) std::copy(g3.begin() + (size_t)o * k3, g3.begin() + (size_t)(o + 1) * k3, p3.begin() + (size_t)o * k3);
+      for (int o = 0; o < C2; ++o) std::copy(g1.begin() + (size_t)o * hc, g1.begin() + (size_t)(o + 1) * hc, p1.begin() + (size_t)o * hp);
+      const HostTensor* bb = need(pr + "1.conv.bias");
+      if (!bb || bb->numel() != hc) PTTS_FAIL(PTTS_EINVAL, "bad bias for %s1.conv", pr.c_str());
+      std::copy(bb->data.begin(), bb->data.end(), b3.begin());
+      if ((rc = make_mat_from(p3, hp, k3, &stages[i].c3)) != PTTS_OK) return rc;
+      if ((rc = make_mat_from(p1, C2, hp, &stages[i].c1)) != PTTS_OK) return rc;
+      stages[i].c3_b = upload(b3);
+    }
     GETV(stages[i].c1_b, pr + "3.conv.bias", C2);
     C = C2;
     idx += 3;

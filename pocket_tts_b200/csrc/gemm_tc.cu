@@ -215,67 +215,100 @@ template <int CH> __device__ __forceinline__ void act_inplace(float* v, int act)
   }
 }
 
-// Row-major epilogue (SWAP = false): this thread owns output row r, columns come from TMEM.
+// Row-major epilogue (SWAP = false).  TMEM hands every thread one output ROW, but global memory
+// wants consecutive lanes on consecutive COLUMNS: each epilogue warp therefore stages its
+// 32 rows x CH columns chunk in shared memory (padded, conflict free both ways) and re-reads it
+// with CH/8 lanes per row, 8 columns per lane, so that bias / gate / residual loads and the
+// out / out2 stores are row-contiguous 16-byte accesses.  Per-row addresses (the RowMaps) are
+// computed once per row into shared memory.
+struct RowMeta {
+  long long out, res, out2;   // element offsets, out < 0: row not written
+};
+constexpr int EPI_STAGE_FLOATS = 32 * 36;                     // per warp
+constexpr size_t EPI_SMEM_BYTES = 8 * EPI_STAGE_FLOATS * 4 + BM_TC * sizeof(RowMeta);
+
 template <int BN, typename TO>
-__device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, const TcParams& P, uint32_t taddr, int r,
-                                              int col0, int half) {
+__device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, const TcParams& P, uint32_t taddr, int row0,
+                                              int col0, int q, int half, int lane, uint8_t* scratch) {
   constexpr int CH = BN >= 32 ? 32 : 16;
   constexpr int NCH = BN / CH;
-  bool valid = r < P.M;
-  TO* orow = nullptr;
-  const TO* rrow = nullptr;
-  TO* o2row = nullptr;
-  if (valid) {
-    const int ob = r / ep.out_map.rows_per_batch, ot = r - ob * ep.out_map.rows_per_batch;
-    valid = ot < ep.out_map.valid_rows;
-    orow = reinterpret_cast<TO*>(ep.out) + ob * ep.out_map.batch_stride + (long long)ot * ep.out_map.ld;
-    if (ep.res) {
-      const int rb = r / ep.res_map.rows_per_batch, rt = r - rb * ep.res_map.rows_per_batch;
-      rrow = reinterpret_cast<const TO*>(ep.res) + rb * ep.res_map.batch_stride + (long long)rt * ep.res_map.ld;
+  constexpr int LD = CH + 4;
+  constexpr int LPR = CH / 8;          // lanes per row when re-reading
+  constexpr int RPI = 32 / LPR;        // rows per iteration
+  RowMeta* meta = reinterpret_cast<RowMeta*>(scratch + 8 * EPI_STAGE_FLOATS * 4);
+  float* stage = reinterpret_cast<float*>(scratch) + (q + 4 * half) * EPI_STAGE_FLOATS;
+  if (half == 0) {
+    const int rl = q * 32 + lane, r = row0 + rl;
+    RowMeta mt{-1, 0, 0};
+    if (r < P.M) {
+      const int ob = r / ep.out_map.rows_per_batch, ot = r - ob * ep.out_map.rows_per_batch;
+      if (ot < ep.out_map.valid_rows) {
+        mt.out = ob * ep.out_map.batch_stride + (long long)ot * ep.out_map.ld;
+        if (ep.res) {
+          const int rb = r / ep.res_map.rows_per_batch, rt = r - rb * ep.res_map.rows_per_batch;
+          mt.res = rb * ep.res_map.batch_stride + (long long)rt * ep.res_map.ld;
+        }
+        if (ep.out2) {
+          const int b2 = r / ep.out2_map.rows_per_batch, t2 = r - b2 * ep.out2_map.rows_per_batch;
+          mt.out2 = b2 * ep.out2_map.batch_stride + (long long)t2 * ep.out2_map.ld;
+        }
+      }
     }
-    if (ep.out2) {
-      const int b2 = r / ep.out2_map.rows_per_batch, t2 = r - b2 * ep.out2_map.rows_per_batch;
-      o2row = reinterpret_cast<TO*>(ep.out2) + b2 * ep.out2_map.batch_stride + (long long)t2 * ep.out2_map.ld;
-    }
+    meta[rl] = mt;
   }
-  const float* grow = ep.gate ? ep.gate + (long long)r * ep.gate_ld : nullptr;
+  asm volatile("bar.sync 1, 256;" ::: "memory");   // the 8 epilogue warps
+  const int sub = lane / LPR, cg = lane % LPR;
 #pragma unroll 1
   for (int ci = half; ci < NCH; ci += 2) {
     const int c = ci * CH, n0 = col0 + c;
     if (n0 >= P.N) break;   // uniform
-    float v[CH];
-    tmem_ld<CH>(taddr + c, v);   // warp-collective: executed by every lane
-    if (valid) {
-      float t[CH];
-      if (ep.bias) {
-        row_load<CH>(ep.bias + n0, t);
+    {
+      float v[CH];
+      tmem_ld<CH>(taddr + c, v);   // warp-collective
 #pragma unroll
-        for (int j = 0; j < CH; ++j) v[j] += t[j];
-      }
-      act_inplace<CH>(v, ep.act_pre);
-      if (grow) {
-        row_load<CH>(grow + n0, t);
-#pragma unroll
-        for (int j = 0; j < CH; ++j) v[j] *= t[j];
-      }
-      if (ep.colscale) {
-        row_load<CH>(ep.colscale + n0, t);
-#pragma unroll
-        for (int j = 0; j < CH; ++j) v[j] *= t[j];
-      }
-      if (ep.alpha != 1.0f) {
-#pragma unroll
-        for (int j = 0; j < CH; ++j) v[j] *= ep.alpha;
-      }
-      if (rrow) {
-        row_load<CH>(rrow + n0, t);
-#pragma unroll
-        for (int j = 0; j < CH; ++j) v[j] += t[j];
-      }
-      if (o2row) row_store<CH>(o2row + n0, v);
-      act_inplace<CH>(v, ep.act_post);
-      row_store<CH>(orow + n0, v);
+      for (int j = 0; j < CH; j += 4) *reinterpret_cast<float4*>(stage + lane * LD + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
     }
+    __syncwarp();
+    const int n = n0 + cg * 8;
+    float bias[8], cs[8];
+    if (ep.bias) row_load<8>(ep.bias + n, bias);
+    if (ep.colscale) row_load<8>(ep.colscale + n, cs);
+#pragma unroll
+    for (int it = 0; it < LPR; ++it) {
+      const int rl = q * 32 + it * RPI + sub;
+      const RowMeta mt = meta[rl];
+      if (mt.out >= 0) {
+        float x[8], t[8];
+        row_load<8>(stage + (it * RPI + sub) * LD + cg * 8, x);
+        if (ep.bias) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] += bias[j];
+        }
+        act_inplace<8>(x, ep.act_pre);
+        if (ep.gate) {
+          row_load<8>(ep.gate + (long long)(row0 + rl) * ep.gate_ld + n, t);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] *= t[j];
+        }
+        if (ep.colscale) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] *= cs[j];
+        }
+        if (ep.alpha != 1.0f) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] *= ep.alpha;
+        }
+        if (ep.res) {
+          row_load<8>(reinterpret_cast<const TO*>(ep.res) + mt.res + n, t);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) x[j] += t[j];
+        }
+        if (ep.out2) row_store<8>(reinterpret_cast<TO*>(ep.out2) + mt.out2 + n, x);
+        act_inplace<8>(x, ep.act_post);
+        row_store<8>(reinterpret_cast<TO*>(ep.out) + mt.out + n, x);
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -501,7 +534,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
       partial_push<BN>(P, taddr, slab, P.cluster, (int)blockIdx.z, q * 32 + lane, half);
     } else if (nkb > 0) {
       if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half);
-      else epilogue_rows<BN, TO>(ep, P, taddr, r, col0, half);
+      else epilogue_rows<BN, TO>(ep, P, taddr, row0, col0, q, half, lane, tiles);
     }
     tc_fence_before();
     if (warp == 2) TC_TRACE(3);
@@ -570,7 +603,9 @@ template <int BN, bool SWAP, typename TO>
 static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, const TcParams& P, const GemmEpilogue& ep,
                               dim3 grid, bool pdl, cudaStream_t st) {
   const bool clustered = SWAP && P.cluster > 1;
-  const size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + (clustered ? (size_t)BN * BM_TC * sizeof(float) : 0) + 1024;
+  size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + (clustered ? (size_t)BN * BM_TC * sizeof(float) : 0);
+  if (!SWAP) smem = std::max(smem, EPI_SMEM_BYTES);   // the epilogue staging reuses the (drained) pipeline buffers
+  smem += 1024;
   static bool attr_done = false;
   auto kern = gemm_tc_kernel<BN, SWAP, TO>;
   if (!attr_done) {
