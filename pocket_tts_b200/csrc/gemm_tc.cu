@@ -65,6 +65,30 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
 __device__ __forceinline__ void tc_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// 32-bit shared-address forms for the single-thread issue loops (no generic->shared conversion,
+// no 64-bit address arithmetic per k-block)
+__device__ __forceinline__ void mbar_expect_tx_a(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra WAIT_DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "WAIT_DONE:\n\t"
+      "}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_a(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_commit_a(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
@@ -457,13 +481,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     // first ring pass: weight tiles first (independent of the previous kernel), then, once the
     // previous kernel's results are visible, the activation tiles of the same stages
+    const uint32_t t0a = smem_u32(tiles), f0a = smem_u32(&full_bar[0]);
     for (int i = 0; i < n_pre; ++i) {
-      mbar_expect_tx(&full_bar[i], STAGE_BYTES);
-      tma_load_2d(tiles + (size_t)i * STAGE_BYTES + w_off, tm_w, &full_bar[i], (kb0 + i) * BK_TC, w_row);
+      mbar_expect_tx_a(f0a + 8u * i, STAGE_BYTES);
+      tma_load_2d_a(t0a + i * STAGE_BYTES + w_off, tm_w, f0a + 8u * i, (kb0 + i) * BK_TC, w_row);
     }
     pdl_wait();
     for (int i = 0; i < n_pre; ++i)
-      tma_load_2d(tiles + (size_t)i * STAGE_BYTES + a_off, tm_a, &full_bar[i], (kb0 + i) * BK_TC, a_row);
+      tma_load_2d_a(t0a + i * STAGE_BYTES + a_off, tm_a, f0a + 8u * i, (kb0 + i) * BK_TC, a_row);
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "n"(TMEM_COLS) : "memory");
@@ -477,47 +502,53 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   const uint32_t tmem_base = tmem_base_smem;
   if (warp == 2) TC_TRACE(0);
 
+  const uint32_t tiles_a = smem_u32(tiles), full_a = smem_u32(&full_bar[0]), empty_a = smem_u32(&empty_bar[0]);
   if (warp == 0) {
-    // ===== TMA producer: the whole warp walks the ring, one lane issues =====
+    // ===== TMA producer: the whole warp walks the ring, one lane issues.  Stage / phase are
+    // tracked incrementally: a runtime i % stages costs more than the two TMA issues. =====
+    uint32_t s = 0, ph = 1;   // i = n_pre is the first k-block of ring pass 1 (only reached when n_pre == stages)
+    int kcoord = (kb0 + n_pre) * BK_TC;
     for (int i = n_pre; i < nkb; ++i) {
-      const int s = i % P.stages;
-      const uint32_t ph = (i / P.stages) & 1;
-      mbar_wait(&empty_bar[s], ph ^ 1);
+      mbar_wait_a(empty_a + 8u * s, ph ^ 1u);
       TC_TRACE(8 + i * 4 + 0);
       if (lane == 0) {
-        mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-        uint8_t* st = tiles + (size_t)s * STAGE_BYTES;
-        tma_load_2d(st + w_off, tm_w, &full_bar[s], (kb0 + i) * BK_TC, w_row);
-        tma_load_2d(st + a_off, tm_a, &full_bar[s], (kb0 + i) * BK_TC, a_row);
+        const uint32_t st = tiles_a + s * STAGE_BYTES, fb = full_a + 8u * s;
+        mbar_expect_tx_a(fb, STAGE_BYTES);
+        tma_load_2d_a(st + w_off, tm_w, fb, kcoord, w_row);
+        tma_load_2d_a(st + a_off, tm_a, fb, kcoord, a_row);
       }
       __syncwarp();
+      kcoord += BK_TC;
+      if (++s == (uint32_t)P.stages) { s = 0; ph ^= 1u; }
     }
     if (clustered) cluster_wait_acquire();
   } else if (warp == 1) {
     // ===== MMA issuer: whole warp waits, one lane issues =====
     // instruction descriptor: D=f32, A=B=bf16, both K-major, N>>3 at bit 17, M>>4 at bit 24
     const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM_TC >> 4) << 24);
+    const uint64_t adesc0 = make_sw128_desc(tiles_a), bdesc0 = make_sw128_desc(tiles_a + A_BYTES);
+    const uint32_t tfull_a = smem_u32(&tmem_full_bar);
+    uint32_t s = 0, ph = 0;
     for (int i = 0; i < nkb; ++i) {
-      const int s = i % P.stages;
-      const uint32_t ph = (i / P.stages) & 1;
-      mbar_wait(&full_bar[s], ph);
+      mbar_wait_a(full_a + 8u * s, ph);
       tc_fence_after();
       TC_TRACE(8 + i * 4 + 1);
       if (lane == 0) {
-        const uint32_t a_addr = smem_u32(tiles + (size_t)s * STAGE_BYTES);
-        const uint64_t adesc = make_sw128_desc(a_addr), bdesc = make_sw128_desc(a_addr + A_BYTES);
+        const uint64_t soff = (uint64_t)((s * STAGE_BYTES) >> 4);   // stage offset in the 16-byte address field
+        const uint64_t adesc = adesc0 + soff, bdesc = bdesc0 + soff;
 #pragma unroll
         for (int k = 0; k < BK_TC / 16; ++k) {
           // advance 16 bf16 = 32 bytes inside the swizzled 128-byte row: +2 in 16-byte units
           tc_mma_bf16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (i | k) != 0);
         }
-        tc_commit(&empty_bar[s]);   // frees the smem stage when these MMAs retire
-        if (i == nkb - 1) tc_commit(&tmem_full_bar);    // accumulator complete
+        tc_commit_a(empty_a + 8u * s);   // frees the smem stage when these MMAs retire
+        if (i == nkb - 1) tc_commit_a(tfull_a);    // accumulator complete
       }
       TC_TRACE(8 + i * 4 + 2);
       __syncwarp();
+      if (++s == (uint32_t)P.stages) { s = 0; ph ^= 1u; }
     }
-    if (nkb == 0 && lane == 0) tc_commit(&tmem_full_bar);
+    if (nkb == 0 && lane == 0) tc_commit_a(tfull_a);
     if (clustered) cluster_wait_acquire();
   } else {
     // ===== epilogue warps 2..9: TMEM lane quarter = warp % 4, two warps share a quarter and
@@ -712,14 +743,31 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     }
 #undef TC_CASE
   }
-  // row-major: largest BN that still gives every SM a CTA (weights re-read from L2, not HBM)
-  int bn = pick_bn(p.N);
+  // row-major tile width from a small cost model (measured with the clock trace): a CTA costs
+  // ~1.5 us set-up + 0.24 us per k-block (four tcgen05.mma issues + commit, independent of N) +
+  // ~2 us epilogue latency + 0.3 us per 64 columns; the grid runs in waves of n_sms CTAs.
   const int tiles_m = (p.M + BM_TC - 1) / BM_TC;
-  while (bn > 32 && tiles_m * ((p.N + bn - 1) / bn) < n_sms) bn >>= 1;
+  int bn = pick_bn(p.N);
+  {
+    double best = 1e30;
+    for (int cand = pick_bn(p.N); cand >= 32; cand >>= 1) {
+      const int ctas = tiles_m * ((p.N + cand - 1) / cand);
+      // multi-wave grids run two CTAs per SM (stage ring capped at ~108 KB below): one CTA's
+      // epilogue overlaps the other's mainloop, so a "wave" holds 2 * n_sms CTAs at ~1.3x the time
+      const bool two = ctas > n_sms;
+      const int waves = two ? (ctas + 2 * n_sms - 1) / (2 * n_sms) : 1;
+      const double t = waves * (two ? 1.3 : 1.0) * (3.5 + 0.24 * P.num_kb + 0.3 * cand / 64.0);
+      if (t < best - 1e-9) { best = t; bn = cand; }
+    }
+  }
   if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
   if (!make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
   P.kb_per_split = P.num_kb;
-  P.stages = (int)std::max<size_t>(1, std::min<size_t>(std::min(P.num_kb, 6), TC_SMEM_LIMIT / ((size_t)(BM_TC + bn) * 128)));
+  {
+    const int ctas = tiles_m * ((p.N + bn - 1) / bn);
+    const size_t budget = ctas > n_sms ? (size_t)108 * 1024 : TC_SMEM_LIMIT;   // 2 CTAs per SM for multi-wave grids
+    P.stages = (int)std::max<size_t>(1, std::min<size_t>(std::min(P.num_kb, 6), budget / ((size_t)(BM_TC + bn) * 128)));
+  }
   dim3 grid(tiles_m, (p.N + bn - 1) / bn, 1);
 #define TC_CASE(BNV)                                                                          \
   case BNV:                                                                                   \
