@@ -36,6 +36,9 @@ Engine::~Engine() {
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (void* p : allocs) cudaFree(p);
   if (h_pinned) cudaFreeHost(h_pinned);
+  if (ev_fork) cudaEventDestroy(ev_fork);
+  if (ev_join) cudaEventDestroy(ev_join);
+  if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
 }
 
@@ -59,6 +62,10 @@ int Engine::init() {
     PTTS_FAIL(PTTS_EINVAL, "unknown precision %d", c.precision);
   PTTS_CUDA_CHECK(cudaSetDevice(c.device));
   PTTS_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  PTTS_CUDA_CHECK(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+  PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+  PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
+  if (const char* f = getenv("PTTS_PIPELINE")) use_pipeline = !(f[0] == '0');
   PTTS_CUDA_CHECK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, c.device));
   if (const char* f = getenv("PTTS_FORCE_SIMT")) use_tc = !(f[0] == '1');
   act_type = c.precision == PTTS_PRECISION_BF16 ? 1 : 0;
@@ -101,6 +108,8 @@ int Engine::init() {
   noise_buf = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
   lat_in = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
   x_lat = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
+  lat_ring[0] = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
+  lat_ring[1] = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
   c_cond = act_alloc((size_t)S * D);
   cemb = dmalloc<float>(allocs, (size_t)S * F, stream);
   sy = act_alloc((size_t)S * F);

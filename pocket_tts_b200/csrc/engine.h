@@ -51,10 +51,12 @@ struct ConvStageW {
 
 struct GraphKey {
   int n, lsd, audio;
+  int mode = 0;   // 0: sequential frame; 8 + parity*4 + do_flow*2 + do_mimi: pipelined frame
   bool operator<(const GraphKey& o) const {
     if (n != o.n) return n < o.n;
     if (lsd != o.lsd) return lsd < o.lsd;
-    return audio < o.audio;
+    if (audio != o.audio) return audio < o.audio;
+    return mode < o.mode;
   }
 };
 struct GraphEntry {
@@ -94,6 +96,9 @@ class Engine {
 
   ptts_config cfg;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;          // Mimi branch of the pipelined frame
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool use_pipeline = true;                // PTTS_PIPELINE=0 disables
   long long launches = 0;
   bool use_graphs = true;
   bool use_tc = true;   // bf16 mode: tcgen05 GEMMs (PTTS_FORCE_SIMT=1 disables)
@@ -116,6 +121,10 @@ class Engine {
   int flow_sequence(int n, int lsd);
   int mimi_sequence(int n, const float* latents);
   int frame(int n, int lsd, int audio);  // eager or graph
+  // FlowLM + head of the current frame on `stream` in parallel with the Mimi decode of the previous
+  // frame's latents on `stream2` (two branches of one graph), like the reference's decoder thread
+  // (tts_model.py:651-658): the Mimi chain never feeds back into the FlowLM chain.
+  int frame_pipelined(int n, int lsd, int parity, bool do_flow, bool do_mimi);
   void* act_alloc(size_t elems);
   // ResBlock hidden width as stored (bf16 mode pads to a multiple of 64 channels)
   int hid_width(int hc) const { return act_type == 1 ? ((hc + 63) / 64) * 64 : hc; }
@@ -174,6 +183,8 @@ class Engine {
   std::map<GraphKey, GraphEntry> graphs;
   std::vector<int> cur_slots;
   float* h_pinned = nullptr;
+  float* lat_ring[2] = {nullptr, nullptr};   // latents handed from the FlowLM branch to the Mimi branch
+  float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)
   std::map<std::string, std::pair<const void*, std::pair<int, long long>>> debug_bufs;  // name -> (ptr,(type,elems per row unit))
 };
 

@@ -217,6 +217,55 @@ int Engine::frame(int n, int lsd, int audio) {
   return PTTS_OK;
 }
 
+int Engine::frame_pipelined(int n, int lsd, int parity, bool do_flow, bool do_mimi) {
+  auto body = [&]() -> int {
+    int rc = PTTS_OK;
+    if (do_mimi && do_flow) {
+      PTTS_CUDA_CHECK(cudaEventRecord(ev_fork, stream));
+      PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_fork, 0));
+    }
+    if (do_flow) {
+      commit_out = lat_ring[parity];
+      rc = flow_sequence(n, lsd);
+      commit_out = nullptr;
+      if (rc != PTTS_OK) return rc;
+    }
+    if (do_mimi) {
+      cudaStream_t main_stream = stream;
+      if (do_flow) stream = stream2;           // the launchers read the member
+      rc = mimi_sequence(n, lat_ring[parity ^ 1]);
+      stream = main_stream;
+      if (rc != PTTS_OK) return rc;
+      if (do_flow) {
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_join, stream2));
+        PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_join, 0));
+      }
+    }
+    return PTTS_OK;
+  };
+  if (!use_graphs) return body();
+  GraphKey key{n, lsd, 1, 8 + parity * 4 + (do_flow ? 2 : 0) + (do_mimi ? 1 : 0)};
+  auto it = graphs.find(key);
+  if (it == graphs.end()) {
+    const long long before = launches;
+    cudaGraph_t graph = nullptr;
+    PTTS_CUDA_CHECK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+    int rc = body();
+    cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+    if (rc != PTTS_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+    PTTS_CUDA_CHECK(ce);
+    GraphEntry ent;
+    ent.kernels = launches - before;
+    launches = before;
+    PTTS_CUDA_CHECK(cudaGraphInstantiate(&ent.exec, graph, 0));
+    cudaGraphDestroy(graph);
+    it = graphs.emplace(key, ent).first;
+  }
+  PTTS_CUDA_CHECK(cudaGraphLaunch(it->second.exec, stream));
+  launches += it->second.kernels;
+  return PTTS_OK;
+}
+
 int Engine::step(int n, const int* slots, const float* noise_any, int lsd, int audio, float* out_lat,
                  float* out_eos, float* out_pcm) {
   NEED_READY();
@@ -272,18 +321,33 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
   if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
   const int Ld = cfg.ldim;
   const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
-  for (int f = 0; f < n_frames; ++f) {
-    PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_dev + (size_t)f * n * Ld, (size_t)n * Ld * sizeof(float),
-                                    cudaMemcpyDeviceToDevice, stream));
-    static const int part = [] { const char* e = getenv("PTTS_PROFILE_PART"); return e ? atoi(e) : 0; }();  // 1: FlowLM+head only, 2: Mimi only (profiling)
-    if (part == 2) { if ((rc = mimi_sequence(n, x_lat)) != PTTS_OK) return rc; }
-    else if ((rc = frame(n, lsd, part == 1 ? 0 : 1)) != PTTS_OK) return rc;
+  static const int part = [] { const char* e = getenv("PTTS_PROFILE_PART"); return e ? atoi(e) : 0; }();  // 1: FlowLM+head only, 2: Mimi only (profiling)
+  const bool piped = use_pipeline && part == 0;
+  auto copy_pcm = [&](int f) -> int {
     if (out_pcm_dev)
       PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_dev + (size_t)f * fs, (size_t)n_frames * fs * sizeof(float), pcm,
                                         fs * sizeof(float), fs * sizeof(float), n, cudaMemcpyDeviceToDevice, stream));
+    return PTTS_OK;
+  };
+  for (int f = 0; f < n_frames; ++f) {
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_dev + (size_t)f * n * Ld, (size_t)n * Ld * sizeof(float),
+                                    cudaMemcpyDeviceToDevice, stream));
+    if (piped) {
+      // FlowLM(f) || Mimi(f-1); the PCM of frame f-1 is complete when this graph has joined
+      if ((rc = frame_pipelined(n, lsd, f & 1, true, f > 0)) != PTTS_OK) return rc;
+      if (f > 0 && (rc = copy_pcm(f - 1)) != PTTS_OK) return rc;
+    } else {
+      if (part == 2) { if ((rc = mimi_sequence(n, x_lat)) != PTTS_OK) return rc; }
+      else if ((rc = frame(n, lsd, part == 1 ? 0 : 1)) != PTTS_OK) return rc;
+      if ((rc = copy_pcm(f)) != PTTS_OK) return rc;
+    }
     if (out_lat_dev)
       PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat_dev + (size_t)f * n * Ld, x_lat, (size_t)n * Ld * sizeof(float),
                                       cudaMemcpyDeviceToDevice, stream));
+  }
+  if (piped) {   // drain: Mimi decode of the last frame
+    if ((rc = frame_pipelined(n, lsd, n_frames & 1, false, true)) != PTTS_OK) return rc;
+    if ((rc = copy_pcm(n_frames - 1)) != PTTS_OK) return rc;
   }
   for (int i = 0; i < n; ++i) {
     host_offsets[slots[i]] += n_frames;

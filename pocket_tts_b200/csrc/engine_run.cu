@@ -133,7 +133,7 @@ int Engine::flow_sequence(int n, int lsd) {
       if ((rc = gemm("head.final", g, true, plain(F), final_lin, n, ep, false)) != PTTS_OK) return rc;
     }
   }
-  LAUNCH("head.commit", launch_commit_latent(x_lat, d_slot_ids, prev_latent, nullptr, n, Ld, stream));
+  LAUNCH("head.commit", launch_commit_latent(x_lat, d_slot_ids, prev_latent, commit_out, n, Ld, stream));
   return PTTS_OK;
 }
 

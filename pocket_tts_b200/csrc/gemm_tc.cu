@@ -629,6 +629,7 @@ static bool make_map(CUtensorMap* out, const void* base, long long rows, int K, 
 }
 
 constexpr size_t TC_SMEM_LIMIT = 225 * 1024;
+constexpr size_t TC_CORESIDENT_SMEM = 108 * 1024;   // two CTAs per SM
 
 template <int BN, bool SWAP, typename TO>
 static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, const TcParams& P, const GemmEpilogue& ep,
@@ -730,7 +731,10 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     if ((P.num_kb + P.kb_per_split - 1) / P.kb_per_split != splits) { splits = 1; P.kb_per_split = P.num_kb; }
     P.cluster = splits;
     const size_t stage = (size_t)(BM_TC + bn) * 128, slab = splits > 1 ? (size_t)bn * BM_TC * sizeof(float) : 0;
-    P.stages = (int)std::max<size_t>(1, std::min<size_t>(std::min(P.kb_per_split, 6), (TC_SMEM_LIMIT - slab) / stage));
+    // keep a CTA under ~half an SM's shared memory when possible: kernels of the two graph branches
+    // (FlowLM chain || Mimi chain) and consecutive waves can then share an SM
+    const size_t budget = (stage + slab <= TC_CORESIDENT_SMEM) ? TC_CORESIDENT_SMEM : TC_SMEM_LIMIT;
+    P.stages = (int)std::max<size_t>(1, std::min<size_t>(std::min(P.kb_per_split, 6), (budget - slab) / stage));
     dim3 grid(tiles, 1, splits);
 #define TC_CASE(BNV)                                                                          \
   case BNV:                                                                                   \
@@ -765,7 +769,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   P.kb_per_split = P.num_kb;
   {
     const int ctas = tiles_m * ((p.N + bn - 1) / bn);
-    const size_t budget = ctas > n_sms ? (size_t)108 * 1024 : TC_SMEM_LIMIT;   // 2 CTAs per SM for multi-wave grids
+    (void)ctas;
+    const size_t budget = ((size_t)(BM_TC + bn) * 128 <= TC_CORESIDENT_SMEM) ? TC_CORESIDENT_SMEM : TC_SMEM_LIMIT;
     P.stages = (int)std::max<size_t>(1, std::min<size_t>(std::min(P.num_kb, 6), budget / ((size_t)(BM_TC + bn) * 128)));
   }
   dim3 grid(tiles_m, (p.N + bn - 1) / bn, 1);

@@ -162,6 +162,39 @@ def test_batch_of_64_streams_vs_oracle_english_6l():
     eng.close()
 
 
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_pipelined_run_frames_equals_step_sequence(precision):
+    """ptts_run_frames overlaps FlowLM(f) with Mimi(f-1) on two streams inside one CUDA graph; its
+    latents and PCM must be bit-identical to the same frames issued one ptts_step at a time."""
+    case = load_case("gen_2l")
+    orc = oracle_for(2)
+    G, B = 6, 3
+    eng = make_engine(2, precision=precision)
+    conds = [case["cond"][0]] * B
+    toks = [case["tokens"][0]] * B
+    noise = torch.randn(G, B, 32, generator=torch.Generator().manual_seed(11)) * 0.7 ** 0.5
+    a = _prefill_streams(eng, orc, conds, toks)
+    b = _prefill_streams(eng, orc, conds, toks)
+    lat_a, pcm_a = [], []
+    for g in range(G):
+        lat, _, pcm = eng.step(a, noise[g])
+        lat_a.append(lat); pcm_a.append(pcm)
+    lat_a, pcm_a = torch.stack(lat_a), torch.cat(pcm_a, dim=1)
+    pcm_b = torch.empty(B, G * 1920, device="cuda")
+    lat_b = torch.empty(G, B, 32, device="cuda")
+    eng.run_frames(b, noise.cuda().contiguous(), out_pcm=pcm_b, out_latents=lat_b)
+    eng.synchronize()
+    assert torch.equal(lat_a, lat_b.cpu())
+    assert torch.equal(pcm_a, pcm_b.cpu())
+    # a second call continues the same streams (pipeline was drained at the end of the first)
+    lat2, _, pcm2 = eng.step(a, noise[0])
+    pcm_c = torch.empty(B, 1920, device="cuda")
+    eng.run_frames(b, noise[:1].cuda().contiguous(), out_pcm=pcm_c)
+    eng.synchronize()
+    assert torch.equal(pcm2, pcm_c.cpu())
+    eng.close()
+
+
 def test_error_conventions():
     from pocket_tts_b200 import _native as N
     from pocket_tts_b200.engine import GenerationEngine, ModelConfig
