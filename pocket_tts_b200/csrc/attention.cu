@@ -76,7 +76,43 @@ __device__ __forceinline__ void attend4(OnlineSm& s, const TK* __restrict__ kbas
 
 // =====================================================================================
 // decode: one new position per stream.  grid (H, n), 128 threads.
+// A lane owns a 16-byte slice of a K / V row (8 bf16 or 4 fp32 dims) and a 32-lane load covers
+// RPL = 4 (bf16) or 2 (fp32) consecutive positions, so K/V stream in as fully coalesced 512-byte
+// requests.  Every lane group keeps its own online-softmax state for the positions it sees (no
+// per-iteration cross-lane max / sum); U loads of K and of V are in flight per warp before any is
+// consumed.  Groups are merged once at the end (shuffles, then shared memory across warps).
 // =====================================================================================
+template <typename TK> struct KvVec;
+template <> struct KvVec<bf16> {
+  static constexpr int EPL = 8;   // elements per lane
+  __device__ static void load(const bf16* p, float* f) {
+    const uint4 r = *reinterpret_cast<const uint4*>(p);
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[i]));
+      f[2 * i] = t.x; f[2 * i + 1] = t.y;
+    }
+  }
+  __device__ static void store(bf16* p, const float* f) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __nv_bfloat162 t = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&t);
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+template <> struct KvVec<float> {
+  static constexpr int EPL = 4;
+  __device__ static void load(const float* p, float* f) {
+    const float4 r = *reinterpret_cast<const float4*>(p);
+    f[0] = r.x; f[1] = r.y; f[2] = r.z; f[3] = r.w;
+  }
+  __device__ static void store(float* p, const float* f) { *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]); }
+};
+
 template <typename TK, typename TO>
 __global__ void __launch_bounds__(128)
 attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs,
@@ -85,52 +121,122 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   pdl_launch_dependents();
   pdl_wait();
   constexpr int NW = 4;
-  __shared__ float sm_m[NW], sm_l[NW];
-  __shared__ float2 sm_acc[NW][32];
+  constexpr int EPL = KvVec<TK>::EPL;      // dims per lane
+  constexpr int LPR = 64 / EPL;            // lanes per row: 8 / 16
+  constexpr int RPL = 32 / LPR;            // rows per warp load: 4 / 2
+  constexpr int U = 4;                     // loads in flight per warp (of K and of V)
+  __shared__ float sm_m[NW][32], sm_l[NW][32];
+  __shared__ float sm_acc[NW][32][EPL];
   const int h = blockIdx.x, i = blockIdx.y;
   const int slot = slot_ids[i];
   const int pos = offsets[slot];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int sub = lane / LPR, ch = lane % LPR;   // row within a load, 16-byte chunk of the row
   const int d_model = g.H * 64;
-  const float* row = qkv + (long long)i * 3 * d_model + h * 64 + 2 * lane;
-  const float fr = freqs[lane];
+  const float* row = qkv + (long long)i * 3 * d_model + h * 64 + ch * EPL;
 
-  // every warp rotates q redundantly (registers); warp 0 appends k and v
-  const float2 q = rope_pair(load2(row), (float)pos, fr);
-  if (w == 0) {
-    const float2 k = rope_pair(load2(row + d_model), (float)pos, fr);
-    const float2 v = load2(row + 2 * d_model);
-    store2(kv_row<TK>(g, layer, slot, 0, h, pos) + 2 * lane, k);
-    store2(kv_row<TK>(g, layer, slot, 1, h, pos) + 2 * lane, v);
+  // rotate this lane's slice of q (interleaved pairs, rope.py:36-58); lanes with sub == 0 of
+  // warp 0 append the rotated k and v
+  float q[EPL];
+  {
+    float kx[EPL], vx[EPL];
+#pragma unroll
+    for (int e = 0; e < EPL; e += 2) {
+      const float fr = freqs[(ch * EPL + e) >> 1];
+      const float2 qq = rope_pair(load2(row + e), (float)pos, fr);
+      q[e] = qq.x * 0.125f; q[e + 1] = qq.y * 0.125f;   // fold the 1/sqrt(64) softmax scale into q
+      if (w == 0 && sub == 0) {
+        const float2 kk = rope_pair(load2(row + d_model + e), (float)pos, fr);
+        const float2 vv = load2(row + 2 * d_model + e);
+        kx[e] = kk.x; kx[e + 1] = kk.y; vx[e] = vv.x; vx[e + 1] = vv.y;
+      }
+    }
+    if (w == 0 && sub == 0) {
+      KvVec<TK>::store(kv_row<TK>(g, layer, slot, 0, h, pos) + ch * EPL, kx);
+      KvVec<TK>::store(kv_row<TK>(g, layer, slot, 1, h, pos) + ch * EPL, vx);
+    }
   }
   __syncthreads();  // appended row visible to the block
 
-  const TK* kbase = kv_row<TK>(g, layer, slot, 0, h, 0);
-  const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0);
+  const TK* kbase = kv_row<TK>(g, layer, slot, 0, h, 0) + ch * EPL;
+  const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0) + ch * EPL;
   const int L = pos + 1;
-  OnlineSm s{-INFINITY, 0.0f, make_float2(0.f, 0.f)};
-  for (int p0 = w * 4; p0 < L; p0 += NW * 4) {
-    const int cnt = min(4, L - p0);
-    attend4<TK>(s, kbase, vbase, p0, cnt, q, 0.125f, lane);
-  }
-  if (lane == 0) { sm_m[w] = s.m; sm_l[w] = s.l; }
-  sm_acc[w][lane] = s.acc;
-  __syncthreads();
-  if (w == 0) {
-    float m = -INFINITY;
+  float m = -INFINITY, l = 0.0f, acc[EPL];
 #pragma unroll
-    for (int j = 0; j < NW; ++j) m = fmaxf(m, sm_m[j]);
-    float l = 0.0f;
-    float2 a = make_float2(0.f, 0.f);
+  for (int e = 0; e < EPL; ++e) acc[e] = 0.0f;
+  constexpr int STEP = NW * U * RPL;   // positions per block iteration
+  for (int p0 = w * U * RPL; p0 < L; p0 += STEP) {
+    float kf[U][EPL], vf[U][EPL];
 #pragma unroll
-    for (int j = 0; j < NW; ++j) {
-      const float c = expf(sm_m[j] - m);  // warps without positions hold m=-inf -> 0
-      l += sm_l[j] * c;
-      a.x += sm_acc[j][lane].x * c;
-      a.y += sm_acc[j][lane].y * c;
+    for (int u = 0; u < U; ++u) {
+      const int p = p0 + u * RPL + sub;
+      if (p < L) {
+        KvVec<TK>::load(kbase + (long long)p * 64, kf[u]);
+        KvVec<TK>::load(vbase + (long long)p * 64, vf[u]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) { kf[u][e] = 0.0f; vf[u][e] = 0.0f; }
+      }
     }
-    const float inv = 1.0f / l;
-    store2(out + (long long)i * d_model + h * 64 + 2 * lane, make_float2(a.x * inv, a.y * inv));
+    float sc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float a = 0.0f;
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) a = fmaf(q[e], kf[u][e], a);
+      sc[u] = a;
+    }
+#pragma unroll
+    for (int o = 1; o < LPR; o <<= 1) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) sc[u] += __shfl_xor_sync(0xffffffffu, sc[u], o);
+    }
+    float mx = m;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (p0 + u * RPL + sub >= L) sc[u] = -INFINITY;
+      mx = fmaxf(mx, sc[u]);
+    }
+    if (mx > -INFINITY) {   // this lane group has seen at least one position
+      const float corr = expf(m - mx);
+      l *= corr;
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) acc[e] *= corr;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const float pr = expf(sc[u] - mx);
+        l += pr;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) acc[e] = fmaf(pr, vf[u][e], acc[e]);
+      }
+      m = mx;
+    }
+  }
+  sm_m[w][lane] = m;
+  sm_l[w][lane] = l;
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) sm_acc[w][lane][e] = acc[e];
+  __syncthreads();
+  if (w == 0 && sub == 0) {
+    // merge the NW * RPL partial states that share this chunk of dims
+    float mm = -INFINITY;
+    for (int j = 0; j < NW; ++j)
+      for (int r = 0; r < RPL; ++r) mm = fmaxf(mm, sm_m[j][r * LPR + ch]);
+    float ll = 0.0f, a[EPL];
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) a[e] = 0.0f;
+    for (int j = 0; j < NW; ++j)
+      for (int r = 0; r < RPL; ++r) {
+        const int src = r * LPR + ch;
+        const float c = expf(sm_m[j][src] - mm);   // empty partials hold m = -inf -> 0
+        ll += sm_l[j][src] * c;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) a[e] = fmaf(sm_acc[j][src][e], c, a[e]);
+      }
+    const float inv = 1.0f / ll;
+    TO* o = out + (long long)i * d_model + h * 64 + ch * EPL;
+#pragma unroll
+    for (int e = 0; e < EPL; e += 2) store2(o + e, make_float2(a[e] * inv, a[e + 1] * inv));
   }
 }
 

@@ -61,8 +61,12 @@ int Engine::init() {
   if (c.precision != PTTS_PRECISION_FP32 && c.precision != PTTS_PRECISION_BF16)
     PTTS_FAIL(PTTS_EINVAL, "unknown precision %d", c.precision);
   PTTS_CUDA_CHECK(cudaSetDevice(c.device));
-  PTTS_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-  PTTS_CUDA_CHECK(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+  // the FlowLM chain (many short dependent kernels) outranks the Mimi branch (few wide kernels): its
+  // CTAs are dispatched first whenever an SM frees up, so the wide SEANet grids do not stall it
+  int prio_lo = 0, prio_hi = 0;
+  PTTS_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, prio_hi));
+  PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&stream2, cudaStreamNonBlocking, prio_lo));
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   if (const char* f = getenv("PTTS_PIPELINE")) use_pipeline = !(f[0] == '0');
