@@ -252,7 +252,7 @@ constexpr int EPI_STAGE_FLOATS = 32 * 36;                     // per warp
 constexpr size_t EPI_SMEM_BYTES = 8 * EPI_STAGE_FLOATS * 4 + BM_TC * sizeof(RowMeta);
 
 template <int BN, typename TO>
-__device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, const TcParams& P, uint32_t taddr, int row0,
+__device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, int M, int N, uint32_t taddr, int row0,
                                               int col0, int q, int half, int lane, uint8_t* scratch) {
   constexpr int CH = BN >= 32 ? 32 : 16;
   constexpr int NCH = BN / CH;
@@ -264,7 +264,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, const TcPa
   if (half == 0) {
     const int rl = q * 32 + lane, r = row0 + rl;
     RowMeta mt{-1, 0, 0};
-    if (r < P.M) {
+    if (r < M) {
       const int ob = r / ep.out_map.rows_per_batch, ot = r - ob * ep.out_map.rows_per_batch;
       if (ot < ep.out_map.valid_rows) {
         mt.out = ob * ep.out_map.batch_stride + (long long)ot * ep.out_map.ld;
@@ -285,7 +285,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, const TcPa
 #pragma unroll 1
   for (int ci = half; ci < NCH; ci += 2) {
     const int c = ci * CH, n0 = col0 + c;
-    if (n0 >= P.N) break;   // uniform
+    if (n0 >= N) break;   // uniform
     {
       float v[CH];
       tmem_ld<CH>(taddr + c, v);   // warp-collective
@@ -565,7 +565,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
       partial_push<BN>(P, taddr, slab, P.cluster, (int)blockIdx.z, q * 32 + lane, half);
     } else if (nkb > 0) {
       if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half);
-      else epilogue_rows<BN, TO>(ep, P, taddr, row0, col0, q, half, lane, tiles);
+      else epilogue_rows<BN, TO>(ep, P.M, P.N, taddr, row0, col0, q, half, lane, tiles);
     }
     tc_fence_before();
     if (warp == 2) TC_TRACE(3);
@@ -577,6 +577,127 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     if (warp >= 2) epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64);
     if (warp == 2) TC_TRACE(6);
   }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Persistent row-major GEMM (Mimi transformer, SEANet convolutions, prefill): one CTA per SM
+// walks a static round-robin list of 128 x BN output tiles.  The smem ring keeps running across
+// tiles, the accumulator is double-buffered in TMEM (2 x BN columns) so the epilogue of tile i
+// overlaps the tcgen05.mma stream of tile i+1, and set-up (barriers, TMEM allocation, tensor-map
+// fetch) is paid once per SM instead of once per tile.  One resident CTA of ~110-180 KB leaves the
+// rest of the SM (shared memory, TMEM columns) to the kernels of the concurrent FlowLM branch.
+struct TcRowsParams {
+  int M, N, num_kb, stages;
+  int tiles_n, n_tiles;
+};
+
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+template <int BN, typename TO>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_tc_rows_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w,
+                    TcRowsParams P, GemmEpilogue ep) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  constexpr uint32_t A_BYTES = BM_TC * 128, B_BYTES = BN * 128, STAGE_BYTES = A_BYTES + B_BYTES;
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* scratch = tiles + (size_t)P.stages * STAGE_BYTES;   // epilogue staging + row metadata
+  __shared__ __align__(8) uint64_t full_bar[MAX_STAGES];
+  __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
+  __shared__ __align__(8) uint64_t tfull_bar[2];
+  __shared__ __align__(8) uint64_t tempty_bar[2];
+  __shared__ uint32_t tmem_base_smem;
+  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_w) : "memory");
+    for (int s = 0; s < P.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  pdl_wait();
+  const uint32_t tmem_base = tmem_base_smem;
+  const uint32_t tiles_a = smem_u32(tiles), full_a = smem_u32(&full_bar[0]), empty_a = smem_u32(&empty_bar[0]);
+  const uint32_t tfull_a = smem_u32(&tfull_bar[0]), tempty_a = smem_u32(&tempty_bar[0]);
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    uint32_t s = 0, ph = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      const int mt = tile / P.tiles_n, nt = tile - mt * P.tiles_n;
+      const int row0 = mt * BM_TC, col0 = nt * BN;
+      for (int kb = 0; kb < P.num_kb; ++kb) {
+        mbar_wait_a(empty_a + 8u * s, ph ^ 1u);
+        if (lane == 0) {
+          const uint32_t st = tiles_a + s * STAGE_BYTES, fb = full_a + 8u * s;
+          mbar_expect_tx_a(fb, STAGE_BYTES);
+          tma_load_2d_a(st + A_BYTES, &tm_w, fb, kb * BK_TC, col0);
+          tma_load_2d_a(st, &tm_a, fb, kb * BK_TC, row0);
+        }
+        __syncwarp();
+        if (++s == (uint32_t)P.stages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM_TC >> 4) << 24);
+    const uint64_t adesc0 = make_sw128_desc(tiles_a), bdesc0 = make_sw128_desc(tiles_a + A_BYTES);
+    uint32_t s = 0, ph = 0, t = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++t) {
+      const uint32_t buf = t & 1u, use = t >> 1;
+      mbar_wait_a(tempty_a + 8u * buf, (use & 1u) ^ 1u);   // epilogue drained this accumulator (first use: passes)
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + buf * BN;
+      for (int kb = 0; kb < P.num_kb; ++kb) {
+        mbar_wait_a(full_a + 8u * s, ph);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint64_t soff = (uint64_t)((s * STAGE_BYTES) >> 4);
+          const uint64_t adesc = adesc0 + soff, bdesc = bdesc0 + soff;
+#pragma unroll
+          for (int k = 0; k < BK_TC / 16; ++k)
+            tc_mma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+          tc_commit_a(empty_a + 8u * s);
+          if (kb == P.num_kb - 1) tc_commit_a(tfull_a + 8u * buf);
+        }
+        __syncwarp();
+        if (++s == (uint32_t)P.stages) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else {
+    // ===== epilogue warps 2..9 =====
+    const int q = warp & 3, half = (warp - 2) >> 2;
+    uint32_t t = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++t) {
+      const uint32_t buf = t & 1u, use = t >> 1;
+      const int mt = tile / P.tiles_n, nt = tile - mt * P.tiles_n;
+      mbar_wait_a(tfull_a + 8u * buf, use & 1u);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
+      asm volatile("bar.sync 1, 256;" ::: "memory");   // previous tile's row metadata no longer in use
+      epilogue_rows<BN, TO>(ep, P.M, P.N, taddr, mt * BM_TC, nt * BN, q, half, lane, scratch);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(tempty_a + 8u * buf);
+    }
+  }
+  tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
@@ -630,6 +751,7 @@ static bool make_map(CUtensorMap* out, const void* base, long long rows, int K, 
 
 constexpr size_t TC_SMEM_LIMIT = 225 * 1024;
 constexpr size_t TC_CORESIDENT_SMEM = 108 * 1024;   // two CTAs per SM
+constexpr size_t TC_ROWS_SMEM = 112 * 1024;         // persistent row-major kernel: leaves ~85 KB per SM to the other branch
 
 template <int BN, bool SWAP, typename TO>
 static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, const TcParams& P, const GemmEpilogue& ep,
@@ -693,6 +815,30 @@ void tc_trace_dump(const char* what) {
             h[8 + i * 4 + 1] - t0, h[8 + i * 4 + 2] - t0);
 }
 
+template <int BN, typename TO>
+static cudaError_t launch_rows(const CUtensorMap& ta, const CUtensorMap& tw, const TcRowsParams& P, const GemmEpilogue& ep,
+                               int grid, bool pdl, cudaStream_t st) {
+  const size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + EPI_SMEM_BYTES + 1024;
+  static bool attr_done = false;
+  auto kern = gemm_tc_rows_kernel<BN, TO>;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_LIMIT + 1024);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(TC_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, ta, tw, P, ep);
+}
+
 static int pick_bn(int n) {
   if (n <= 16) return 16;
   if (n <= 32) return 32;
@@ -747,10 +893,48 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     }
 #undef TC_CASE
   }
+  // row-major: persistent kernel, one CTA per SM over a static tile list.  Tile width from a small
+  // cost model (clock trace): ~0.24 us per k-block of tcgen05.mma issue (independent of N) against
+  // ~0.5 us + 0.3 us per 64 columns of epilogue, which overlap across tiles; ~3 us to start up.
+  const int tiles_m = (p.M + BM_TC - 1) / BM_TC;
+  static const bool old_rows = [] { const char* e = getenv("PTTS_TC_ROWS"); return e && e[0] == 'o'; }();
+  // measured (ncu, B=64): the persistent kernel wins when a tile has >= 8 k-blocks of mainloop to hide its
+  // epilogue behind; thin layers (K <= 384) do better as one tile per CTA with two CTAs per SM
+  if (!old_rows && p.N % 32 == 0 && P.num_kb >= 8) {
+    int bn = pick_bn(p.N);
+    if (bn < 32) bn = 32;
+    double best = 1e30;
+    for (int cand = bn; cand >= 32; cand >>= 1) {
+      const int tiles = tiles_m * ((p.N + cand - 1) / cand);
+      const int per_cta = (tiles + n_sms - 1) / n_sms;
+      const double epi = 0.5 + 0.3 * cand / 64.0, main = 0.24 * P.num_kb;
+      const double t = 3.0 + per_cta * std::max(main, epi) + std::min(main, epi);
+      if (t < best - 1e-9) { best = t; bn = cand; }
+    }
+    TcRowsParams R{};
+    R.M = p.M; R.N = p.N; R.num_kb = P.num_kb;
+    R.tiles_n = (p.N + bn - 1) / bn;
+    R.n_tiles = tiles_m * R.tiles_n;
+    const size_t stage = (size_t)(BM_TC + bn) * 128;
+    const size_t budget = (2 * stage + EPI_SMEM_BYTES <= TC_ROWS_SMEM) ? TC_ROWS_SMEM : TC_SMEM_LIMIT;
+    R.stages = (int)std::max<size_t>(2, std::min<size_t>(6, (budget - EPI_SMEM_BYTES) / stage));
+    if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
+    if (!make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
+    const int grid = std::min(R.n_tiles, n_sms);
+#define TC_CASE(BNV)                                                                  \
+  case BNV:                                                                           \
+    return out_type == 0 ? launch_rows<BNV, float>(ta, tw, R, ep, grid, pdl, st)      \
+                         : launch_rows<BNV, bf16>(ta, tw, R, ep, grid, pdl, st);
+    switch (bn) {
+      TC_CASE(32) TC_CASE(64) TC_CASE(128)
+      default: return out_type == 0 ? launch_rows<256, float>(ta, tw, R, ep, grid, pdl, st)
+                                    : launch_rows<256, bf16>(ta, tw, R, ep, grid, pdl, st);
+    }
+#undef TC_CASE
+  }
   // row-major tile width from a small cost model (measured with the clock trace): a CTA costs
   // ~1.5 us set-up + 0.24 us per k-block (four tcgen05.mma issues + commit, independent of N) +
   // ~2 us epilogue latency + 0.3 us per 64 columns; the grid runs in waves of n_sms CTAs.
-  const int tiles_m = (p.M + BM_TC - 1) / BM_TC;
   int bn = pick_bn(p.N);
   {
     double best = 1e30;
