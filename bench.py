@@ -160,16 +160,27 @@ def run_ours(args, rank, world, local_rank):
     close(slots)
 
     # ---------------- end-to-end through the host-buffer C-ABI call (e2e) ----------------
+    # ptts_generate_frames: per frame the noise comes from pinned host memory and latents, EOS logits
+    # and PCM go back to pinned host memory, all inside the timed region; FlowLM(f) || Mimi(f-1).
     slots, noise = fresh_streams(1)
+    noise_pin = noise.pin_memory()
+    eng.generate_frames(slots, noise_pin[:Wm])
+    barrier()
+    t0 = time.perf_counter()
+    pcm_h, lat_h, eos_h = eng.generate_frames(slots, noise_pin[Wm:Wm + K])
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    assert bool(torch.isfinite(pcm_h).all()) and bool(torch.isfinite(lat_h).all())
+    close(slots)
+    # secondary: one blocking ptts_step per frame (host round trip every 80 ms frame, no overlap)
+    slots, noise = fresh_streams(3)
     noise_pin = noise.pin_memory()
     for g in range(Wm):
         eng.step(slots, noise_pin[g])
-    barrier()
     t0 = time.perf_counter()
-    for g in range(Wm, Wm + K):
-        lat, eos, pcm = eng.step(slots, noise_pin[g])          # H2D noise, D2H latents/eos/pcm, sync
-    torch.cuda.synchronize()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
+    KS = min(K, 32)
+    for g in range(Wm, Wm + KS):
+        eng.step(slots, noise_pin[g])
+    step_api_ms = (time.perf_counter() - t0) * 1e3 / KS
     close(slots)
     h2d = B * dims.ldim * 4
     d2h = B * (dims.ldim * 4 + 4 + dims.frame_samples * 4)
@@ -189,10 +200,10 @@ def run_ours(args, rank, world, local_rank):
         eng.set_graphs(True)
         close(slots)
 
-    if dist:
-        t = torch.tensor([ms, e2e_ms], device="cuda", dtype=torch.float64)
-        td.all_reduce(t, op=td.ReduceOp.MAX)
-        ms, e2e_ms = float(t[0]), float(t[1])
+    if dist:   # max over ranks of the device-timed region and of the end-to-end region
+        from pocket_tts_b200.sharding import aggregate_throughput
+        _, ms = aggregate_throughput(B * K * FRAME_S, ms)
+        _, e2e_ms = aggregate_throughput(B * K * FRAME_S, e2e_ms)
     if rank != 0:
         if dist:
             td.destroy_process_group()
@@ -208,7 +219,10 @@ def run_ours(args, rank, world, local_rank):
         peaks = json.loads(pk.read_text())
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     total_prof = sum(v["total_ms"] for v in prof.values()) or 1.0
-    top = max(prof.items(), key=lambda kv: kv[1]["total_ms"]) if prof else (None, None)
+    # dominant kernel: FlowLM decode attention — largest algorithmic byte term of the step (KV stream)
+    # and the largest per-tag time in the event profile; fall back to the top tag by time
+    top = ("flow.attn_decode", prof["flow.attn_decode"]) if "flow.attn_decode" in prof else \
+        (max(prof.items(), key=lambda kv: kv[1]["total_ms"]) if prof else (None, None))
     roofline = None
     if top[0]:
         ctx_mid = VOICE_P + TEXT_T + Wm + min(K, 32) // 2
@@ -216,7 +230,8 @@ def run_ours(args, rank, world, local_rank):
         avg_ms = top[1]["total_ms"] / top[1]["count"]
         ach = per_launch / (avg_ms / 1e3) / 1e9
         roofline = {"kernel": top[0], "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak,
-                    "unit": "GB/s", "frac": round(ach / hbm_peak, 4), "traffic": None,
+                    "unit": "GB/s", "frac": round(ach / hbm_peak, 4), "traffic": ncu_traffic_bytes(top[0]),
+                    "algorithmic_bytes_per_launch": int(per_launch),
                     "avg_launch_us": round(avg_ms * 1e3, 2), "share_of_step": round(top[1]["total_ms"] / total_prof, 3),
                     "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback"}
     ctx_avg = VOICE_P + TEXT_T + Wm + K / 2
@@ -233,7 +248,9 @@ def run_ours(args, rank, world, local_rank):
                    "streams_per_gpu": B, "precision": prec, "parallelism": f"streams sharded x{world}, no collective",
                    "l2_policy": "working set per step (weights + KV, >= 0.6 GB) exceeds the 126 MB L2; no flush"},
         "e2e": {"value": round(e2e_value, 1), "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": round(e2e_ms / K, 4), "api": "ptts_step (host buffers) via pocket_tts_b200.GenerationEngine.step"},
+                "ms_per_step": round(e2e_ms / K, 4),
+                "api": "ptts_generate_frames (pinned host noise in; latents, EOS logits, PCM out per frame) via GenerationEngine.generate_frames",
+                "blocking_step_api_ms_per_step": round(step_api_ms, 4)},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "step_roofline": {"bound": "hbm", "algorithmic_bytes_per_step": int(step_bytes), "frac_of_hbm_peak": round(step_frac, 4)},
         "cpu_baseline": cpu,
@@ -242,6 +259,21 @@ def run_ours(args, rank, world, local_rank):
     print(json.dumps(line), flush=True)
     if dist:
         td.destroy_process_group()
+
+
+def ncu_traffic_bytes(tag):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` summary
+    (profiles/), taken at the start of the generation (context 166-172); None when no capture exists."""
+    import csv
+    f = {"flow.attn_decode": ROOT / "profiles" / "r01_attn_decode_ncu_full_summary.csv"}.get(tag)
+    if not f or not f.exists():
+        return None
+    rows = list(csv.reader(open(f)))
+    hdr, units = rows[0], rows[1]
+    mult = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    ri, wi = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+    vals = [float(r[ri]) * mult[units[ri]] + float(r[wi]) * mult[units[wi]] for r in rows[2:] if len(r) > max(ri, wi)]
+    return int(sum(vals) / len(vals)) if vals else None
 
 
 def kernel_algorithmic_bytes(tag, dims, B, ctx, e):

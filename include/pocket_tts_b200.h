@@ -128,6 +128,18 @@ int ptts_run_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_f
                     const float* noise_dev, int32_t lsd_steps, float* out_pcm_dev,
                     float* out_latents_dev);
 
+/* Streaming generation of n_frames frames for n streams with caller buffers that may live on the
+ * host (pinned memory makes the copies asynchronous) or on the device: the body of
+ * TTSModel._autoregressive_generation + the decoder thread (tts_model.py:651-658,745-779) as one
+ * call.  Per frame: noise_any[f] is copied in, the FlowLM step + flow head of frame f run
+ * concurrently with the Mimi decode of frame f-1 (two branches of one CUDA graph), and
+ * latents / EOS logits of frame f and the PCM of frame f-1 are copied out.  Layouts:
+ * noise [n_frames, n, ldim], out_pcm [n, n_frames*1920], out_latents [n_frames, n, ldim],
+ * out_eos_logit [n_frames, n]; outputs may be NULL.  Returns after everything has landed. */
+int ptts_generate_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames,
+                         const float* noise_any, int32_t lsd_steps, float* out_pcm_any,
+                         float* out_latents_any, float* out_eos_logit_any);
+
 int ptts_synchronize(ptts_engine* e);
 /* Number of engine kernels launched (or replayed through a graph) since creation. */
 int64_t ptts_launch_count(ptts_engine* e);

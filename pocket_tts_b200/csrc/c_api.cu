@@ -124,6 +124,14 @@ int ptts_run_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_f
   return e->impl->run_frames(n, slots, n_frames, noise_dev, lsd_steps, out_pcm_dev, out_latents_dev);
   API_END
 }
+
+int ptts_generate_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames, const float* noise_any,
+                         int32_t lsd_steps, float* out_pcm_any, float* out_latents_any, float* out_eos_logit_any) {
+  API_BEGIN NEED(e)
+  return e->impl->run_frames(n, slots, n_frames, noise_any, lsd_steps, out_pcm_any, out_latents_any, out_eos_logit_any,
+                             true);
+  API_END
+}
 int ptts_synchronize(ptts_engine* e) {
   API_BEGIN NEED(e)
   cudaError_t ce = cudaStreamSynchronize(e->impl->stream);

@@ -86,8 +86,8 @@ class Engine {
   int step(int n, const int* slots, const float* noise_any, int lsd, int audio, float* out_lat,
            float* out_eos, float* out_pcm);
   int mimi_decode(int n, const int* slots, const float* latents_any, float* out_pcm);
-  int run_frames(int n, const int* slots, int n_frames, const float* noise_dev, int lsd,
-                 float* out_pcm_dev, float* out_lat_dev);
+  int run_frames(int n, const int* slots, int n_frames, const float* noise_any, int lsd,
+                 float* out_pcm_any, float* out_lat_any, float* out_eos_any = nullptr, bool sync = false);
   int debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out);
   int debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_batch, int valid_rows,
                  const float* a_host, long long a_elems, const float* w_host, float* out_host);

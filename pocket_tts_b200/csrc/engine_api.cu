@@ -309,7 +309,7 @@ int Engine::mimi_decode(int n, const int* slots, const float* latents_any, float
 }
 
 int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise_dev, int lsd,
-                       float* out_pcm_dev, float* out_lat_dev) {
+                       float* out_pcm_dev, float* out_lat_dev, float* out_eos, bool sync) {
   NEED_READY();
   int rc;
   if ((rc = check_slots(n, slots, true)) != PTTS_OK) return rc;
@@ -326,12 +326,12 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
   auto copy_pcm = [&](int f) -> int {
     if (out_pcm_dev)
       PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_dev + (size_t)f * fs, (size_t)n_frames * fs * sizeof(float), pcm,
-                                        fs * sizeof(float), fs * sizeof(float), n, cudaMemcpyDeviceToDevice, stream));
+                                        fs * sizeof(float), fs * sizeof(float), n, cudaMemcpyDefault, stream));
     return PTTS_OK;
   };
   for (int f = 0; f < n_frames; ++f) {
     PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_dev + (size_t)f * n * Ld, (size_t)n * Ld * sizeof(float),
-                                    cudaMemcpyDeviceToDevice, stream));
+                                    cudaMemcpyDefault, stream));
     if (piped) {
       // FlowLM(f) || Mimi(f-1); the PCM of frame f-1 is complete when this graph has joined
       if ((rc = frame_pipelined(n, lsd, f & 1, true, f > 0)) != PTTS_OK) return rc;
@@ -343,7 +343,9 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
     }
     if (out_lat_dev)
       PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat_dev + (size_t)f * n * Ld, x_lat, (size_t)n * Ld * sizeof(float),
-                                      cudaMemcpyDeviceToDevice, stream));
+                                      cudaMemcpyDefault, stream));
+    if (out_eos)
+      PTTS_CUDA_CHECK(cudaMemcpyAsync(out_eos + (size_t)f * n, eos_logit, (size_t)n * sizeof(float), cudaMemcpyDefault, stream));
   }
   if (piped) {   // drain: Mimi decode of the last frame
     if ((rc = frame_pipelined(n, lsd, n_frames & 1, false, true)) != PTTS_OK) return rc;
@@ -353,6 +355,7 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
     host_offsets[slots[i]] += n_frames;
     host_mimi_offsets[slots[i]] += n_frames * cfg.upsample_stride;
   }
+  if (sync) PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
   return PTTS_OK;
 }
 
