@@ -364,6 +364,8 @@ attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   uint32_t* Vs = Ks + maxw * LD;
   float* Ps = reinterpret_cast<float*>(Vs + maxw * LD);   // [TQ][maxw]
   float* Qs = Ps + TQ * maxw;                              // [TQ][64]
+  pdl_launch_dependents();
+  pdl_wait();                                              // qkv comes from the previous kernel
   const int h = blockIdx.x, i = blockIdx.y;
   const int slot = slot_ids[i];
   const int off = offsets[slot];
