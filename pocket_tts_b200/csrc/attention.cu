@@ -352,13 +352,27 @@ __device__ __forceinline__ float2 kv_word_pair(const uint32_t* row, int c, float
   return make_float2(__uint_as_float(row[2 * c]), __uint_as_float(row[2 * c + 1]));
 }
 
+template <typename TK> __device__ __forceinline__ void kv_smem_store(uint32_t* row, int lane, float2 v);
+template <> __device__ __forceinline__ void kv_smem_store<bf16>(uint32_t* row, int lane, float2 v) {
+  const __nv_bfloat162 b = __floats2bfloat162_rn(v.x, v.y);
+  row[lane] = *reinterpret_cast<const uint32_t*>(&b);
+}
+template <> __device__ __forceinline__ void kv_smem_store<float>(uint32_t* row, int lane, float2 v) {
+  row[2 * lane] = __float_as_uint(v.x);
+  row[2 * lane + 1] = __float_as_uint(v.y);
+}
+
+// grid (H, n, frames): block z owns the T tokens of frame z of this pass (a pass appends frames * T tokens
+// per stream).  Keys / values of positions before the pass come from the ring; those of this pass (own
+// frame and earlier frames) are rotated straight from the packed projection and rounded to the cache
+// type, so no block depends on another block's ring writes; a block appends only its own T tokens.
 template <typename TK, typename TO>
 __global__ void __launch_bounds__(256)
 attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs, const int* __restrict__ offsets,
                    const int* __restrict__ slot_ids, KvGeom g, int layer, int context, int T, int maxw,
                    TO* __restrict__ out) {
   constexpr int NW = 8, TQ = 16, NKL = 9;   // warps, max queries, max keys per lane (maxw <= 288)
-  constexpr int LD = KvWords<TK>::LD, ROWW = KvWords<TK>::ROW;
+  constexpr int LD = KvWords<TK>::LD;
   extern __shared__ __align__(16) uint32_t smw[];
   uint32_t* Ks = smw;
   uint32_t* Vs = Ks + maxw * LD;
@@ -366,41 +380,49 @@ attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   float* Qs = Ps + TQ * maxw;                              // [TQ][64]
   pdl_launch_dependents();
   pdl_wait();                                              // qkv comes from the previous kernel
-  const int h = blockIdx.x, i = blockIdx.y;
+  const int h = blockIdx.x, i = blockIdx.y, z = blockIdx.z, frames = gridDim.z;
   const int slot = slot_ids[i];
-  const int off = offsets[slot];
-  const int r0 = i * T;
+  const int off0 = offsets[slot];                          // position of the pass's first token
+  const int off = off0 + z * T;                            // position of this block's first token
+  const int r_pass = i * frames * T;                       // first projection row of the stream's pass
+  const int r0 = r_pass + z * T;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int d_model = g.H * 64;
   const float fr = freqs[lane];
 
-  // phase 1: RoPE, append rotated k / v to the ring, keep rotated q in shared memory
+  // phase 1: rotated q of the own tokens
   for (int t = w; t < T; t += NW) {
     const float* row = qkv + (long long)(r0 + t) * 3 * d_model + h * 64 + 2 * lane;
-    const float pos = (float)(off + t);
-    const float2 q = rope_pair(load2(row), pos, fr);
+    const float2 q = rope_pair(load2(row), (float)(off + t), fr);
     Qs[t * 64 + 2 * lane] = q.x;
     Qs[t * 64 + 2 * lane + 1] = q.y;
-    const float2 k = rope_pair(load2(row + d_model), pos, fr);
-    const float2 v = load2(row + 2 * d_model);
-    store2(kv_row<TK>(g, layer, slot, 0, h, off + t) + 2 * lane, k);
-    store2(kv_row<TK>(g, layer, slot, 1, h, off + t) + 2 * lane, v);
   }
-  __syncthreads();
-
-  // phase 2: stage the visible window [lo, off+T-1] (including the rows just written)
+  // phase 2: stage the visible window [lo, off+T-1]
   const int lo = max(0, off - context + 1);
   const int W = off + T - lo;
   for (int j = w; j < W; j += NW) {
-    const TK* kr = kv_row<TK>(g, layer, slot, 0, h, lo + j);
-    const TK* vr = kv_row<TK>(g, layer, slot, 1, h, lo + j);
-    if (sizeof(TK) == 2) {
-      Ks[j * LD + lane] = reinterpret_cast<const uint32_t*>(kr)[lane];
-      Vs[j * LD + lane] = reinterpret_cast<const uint32_t*>(vr)[lane];
+    const int pj = lo + j;
+    if (pj < off0) {
+      const TK* kr = kv_row<TK>(g, layer, slot, 0, h, pj);
+      const TK* vr = kv_row<TK>(g, layer, slot, 1, h, pj);
+      if (sizeof(TK) == 2) {
+        Ks[j * LD + lane] = reinterpret_cast<const uint32_t*>(kr)[lane];
+        Vs[j * LD + lane] = reinterpret_cast<const uint32_t*>(vr)[lane];
+      } else {
+        const uint2 kk = reinterpret_cast<const uint2*>(kr)[lane], vv = reinterpret_cast<const uint2*>(vr)[lane];
+        Ks[j * LD + 2 * lane] = kk.x; Ks[j * LD + 2 * lane + 1] = kk.y;
+        Vs[j * LD + 2 * lane] = vv.x; Vs[j * LD + 2 * lane + 1] = vv.y;
+      }
     } else {
-      const uint2 kk = reinterpret_cast<const uint2*>(kr)[lane], vv = reinterpret_cast<const uint2*>(vr)[lane];
-      Ks[j * LD + 2 * lane] = kk.x; Ks[j * LD + 2 * lane + 1] = kk.y;
-      Vs[j * LD + 2 * lane] = vv.x; Vs[j * LD + 2 * lane + 1] = vv.y;
+      const float* row = qkv + (long long)(r_pass + (pj - off0)) * 3 * d_model + h * 64 + 2 * lane;
+      const float2 k = rope_pair(load2(row + d_model), (float)pj, fr);
+      const float2 v = load2(row + 2 * d_model);
+      kv_smem_store<TK>(Ks + j * LD, lane, k);
+      kv_smem_store<TK>(Vs + j * LD, lane, v);
+      if (pj >= off) {   // own token: append to the ring
+        store2(kv_row<TK>(g, layer, slot, 0, h, pj) + 2 * lane, k);
+        store2(kv_row<TK>(g, layer, slot, 1, h, pj) + 2 * lane, v);
+      }
     }
   }
   __syncthreads();
@@ -463,11 +485,12 @@ attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
 
 cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets, const int* slot_ids,
                                KvGeom kv, int layer, int context, int T, void* out, int out_type, int n,
-                               cudaStream_t st) {
-  if (kv.D != 64 || !kv.ring || (kv.cap & (kv.cap - 1)) || T < 1 || T > 16) return cudaErrorInvalidValue;
+                               cudaStream_t st, int frames) {
+  if (kv.D != 64 || !kv.ring || (kv.cap & (kv.cap - 1)) || T < 1 || T > 16 || frames < 1) return cudaErrorInvalidValue;
+  if (context + frames * T > kv.cap) return cudaErrorInvalidValue;   // a pass must not wrap onto keys it still reads
   const int maxw = ((context + T - 1 + 7) / 8) * 8;
   if (maxw > 288 || maxw > kv.cap) return cudaErrorInvalidValue;
-  dim3 grid(kv.H, n);
+  dim3 grid(kv.H, n, frames);
   const int ld = kv.type == 1 ? KvWords<bf16>::LD : KvWords<float>::LD;
   const size_t smem = ((size_t)2 * maxw * ld + (size_t)16 * maxw + 16 * 64) * 4;
 #define WIN_CASE(TKT, TOT)                                                                                        \

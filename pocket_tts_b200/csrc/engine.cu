@@ -1,6 +1,7 @@
 // Engine implementation, part 1: memory, weight loading and re-layout.
 #include "engine.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -15,6 +16,11 @@ void set_error_cuda(cudaError_t e, const char* expr, const char* file, int line)
   snprintf(buf, sizeof buf, "CUDA error %s (%s) at %s:%d: %s", cudaGetErrorName(e), cudaGetErrorString(e),
            file, line, expr);
   g_err = buf;
+  if (const unsigned* d = mega_diag_words())
+    if (d[0]) {
+      snprintf(buf, sizeof buf, " [step kernel: wait 0x%x timed out in CTA %u thread %u]", d[0], d[1], d[2]);
+      g_err += buf;
+    }
 }
 const char* get_error() { return g_err.c_str(); }
 void prefer_max_smem_carveout(const void* kern) {
@@ -36,8 +42,14 @@ Engine::~Engine() {
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (void* p : allocs) cudaFree(p);
   if (h_pinned) cudaFreeHost(h_pinned);
+  if (h_mega_diag) cudaFreeHost(h_mega_diag);
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
+  for (int k = 0; k < 2; ++k) {
+    for (cudaEvent_t e : {ev_lat[k], ev_mimi[k], ev_copied_lat[k], ev_copied_pcm[k]})
+      if (e) cudaEventDestroy(e);
+  }
+  if (copy_stream) cudaStreamDestroy(copy_stream);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
 }
@@ -66,12 +78,33 @@ int Engine::init() {
   int prio_lo = 0, prio_hi = 0;
   PTTS_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
   PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, prio_hi));
-  PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&stream2, cudaStreamNonBlocking, prio_lo));
+  const bool mimi_hi = [] { const char* e = getenv("PTTS_MIMI_PRIO"); return e && e[0] == '1'; }();
+  PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&stream2, cudaStreamNonBlocking, mimi_hi ? prio_hi : prio_lo));
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   if (const char* f = getenv("PTTS_PIPELINE")) use_pipeline = !(f[0] == '0');
+  if (const char* f = getenv("PTTS_LOOP")) loop_fork = f[0] == 'f';
   PTTS_CUDA_CHECK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, c.device));
+  n_sms_flow = n_sms_mimi = n_sms;
+  {  // PTTS_FLOW_SMS=k: FlowLM chain on k SMs, Mimi branch on the others (green contexts); 0 / unset: shared SMs
+    const char* e = getenv("PTTS_FLOW_SMS");
+    const int want = e ? atoi(e) : 0;
+    if (want >= 8 && want <= n_sms - 8) {
+      cudaStream_t a = nullptr, b = nullptr;
+      int na = 0, nb = 0;
+      if (make_sm_partition(c.device, want, prio_hi, prio_lo, &a, &b, &na, &nb)) {
+        cudaStreamDestroy(stream); cudaStreamDestroy(stream2);
+        stream = a; stream2 = b; n_sms_flow = na; n_sms_mimi = nb; n_sms = na; partitioned = true;
+      }
+    }
+  }
   if (const char* f = getenv("PTTS_FORCE_SIMT")) use_tc = !(f[0] == '1');
+  if (const char* f = getenv("PTTS_MIMI_GROUP")) mimi_gmax = std::max(1, std::min(8, atoi(f)));
+  PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&copy_stream, cudaStreamNonBlocking, prio_lo));
+  for (int k = 0; k < 2; ++k) {
+    for (cudaEvent_t* e : {&ev_lat[k], &ev_mimi[k], &ev_copied_lat[k], &ev_copied_pcm[k]})
+      PTTS_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+  }
   act_type = c.precision == PTTS_PRECISION_BF16 ? 1 : 0;
   act_size = act_type ? 2 : 4;
   const int S = c.max_streams;
@@ -112,8 +145,12 @@ int Engine::init() {
   noise_buf = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
   lat_in = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
   x_lat = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
-  lat_ring[0] = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
-  lat_ring[1] = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);
+  const int GM = mimi_gmax;
+  for (int k = 0; k < 2; ++k) {
+    lat_ring[k] = dmalloc<float>(allocs, (size_t)GM * S * c.ldim, stream);
+    eos_grp[k] = dmalloc<float>(allocs, (size_t)GM * S, stream);
+  }
+  noise_grp = dmalloc<float>(allocs, (size_t)GM * S * c.ldim, stream);
   c_cond = act_alloc((size_t)S * D);
   cemb = dmalloc<float>(allocs, (size_t)S * F, stream);
   sy = act_alloc((size_t)S * F);
@@ -121,11 +158,11 @@ int Engine::init() {
   u = dmalloc<float>(allocs, (size_t)S * F, stream);
   g = act_alloc((size_t)S * F);
   g1 = act_alloc((size_t)S * F);
-  xm = dmalloc<float>(allocs, (size_t)S * U * Md, stream);
-  mqkv = dmalloc<float>(allocs, (size_t)S * U * 3 * Md, stream);
-  m_ln = act_alloc((size_t)S * U * Md);
-  m_attn = act_alloc((size_t)S * U * Md);
-  m_mid = act_alloc((size_t)S * U * c.mimi_ffn);
+  xm = dmalloc<float>(allocs, (size_t)S * GM * U * Md, stream);
+  mqkv = dmalloc<float>(allocs, (size_t)S * GM * U * 3 * Md, stream);
+  m_ln = act_alloc((size_t)S * GM * U * Md);
+  m_attn = act_alloc((size_t)S * GM * U * Md);
+  m_mid = act_alloc((size_t)S * GM * U * c.mimi_ffn);
   if (!h || !qkv || !a_ln || !attn_o || !mid || !mod || !xm || !mqkv || !m_ln || !m_attn || !m_mid)
     PTTS_FAIL(PTTS_ECUDA, "out of device memory for activations");
 
@@ -141,23 +178,27 @@ int Engine::init() {
     hist_state[hist_tab.count] = hd.state;
     hist_tab.count++;
   };
-  b_conv0 = act_alloc((size_t)S * (c.kernel - 1 + T) * C);
+  // conv chain buffers hold up to GM frames per stream; hist_tab records the single-frame geometry
+  b_conv0 = act_alloc((size_t)S * (c.kernel - 1 + GM * T) * C);
   add_hist(b_conv0, c.kernel - 1, T, C);
   for (int i = 0; i < 3; ++i) {
     const int r = c.ratios[i], T2 = T * r, C2 = C / 2, hc = C2 / 2;
-    b_tr[i] = act_alloc((size_t)S * (1 + T) * C);
+    b_tr[i] = act_alloc((size_t)S * (1 + GM * T) * C);
     add_hist(b_tr[i], 1, T, C);
-    b_raw[i] = act_alloc((size_t)S * T2 * C2);
-    b_res[i] = act_alloc((size_t)S * (c.res_kernel - 1 + T2) * C2);
+    b_raw[i] = act_alloc((size_t)S * GM * T2 * C2);
+    b_res[i] = act_alloc((size_t)S * (c.res_kernel - 1 + GM * T2) * C2);
     add_hist(b_res[i], c.res_kernel - 1, T2, C2);
-    b_hid[i] = act_alloc((size_t)S * T2 * hid_width(hc));
+    b_hid[i] = act_alloc((size_t)S * GM * T2 * hid_width(hc));
     T = T2; C = C2;
   }
-  b_last = act_alloc((size_t)S * (c.last_kernel - 1 + T) * C);
+  b_last = act_alloc((size_t)S * (c.last_kernel - 1 + GM * T) * C);
   add_hist(b_last, c.last_kernel - 1, T, C);
-  pcm = dmalloc<float>(allocs, (size_t)S * T, stream);
+  pcm = dmalloc<float>(allocs, (size_t)S * GM * T, stream);
+  pcm_ring[0] = dmalloc<float>(allocs, (size_t)S * GM * T, stream);
+  pcm_ring[1] = dmalloc<float>(allocs, (size_t)S * GM * T, stream);
   if (!b_last || !pcm) PTTS_FAIL(PTTS_ECUDA, "out of device memory for conv buffers");
   PTTS_CUDA_CHECK(cudaMallocHost(&h_pinned, (size_t)S * 4 * sizeof(int) + 64));
+  { int rc = mega_init(); if (rc != PTTS_OK) return rc; }
   PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
   return PTTS_OK;
 }

@@ -5,11 +5,13 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <functional>
 #include <map>
 #include <string>
 #include <vector>
 
 #include "../../include/pocket_tts_b200.h"
+#include "flow_mega.h"
 #include "gemm.cuh"
 #include "kernels.cuh"
 
@@ -48,6 +50,15 @@ struct ConvStageW {
   Mat c3;  float* c3_b;      // [h, 3*C2]
   Mat c1;  float* c1_b;      // [C2, h]
 };
+
+struct MegaPlan {            // phase program of the persistent FlowLM step kernel for one lsd_steps value
+  CUtensorMap* d_maps = nullptr;
+  MegaPhase* d_phases = nullptr;
+  int n_phases = 0;
+};
+const unsigned* mega_diag_words();
+bool make_sm_partition(int device, int flow_sms, int prio_flow, int prio_mimi, cudaStream_t* s_flow, cudaStream_t* s_mimi,
+                       int* n_flow, int* n_mimi);
 
 struct GraphKey {
   int n, lsd, audio;
@@ -99,10 +110,13 @@ class Engine {
   cudaStream_t stream2 = nullptr;          // Mimi branch of the pipelined frame
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   bool use_pipeline = true;                // PTTS_PIPELINE=0 disables
+  bool loop_fork = false;                  // PTTS_LOOP=fork: one two-branch graph per group instead of per-frame FlowLM graphs + per-group Mimi graphs
   long long launches = 0;
   bool use_graphs = true;
   bool use_tc = true;   // bf16 mode: tcgen05 GEMMs (PTTS_FORCE_SIMT=1 disables)
-  int n_sms = 148;
+  int n_sms = 148;                         // SMs the kernels of the current branch may assume (swapped with the stream)
+  int n_sms_flow = 148, n_sms_mimi = 148;  // per branch; differ when the SMs are partitioned (PTTS_FLOW_SMS)
+  bool partitioned = false;
 
  private:
   // ---- helpers
@@ -118,16 +132,31 @@ class Engine {
   void prof_end();
   int transformer_layer_common(const LayerW& L, float* h, int rows, int d, int ffn, void* a,
                                float* qkv, void* ao, void* mid, bool mimi, int li, int n);
-  int flow_sequence(int n, int lsd);
-  int mimi_sequence(int n, const float* latents);
+  int flow_sequence(int n, int lsd, const float* noise = nullptr, float* eos_out = nullptr);
+  // persistent single-launch form of flow_sequence (bf16 mode, <= 128 streams): engine_mega.cu
+  int mega_init();
+  bool mega_eligible(int n) const;
+  int mega_plan(int lsd, MegaPlan** out);
+  int flow_sequence_mega(int n, int lsd, const float* noise, float* eos_out);
+  int mimi_sequence(int n, const float* latents, int frames = 1, float* pcm_out = nullptr);
   int frame(int n, int lsd, int audio);  // eager or graph
   // FlowLM + head of the current frame on `stream` in parallel with the Mimi decode of the previous
   // frame's latents on `stream2` (two branches of one graph), like the reference's decoder thread
   // (tts_model.py:651-658): the Mimi chain never feeds back into the FlowLM chain.
-  int frame_pipelined(int n, int lsd, int parity, bool do_flow, bool do_mimi);
+  int launch_captured(const GraphKey& key, cudaStream_t on, const std::function<int()>& body);
+  int flow_graph(int n, int lsd, int par, int j);
+  int mimi_graph(int n, int g, int par);
+  int group_graph(int n, int lsd, int parity, int g_flow, int g_mimi);
   void* act_alloc(size_t elems);
   // ResBlock hidden width as stored (bf16 mode pads to a multiple of 64 channels)
   int hid_width(int hc) const { return act_type == 1 ? ((hc + 63) / 64) * 64 : hc; }
+
+  bool use_mega = false;                   // PTTS_MEGA=1 selects the persistent step kernel (experimental: see DESIGN.md)
+  int mega_ctas = 128, mega_stages = 6, mega_rows_pad = 64;
+  unsigned *d_mega_sync = nullptr, *h_mega_diag = nullptr, *d_mega_diag = nullptr;
+  float* mega_part = nullptr;
+  unsigned long long* d_mega_trace = nullptr;
+  std::map<int, MegaPlan> mega_plans;
 
   bool ready = false;
   int act_type = 0;  // 0 fp32, 1 bf16
@@ -183,7 +212,13 @@ class Engine {
   std::map<GraphKey, GraphEntry> graphs;
   std::vector<int> cur_slots;
   float* h_pinned = nullptr;
-  float* lat_ring[2] = {nullptr, nullptr};   // latents handed from the FlowLM branch to the Mimi branch
+  float* lat_ring[2] = {nullptr, nullptr};   // latents [mimi_gmax][S][ldim] handed from the FlowLM branch to the Mimi branch
+  float* pcm_ring[2] = {nullptr, nullptr};   // PCM [S][mimi_gmax * 1920] of the group decoded by the Mimi branch
+  float* noise_grp = nullptr;                // [mimi_gmax][S][ldim]
+  float* eos_grp[2] = {nullptr, nullptr};    // [mimi_gmax][S]
+  int mimi_gmax = 4;                         // frames per Mimi pass in the pipelined loop (PTTS_MIMI_GROUP)
+  cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph
+  cudaEvent_t ev_lat[2] = {}, ev_mimi[2] = {}, ev_copied_lat[2] = {}, ev_copied_pcm[2] = {};
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)
   std::map<std::string, std::pair<const void*, std::pair<int, long long>>> debug_bufs;  // name -> (ptr,(type,elems per row unit))
 };

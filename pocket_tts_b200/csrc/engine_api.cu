@@ -3,7 +3,9 @@
 
 #include <cmath>
 #include <cstring>
+#include <algorithm>
 #include <cstdlib>
+#include <functional>
 
 namespace ptts {
 
@@ -189,6 +191,10 @@ int Engine::prefill(int n, const int* slots, const int* lens, const float* embed
 // one frame for the streams in d_slot_ids with noise in noise_buf; graph-replayed when enabled
 int Engine::frame(int n, int lsd, int audio) {
   int rc;
+  if (mega_eligible(n)) {   // the phase program is built (cudaMalloc / cudaMemcpy) outside stream capture
+    MegaPlan* plan = nullptr;
+    if ((rc = mega_plan(lsd, &plan)) != PTTS_OK) return rc;
+  }
   if (!use_graphs) {
     if ((rc = flow_sequence(n, lsd)) != PTTS_OK) return rc;
     if (audio && (rc = mimi_sequence(n, x_lat)) != PTTS_OK) return rc;
@@ -217,41 +223,20 @@ int Engine::frame(int n, int lsd, int audio) {
   return PTTS_OK;
 }
 
-int Engine::frame_pipelined(int n, int lsd, int parity, bool do_flow, bool do_mimi) {
-  auto body = [&]() -> int {
-    int rc = PTTS_OK;
-    if (do_mimi && do_flow) {
-      PTTS_CUDA_CHECK(cudaEventRecord(ev_fork, stream));
-      PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_fork, 0));
-    }
-    if (do_flow) {
-      commit_out = lat_ring[parity];
-      rc = flow_sequence(n, lsd);
-      commit_out = nullptr;
-      if (rc != PTTS_OK) return rc;
-    }
-    if (do_mimi) {
-      cudaStream_t main_stream = stream;
-      if (do_flow) stream = stream2;           // the launchers read the member
-      rc = mimi_sequence(n, lat_ring[parity ^ 1]);
-      stream = main_stream;
-      if (rc != PTTS_OK) return rc;
-      if (do_flow) {
-        PTTS_CUDA_CHECK(cudaEventRecord(ev_join, stream2));
-        PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_join, 0));
-      }
-    }
-    return PTTS_OK;
-  };
+// Graphs of the pipelined loop.  Measured on B200: a CUDA graph's kernel nodes are issued at ~3.5 us per node by
+// one front end shared by all streams, the issue of a graph overlaps the execution of the previous launch only when
+// that is a DIFFERENT executable graph, and graphs of more than ~110 nodes lose that overlap.  So the loop launches
+// one ~70-node FlowLM graph per frame (executables alternate by frame slot and group parity) and one Mimi graph per
+// group of frames, ordered with events instead of intra-graph forks.
+int Engine::launch_captured(const GraphKey& key, cudaStream_t on, const std::function<int()>& body) {
   if (!use_graphs) return body();
-  GraphKey key{n, lsd, 1, 8 + parity * 4 + (do_flow ? 2 : 0) + (do_mimi ? 1 : 0)};
   auto it = graphs.find(key);
   if (it == graphs.end()) {
     const long long before = launches;
     cudaGraph_t graph = nullptr;
-    PTTS_CUDA_CHECK(cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal));
+    PTTS_CUDA_CHECK(cudaStreamBeginCapture(on, cudaStreamCaptureModeThreadLocal));
     int rc = body();
-    cudaError_t ce = cudaStreamEndCapture(stream, &graph);
+    cudaError_t ce = cudaStreamEndCapture(on, &graph);
     if (rc != PTTS_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
     PTTS_CUDA_CHECK(ce);
     GraphEntry ent;
@@ -261,9 +246,76 @@ int Engine::frame_pipelined(int n, int lsd, int parity, bool do_flow, bool do_mi
     cudaGraphDestroy(graph);
     it = graphs.emplace(key, ent).first;
   }
-  PTTS_CUDA_CHECK(cudaGraphLaunch(it->second.exec, stream));
+  PTTS_CUDA_CHECK(cudaGraphLaunch(it->second.exec, on));
   launches += it->second.kernels;
   return PTTS_OK;
+}
+
+// Alternative group form (PTTS_LOOP=fork): ONE graph with two branches per group — `g_flow` FlowLM frames in
+// sequence on `stream` beside the Mimi pass over the previous group's `g_mimi` latents on `stream2`.
+int Engine::group_graph(int n, int lsd, int parity, int g_flow, int g_mimi) {
+  if (g_flow > 0 && mega_eligible(n)) {
+    MegaPlan* plan = nullptr;
+    const int prc = mega_plan(lsd, &plan);
+    if (prc != PTTS_OK) return prc;
+  }
+  const size_t fl = (size_t)n * cfg.ldim;
+  return launch_captured(GraphKey{n, lsd, 1, 1000 + parity * 100 + g_flow * 10 + g_mimi}, stream, [&]() -> int {
+    int rc = PTTS_OK;
+    const bool both = g_flow > 0 && g_mimi > 0;
+    if (both) {
+      PTTS_CUDA_CHECK(cudaEventRecord(ev_fork, stream));
+      PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_fork, 0));
+    }
+    for (int j = 0; j < g_flow; ++j) {
+      commit_out = lat_ring[parity] + j * fl;
+      rc = flow_sequence(n, lsd, noise_grp + j * fl, eos_grp[parity] + (size_t)j * n);
+      commit_out = nullptr;
+      if (rc != PTTS_OK) return rc;
+    }
+    if (g_mimi > 0) {
+      cudaStream_t main_stream = stream;
+      if (both) { stream = stream2; n_sms = n_sms_mimi; }   // the launchers read the members
+      rc = mimi_sequence(n, lat_ring[parity ^ 1], g_mimi, pcm_ring[parity ^ 1]);
+      stream = main_stream;
+      n_sms = n_sms_flow;
+      if (rc != PTTS_OK) return rc;
+      if (both) {
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_join, stream2));
+        PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_join, 0));
+      }
+    }
+    return PTTS_OK;
+  });
+}
+
+// FlowLM step + flow head of frame slot j of the group with parity `par`: noise noise_grp[j] ->
+// latents lat_ring[par][j], EOS logits eos_grp[par][j]
+int Engine::flow_graph(int n, int lsd, int par, int j) {
+  if (mega_eligible(n)) {   // built outside capture
+    MegaPlan* plan = nullptr;
+    const int prc = mega_plan(lsd, &plan);
+    if (prc != PTTS_OK) return prc;
+  }
+  const size_t fl = (size_t)n * cfg.ldim;
+  return launch_captured(GraphKey{n, lsd, 0, 2000 + j * 2 + par}, stream, [&]() -> int {
+    commit_out = lat_ring[par] + j * fl;
+    const int rc = flow_sequence(n, lsd, noise_grp + j * fl, eos_grp[par] + (size_t)j * n);
+    commit_out = nullptr;
+    return rc;
+  });
+}
+
+// Mimi pass over the g latents of lat_ring[par] -> pcm_ring[par], on stream2
+int Engine::mimi_graph(int n, int g, int par) {
+  cudaStream_t main_stream = stream;
+  stream = stream2;   // the launchers read the members
+  n_sms = n_sms_mimi;
+  const int rc = launch_captured(GraphKey{n, 0, 1, 3000 + g * 2 + par}, stream2,
+                                 [&]() -> int { return mimi_sequence(n, lat_ring[par], g, pcm_ring[par]); });
+  stream = main_stream;
+  n_sms = n_sms_flow;
+  return rc;
 }
 
 int Engine::step(int n, const int* slots, const float* noise_any, int lsd, int audio, float* out_lat,
@@ -308,48 +360,125 @@ int Engine::mimi_decode(int n, const int* slots, const float* latents_any, float
   return PTTS_OK;
 }
 
-int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise_dev, int lsd,
-                       float* out_pcm_dev, float* out_lat_dev, float* out_eos, bool sync) {
+// The frame loop (tts_model.py:745-779 + the decoder thread :434-474) for n streams and n_frames frames.
+// Pipelined form: group k of the schedule 1, 1, 2, 4, ... (<= mimi_gmax frames) runs its FlowLM frames while the
+// Mimi pass decodes group k-1; the result copies of a group ride `copy_stream` beside the next group's graph.
+int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise_any, int lsd,
+                       float* out_pcm_any, float* out_lat_any, float* out_eos, bool sync) {
   NEED_READY();
   int rc;
   if ((rc = check_slots(n, slots, true)) != PTTS_OK) return rc;
   if (lsd < 1 || lsd > tcomb_rows) PTTS_FAIL(PTTS_EINVAL, "lsd_steps %d outside loaded flow.tcomb rows %d", lsd, tcomb_rows);
-  if (n_frames < 1 || !noise_dev) PTTS_FAIL(PTTS_EINVAL, "run_frames: bad arguments");
+  if (n_frames < 1 || !noise_any) PTTS_FAIL(PTTS_EINVAL, "run_frames: bad arguments");
   for (int i = 0; i < n; ++i)
     if (host_offsets[slots[i]] + n_frames > cfg.kv_capacity)
       PTTS_FAIL(PTTS_ENOSLOT, "slot %d: %d frames exceed KV capacity", slots[i], n_frames);
   if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
   const int Ld = cfg.ldim;
+  const size_t fl = (size_t)n * Ld;
   const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
   static const int part = [] { const char* e = getenv("PTTS_PROFILE_PART"); return e ? atoi(e) : 0; }();  // 1: FlowLM+head only, 2: Mimi only (profiling)
-  const bool piped = use_pipeline && part == 0;
-  auto copy_pcm = [&](int f) -> int {
-    if (out_pcm_dev)
-      PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_dev + (size_t)f * fs, (size_t)n_frames * fs * sizeof(float), pcm,
-                                        fs * sizeof(float), fs * sizeof(float), n, cudaMemcpyDefault, stream));
-    return PTTS_OK;
-  };
-  for (int f = 0; f < n_frames; ++f) {
-    PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_dev + (size_t)f * n * Ld, (size_t)n * Ld * sizeof(float),
-                                    cudaMemcpyDefault, stream));
-    if (piped) {
-      // FlowLM(f) || Mimi(f-1); the PCM of frame f-1 is complete when this graph has joined
-      if ((rc = frame_pipelined(n, lsd, f & 1, true, f > 0)) != PTTS_OK) return rc;
-      if (f > 0 && (rc = copy_pcm(f - 1)) != PTTS_OK) return rc;
-    } else {
+  const bool piped = use_pipeline && (part == 0 || part >= 3);   // 3: grouped loop without the Mimi branch (profiling)
+  if (!piped) {
+    for (int f = 0; f < n_frames; ++f) {
+      PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_any + (size_t)f * fl, fl * sizeof(float), cudaMemcpyDefault, stream));
       if (part == 2) { if ((rc = mimi_sequence(n, x_lat)) != PTTS_OK) return rc; }
       else if ((rc = frame(n, lsd, part == 1 ? 0 : 1)) != PTTS_OK) return rc;
-      if ((rc = copy_pcm(f)) != PTTS_OK) return rc;
+      if (out_pcm_any)
+        PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_any + (size_t)f * fs, (size_t)n_frames * fs * sizeof(float), pcm,
+                                          fs * sizeof(float), fs * sizeof(float), n, cudaMemcpyDefault, stream));
+      if (out_lat_any)
+        PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat_any + (size_t)f * fl, x_lat, fl * sizeof(float), cudaMemcpyDefault, stream));
+      if (out_eos)
+        PTTS_CUDA_CHECK(cudaMemcpyAsync(out_eos + (size_t)f * n, eos_logit, (size_t)n * sizeof(float), cudaMemcpyDefault, stream));
     }
-    if (out_lat_dev)
-      PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat_dev + (size_t)f * n * Ld, x_lat, (size_t)n * Ld * sizeof(float),
-                                      cudaMemcpyDefault, stream));
-    if (out_eos)
-      PTTS_CUDA_CHECK(cudaMemcpyAsync(out_eos + (size_t)f * n, eos_logit, (size_t)n * sizeof(float), cudaMemcpyDefault, stream));
-  }
-  if (piped) {   // drain: Mimi decode of the last frame
-    if ((rc = frame_pipelined(n, lsd, n_frames & 1, false, true)) != PTTS_OK) return rc;
-    if ((rc = copy_pcm(n_frames - 1)) != PTTS_OK) return rc;
+  } else if (loop_fork) {
+    const bool copies = out_pcm_any || out_lat_any || out_eos;
+    int f0 = 0, k = 0, prev_f0 = 0, prev_g = 0;
+    bool copied[2] = {false, false};
+    while (f0 < n_frames || prev_g > 0) {
+      const int par = k & 1;
+      const int want = k < 2 ? 1 : std::min(mimi_gmax, 1 << std::min(k - 1, 4));
+      const int g = std::min(want, n_frames - f0);   // 0 on the drain group
+      if (copies && copied[par]) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_copied_lat[par], 0));   // buffers of this parity are free again
+      if (g > 0)
+        PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_grp, noise_any + (size_t)f0 * fl, g * fl * sizeof(float), cudaMemcpyDefault, stream));
+      if ((rc = group_graph(n, lsd, par, g, part == 3 ? 0 : prev_g)) != PTTS_OK) return rc;
+      if (copies) {
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_lat[par], stream));
+        PTTS_CUDA_CHECK(cudaStreamWaitEvent(copy_stream, ev_lat[par], 0));
+        if (g > 0 && out_lat_any)
+          PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat_any + (size_t)f0 * fl, lat_ring[par], g * fl * sizeof(float), cudaMemcpyDefault, copy_stream));
+        if (g > 0 && out_eos)
+          PTTS_CUDA_CHECK(cudaMemcpyAsync(out_eos + (size_t)f0 * n, eos_grp[par], (size_t)g * n * sizeof(float), cudaMemcpyDefault, copy_stream));
+        if (prev_g > 0 && out_pcm_any && part != 3)
+          PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_any + (size_t)prev_f0 * fs, (size_t)n_frames * fs * sizeof(float), pcm_ring[par ^ 1],
+                                            prev_g * fs * sizeof(float), prev_g * fs * sizeof(float), n, cudaMemcpyDefault, copy_stream));
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_copied_lat[par], copy_stream));
+        copied[par] = true;
+      }
+      prev_f0 = f0; prev_g = g;
+      f0 += g;
+      ++k;
+    }
+    for (int q = 0; q < 2; ++q)
+      if (copied[q]) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_copied_lat[q], 0));
+  } else {
+    const bool copies = out_pcm_any || out_lat_any || out_eos;
+    const bool do_mimi = part != 3;
+    int f0 = 0;
+    bool used[2] = {false, false};
+    for (int k = 0; f0 < n_frames; ++k) {
+      const int par = k & 1;
+      const int want = k < 2 ? 1 : std::min(mimi_gmax, 1 << std::min(k - 1, 4));
+      const int g = std::min(want, n_frames - f0);
+      if (used[par]) {   // buffers of this parity: the Mimi pass and the copies of group k-2 must have drained them
+        if (do_mimi) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_mimi[par], 0));
+        if (copies) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_copied_lat[par], 0));
+      }
+      static const bool per_frame_noise = [] { const char* e = getenv("PTTS_NOISE_PER_FRAME"); return !(e && e[0] == '0'); }();
+      if (!per_frame_noise)
+        PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_grp, noise_any + (size_t)f0 * fl, g * fl * sizeof(float), cudaMemcpyDefault, stream));
+      for (int j = 0; j < g; ++j) {
+        if (per_frame_noise)
+          PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_grp + j * fl, noise_any + (size_t)(f0 + j) * fl, fl * sizeof(float), cudaMemcpyDefault, stream));
+        if ((rc = flow_graph(n, lsd, par, j)) != PTTS_OK) return rc;
+      }
+      PTTS_CUDA_CHECK(cudaEventRecord(ev_lat[par], stream));
+      if (copies) {
+        PTTS_CUDA_CHECK(cudaStreamWaitEvent(copy_stream, ev_lat[par], 0));
+        if (out_lat_any)
+          PTTS_CUDA_CHECK(cudaMemcpyAsync(out_lat_any + (size_t)f0 * fl, lat_ring[par], g * fl * sizeof(float), cudaMemcpyDefault, copy_stream));
+        if (out_eos)
+          PTTS_CUDA_CHECK(cudaMemcpyAsync(out_eos + (size_t)f0 * n, eos_grp[par], (size_t)g * n * sizeof(float), cudaMemcpyDefault, copy_stream));
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_copied_lat[par], copy_stream));
+      }
+      if (do_mimi) {
+        PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_lat[par], 0));
+        if (copies && used[par]) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_copied_pcm[par], 0));
+        if ((rc = mimi_graph(n, g, par)) != PTTS_OK) return rc;
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_mimi[par], stream2));
+        if (copies) {
+          PTTS_CUDA_CHECK(cudaStreamWaitEvent(copy_stream, ev_mimi[par], 0));
+          if (out_pcm_any)
+            PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_any + (size_t)f0 * fs, (size_t)n_frames * fs * sizeof(float), pcm_ring[par],
+                                              g * fs * sizeof(float), g * fs * sizeof(float), n, cudaMemcpyDefault, copy_stream));
+          PTTS_CUDA_CHECK(cudaEventRecord(ev_copied_pcm[par], copy_stream));
+        }
+      }
+      used[par] = true;
+      f0 += g;
+    }
+    // the caller synchronises `stream`: make it wait for the Mimi passes and copies still in flight
+    for (int q = 0; q < 2; ++q)
+      if (used[q]) {
+        if (do_mimi) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_mimi[q], 0));
+        if (copies) {
+          PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_copied_lat[q], 0));
+          if (do_mimi) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_copied_pcm[q], 0));
+        }
+      }
+    // x_lat / eos_logit of the last frame stay readable through the single-frame buffers' owners
   }
   for (int i = 0; i < n; ++i) {
     host_offsets[slots[i]] += n_frames;

@@ -58,7 +58,7 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
   }
   if (mimi) {
     LAUNCH("mimi.attn", launch_attn_window(qkvb, rope_freqs, mimi_offsets, d_slot_ids, kv_mimi, li, cfg.mimi_context,
-                                           cfg.upsample_stride, ao, act_type, n, stream));
+                                           cfg.upsample_stride, ao, act_type, n, stream, rows / (n * cfg.upsample_stride)));
   } else if (rows == n) {
     LAUNCH("flow.attn_decode", launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, kv_flow, li, ao, act_type, n, stream));
   } else {
@@ -84,19 +84,22 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
 }
 
 // FlowLM step + flow head for the n streams in d_slot_ids; noise in noise_buf.
-int Engine::flow_sequence(int n, int lsd) {
+int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
+  if (!noise) noise = noise_buf;
+  if (!eos_out) eos_out = eos_logit;
   const ptts_config& c = cfg;
   const int D = c.d_model, F = c.flow_dim, Ld = c.ldim;
   const int modld = (c.flow_depth * 3 + 2) * F;
   int rc;
+  if (mega_eligible(n)) return flow_sequence_mega(n, lsd, noise, eos_out);
   LAUNCH("flow.embed", launch_flow_embed(prev_latent, d_slot_ids, bos_emb, w_in, h, n, D, Ld, stream));
   for (int l = 0; l < c.n_layers; ++l)
     if ((rc = transformer_layer_common(flow_layers[l], h, n, D, c.ffn, a_ln, qkv, attn_o, mid, false, l, n)) != PTTS_OK)
       return rc;
-  LAUNCH("flow.final_norm_eos", launch_final_norm_eos(h, out_norm_w, out_norm_b, 1e-5f, eos_w, eos_b, c_cond, act_type, eos_logit, n, D, stream));
+  LAUNCH("flow.final_norm_eos", launch_final_norm_eos(h, out_norm_w, out_norm_b, 1e-5f, eos_w, eos_b, c_cond, act_type, eos_out, n, D, stream));
   LAUNCH("advance", launch_advance(offsets, d_slot_ids, nullptr, 1, n, stream));
   // LSD / Euler integration from the injected noise (flow_lm.py:32-40)
-  PTTS_CUDA_CHECK(cudaMemcpyAsync(x_lat, noise_buf, (size_t)n * Ld * sizeof(float), cudaMemcpyDeviceToDevice, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(x_lat, noise, (size_t)n * Ld * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   {
     GemmEpilogue ep; ep.bias = cond_b; ep.out = cemb; ep.out_map = plain(F);
     if ((rc = gemm("head.cond_embed", c_cond, true, plain(D), cond_embed, n, ep, false)) != PTTS_OK) return rc;
@@ -137,17 +140,23 @@ int Engine::flow_sequence(int n, int lsd) {
   return PTTS_OK;
 }
 
-// Mimi frame decode of `latents` [n, ldim] (device fp32) -> pcm [n, 1920]
-int Engine::mimi_sequence(int n, const float* latents) {
+// Mimi decode of `frames` consecutive latents per stream, latents [frames][n, ldim] (device fp32) ->
+// pcm_out [n, frames * 1920].  One pass over frames * 16 tokens per stream is arithmetically the same as
+// `frames` single-frame passes (causal attention, causal convolutions with carried history).
+int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_out) {
   const ptts_config& c = cfg;
-  const int Md = c.mimi_d, U = c.upsample_stride;
+  const int Md = c.mimi_d, U = c.upsample_stride * frames;
   int rc;
-  LAUNCH("mimi.embed_upsample", launch_mimi_embed(latents, d_slot_ids, emb_std, emb_mean, wq, wup, e_prev, xm, n, Md, c.ldim, U, stream));
+  if (frames < 1 || frames > mimi_gmax) PTTS_FAIL(PTTS_EINVAL, "mimi pass of %d frames (max %d)", frames, mimi_gmax);
+  if (!pcm_out) pcm_out = pcm;
+  HistTable tab = hist_tab;
+  for (int k = 0; k < tab.count; ++k) tab.d[k].T *= frames;
+  LAUNCH("mimi.embed_upsample", launch_mimi_embed(latents, d_slot_ids, emb_std, emb_mean, wq, wup, e_prev, xm, n, Md, c.ldim, c.upsample_stride, frames, stream));
   for (int l = 0; l < c.mimi_layers; ++l)
     if ((rc = transformer_layer_common(mimi_layers[l], xm, n * U, Md, c.mimi_ffn, m_ln, mqkv, m_attn, m_mid, true, l, n)) != PTTS_OK)
       return rc;
   LAUNCH("advance", launch_advance(mimi_offsets, d_slot_ids, nullptr, U, n, stream));
-  LAUNCH("seanet.hist_gather", launch_hist_gather(hist_tab, d_slot_ids, act_type, n, stream));
+  LAUNCH("seanet.hist_gather", launch_hist_gather(tab, d_slot_ids, act_type, n, stream));
   const int h0 = c.kernel - 1;
   LAUNCH("seanet.stage", launch_stage_rows(xm, b_conv0, act_type, n, U, Md, h0, stream));
   const size_t es = act_size;
@@ -184,8 +193,8 @@ int Engine::mimi_sequence(int n, const float* latents) {
     }
     T = T2; C = C2;
   }
-  LAUNCH("seanet.last_conv", launch_last_conv(b_last, act_type, last_w, last_b, pcm, n, T, C, c.last_kernel, stream));
-  LAUNCH("seanet.hist_scatter", launch_hist_scatter(hist_tab, d_slot_ids, act_type, n, stream));
+  LAUNCH("seanet.last_conv", launch_last_conv(b_last, act_type, last_w, last_b, pcm_out, n, T, C, c.last_kernel, stream));
+  LAUNCH("seanet.hist_scatter", launch_hist_scatter(tab, d_slot_ids, act_type, n, stream));
   return PTTS_OK;
 }
 

@@ -7,6 +7,8 @@
 // start at time t: rows overlap, ld = C_in) and K=2S ConvTranspose1d (rows of 2*C_in,
 // ld = C_in, N = S*C_out) — see DESIGN.md "convolutions as overlapping-row GEMMs".
 #pragma once
+#include <cuda.h>
+
 #include "common.cuh"
 
 namespace ptts {
@@ -39,6 +41,8 @@ struct GemmProblem {
 cudaError_t gemm_simt_launch(const GemmProblem& p, int in_type, int out_type, cudaStream_t st);
 // bf16 x bf16 -> fp32 on tcgen05 tensor cores (operands via TMA); a_rows_alloc = addressable A rows
 void tc_trace_dump(const char* what);
+// 2-D bf16 SWIZZLE_128B tensor map (inner dim K, box 64 x box_rows); cached per argument tuple
+bool tc_make_map(CUtensorMap* out, const void* base, long long rows, int K, long long ld, int box_rows);
 cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_alloc, int n_sms, bool pdl,
                            cudaStream_t st);
 

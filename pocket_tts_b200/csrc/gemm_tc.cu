@@ -34,99 +34,9 @@
 #include <tuple>
 
 #include "gemm.cuh"
+#include "tc_ptx.cuh"
 
 namespace ptts {
-
-// --------------------------------------------------------------------------- PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra WAIT_DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "WAIT_DONE:\n\t"
-      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-// 32-bit shared-address forms for the single-thread issue loops (no generic->shared conversion,
-// no 64-bit address arithmetic per k-block)
-__device__ __forceinline__ void mbar_expect_tx_a(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_a(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "WAIT_LOOP:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra WAIT_DONE;\n\t"
-      "bra WAIT_LOOP;\n\t"
-      "WAIT_DONE:\n\t"
-      "}" ::"r"(bar), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d_a(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
-}
-__device__ __forceinline__ void tc_commit_a(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// D[tmem] (+)= A[smem desc] * B[smem desc], bf16 x bf16 -> fp32
-__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                            uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
-}
-
-// shared-memory matrix descriptor: K-major, SWIZZLE_128B, 8-row groups 1024 B apart
-__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t saddr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr >> 4) & 0x3FFF);   // start address, 16-byte units
-  d |= (uint64_t)1 << 16;                   // leading byte offset (unused for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;         // stride byte offset between 8-row core groups
-  d |= (uint64_t)1 << 46;                   // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;                   // SWIZZLE_128B
-  return d;
-}
-
-// ---- thread-block-cluster helpers
-__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
-__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
-__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
-__device__ __forceinline__ uint32_t dsmem_addr(uint32_t local_addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ void dsmem_st(uint32_t addr, float v) {
-  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
-}
-__device__ __forceinline__ float4 ld4f(const float* p) { return *reinterpret_cast<const float4*>(p); }
 
 constexpr int BM_TC = 128;   // TMEM lanes / UMMA M
 constexpr int BK_TC = 64;    // bf16 elements per 128-byte swizzle row
@@ -142,102 +52,6 @@ struct TcParams {
   long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
 };
 #define TC_TRACE(slot) do { if (P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) P.trace[slot] = clock64(); } while (0)
-
-// ---- TMEM -> registers: CH consecutive fp32 columns of this thread's lane
-template <int CH> __device__ __forceinline__ void tmem_ld(uint32_t taddr, float* v);
-template <> __device__ __forceinline__ void tmem_ld<16>(uint32_t taddr, float* v) {
-  uint32_t r[16];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
-template <> __device__ __forceinline__ void tmem_ld<32>(uint32_t taddr, float* v) {
-  uint32_t r[32];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// CH contiguous elements of a row <-> registers, 16-byte vector accesses
-template <int CH> __device__ __forceinline__ void row_load(const float* p, float* v) {
-#pragma unroll
-  for (int j = 0; j < CH; j += 4) { const float4 t = *reinterpret_cast<const float4*>(p + j); v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w; }
-}
-template <int CH> __device__ __forceinline__ void row_load(const bf16* p, float* v) {
-#pragma unroll
-  for (int j = 0; j < CH; j += 8) {
-    const uint4 t = *reinterpret_cast<const uint4*>(p + j);
-    const uint32_t w[4] = {t.x, t.y, t.z, t.w};
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[q]));
-      v[j + 2 * q] = f.x; v[j + 2 * q + 1] = f.y;
-    }
-  }
-}
-template <int CH> __device__ __forceinline__ void row_store(float* p, const float* v) {
-#pragma unroll
-  for (int j = 0; j < CH; j += 4) *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-}
-template <int CH> __device__ __forceinline__ void row_store(bf16* p, const float* v) {
-#pragma unroll
-  for (int j = 0; j < CH; j += 8) {
-    uint32_t w[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const __nv_bfloat162 b = __floats2bfloat162_rn(v[j + 2 * q], v[j + 2 * q + 1]);
-      w[q] = *reinterpret_cast<const uint32_t*>(&b);
-    }
-    *reinterpret_cast<uint4*>(p + j) = make_uint4(w[0], w[1], w[2], w[3]);
-  }
-}
-// Activations of the bf16 mode: results are rounded to bf16 (or feed a bf16 GEMM operand), so the
-// short forms below (absolute error <= 2e-7) are exact to the storage precision while keeping the
-// unrolled epilogue small (the libm erff / expm1f bodies made each kernel ~10k SASS instructions and
-// cold instruction fetch dominated the short decode GEMMs).  The fp32 parity mode never comes here.
-__device__ __forceinline__ float gelu_call(float x) {
-  // erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7)
-  const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  const float e = 1.0f - p * t * __expf(-z * z);
-  return 0.5f * x * (1.0f + copysignf(e, x));
-}
-__device__ __forceinline__ float silu_call(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
-__device__ __forceinline__ float elu_call(float x) {
-  const float small = x * fmaf(x, fmaf(x, fmaf(x, fmaf(x, 0.0083333333f, 0.041666667f), 0.16666667f), 0.5f), 1.0f);
-  const float big = __expf(x) - 1.0f;
-  return x > 0.0f ? x : (x > -0.125f ? small : big);
-}
-template <int CH> __device__ __forceinline__ void act_inplace(float* v, int act) {
-  if (act == ACT_NONE) return;
-  if (act == ACT_GELU) {
-#pragma unroll
-    for (int j = 0; j < CH; ++j) v[j] = gelu_call(v[j]);
-  } else if (act == ACT_SILU) {
-#pragma unroll
-    for (int j = 0; j < CH; ++j) v[j] = silu_call(v[j]);
-  } else {
-#pragma unroll
-    for (int j = 0; j < CH; ++j) v[j] = elu_call(v[j]);
-  }
-}
 
 // Row-major epilogue (SWAP = false).  TMEM hands every thread one output ROW, but global memory
 // wants consecutive lanes on consecutive COLUMNS: each epilogue warp therefore stages its
@@ -596,9 +410,6 @@ struct TcRowsParams {
   int tiles_n, n_tiles;
 };
 
-__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
 
 template <int BN, typename TO>
 __global__ void __launch_bounds__(TC_THREADS, 1)
@@ -725,7 +536,7 @@ static EncodeTiledFn get_encode() {
 
 // 2-D bf16 tensor map: inner dim K (contiguous), outer dim `rows` with stride `ld` elements
 // (ld < K is allowed: overlapping rows = streaming convolution windows), box = 64 x box_rows.
-static bool make_map(CUtensorMap* out, const void* base, long long rows, int K, long long ld, int box_rows) {
+bool tc_make_map(CUtensorMap* out, const void* base, long long rows, int K, long long ld, int box_rows) {
   using Key = std::tuple<const void*, long long, int, long long, int>;
   static std::map<Key, CUtensorMap> cache;
   static std::mutex mu;
@@ -866,8 +677,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   GemmEpilogue ep = p.ep;
   if (swap) {
     const int bn = pick_bn(p.M);
-    if (!make_map(&tw, p.W, p.N, p.K, p.K, BM_TC)) return cudaErrorUnknown;
-    if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, bn)) return cudaErrorUnknown;
+    if (!tc_make_map(&tw, p.W, p.N, p.K, p.K, BM_TC)) return cudaErrorUnknown;
+    if (!tc_make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, bn)) return cudaErrorUnknown;
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
     // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix
     int splits = 1;
@@ -901,7 +712,9 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   // measured (ncu, B=64): the persistent kernel wins when a tile has >= 8 k-blocks of mainloop to hide its
   // epilogue behind; thin layers (K <= 384) do better as one tile per CTA with two CTAs per SM
   if (!old_rows && p.N % 32 == 0 && P.num_kb >= 8) {
-    int bn = pick_bn(p.N);
+    // at most 128 columns per accumulator (2 x 128 TMEM columns per CTA): a resident 512-column CTA would make
+    // every tcgen05.alloc of the concurrent FlowLM branch on that SM wait until it retires
+    int bn = std::min(pick_bn(p.N), 128);
     if (bn < 32) bn = 32;
     double best = 1e30;
     for (int cand = bn; cand >= 32; cand >>= 1) {
@@ -918,8 +731,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     const size_t stage = (size_t)(BM_TC + bn) * 128;
     const size_t budget = (2 * stage + EPI_SMEM_BYTES <= TC_ROWS_SMEM) ? TC_ROWS_SMEM : TC_SMEM_LIMIT;
     R.stages = (int)std::max<size_t>(2, std::min<size_t>(6, (budget - EPI_SMEM_BYTES) / stage));
-    if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
-    if (!make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
+    if (!tc_make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
+    if (!tc_make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
     const int grid = std::min(R.n_tiles, n_sms);
 #define TC_CASE(BNV)                                                                  \
   case BNV:                                                                           \
@@ -935,10 +748,10 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   // row-major tile width from a small cost model (measured with the clock trace): a CTA costs
   // ~1.5 us set-up + 0.24 us per k-block (four tcgen05.mma issues + commit, independent of N) +
   // ~2 us epilogue latency + 0.3 us per 64 columns; the grid runs in waves of n_sms CTAs.
-  int bn = pick_bn(p.N);
+  int bn = std::min(pick_bn(p.N), 128);
   {
     double best = 1e30;
-    for (int cand = pick_bn(p.N); cand >= 32; cand >>= 1) {
+    for (int cand = bn; cand >= 32; cand >>= 1) {
       const int ctas = tiles_m * ((p.N + cand - 1) / cand);
       // multi-wave grids run two CTAs per SM (stage ring capped at ~108 KB below): one CTA's
       // epilogue overlaps the other's mainloop, so a "wave" holds 2 * n_sms CTAs at ~1.3x the time
@@ -948,8 +761,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
       if (t < best - 1e-9) { best = t; bn = cand; }
     }
   }
-  if (!make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
-  if (!make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
+  if (!tc_make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
+  if (!tc_make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
   P.kb_per_split = P.num_kb;
   {
     const int ctas = tiles_m * ((p.N + bn - 1) / bn);

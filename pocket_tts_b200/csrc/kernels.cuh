@@ -40,7 +40,7 @@ cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* of
 // window `context` over the ring cache; the visible window is staged once in shared memory.
 cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets,
                                const int* slot_ids, KvGeom kv, int layer, int context, int T, void* out,
-                               int out_type, int n, cudaStream_t st);
+                               int out_type, int n, cudaStream_t st, int frames = 1);
 
 // offsets[slot_ids[i]] += inc[i] (inc == nullptr: += const_inc)
 cudaError_t launch_advance(int* offsets, const int* slot_ids, const int* inc, int const_inc, int n,
@@ -70,7 +70,8 @@ cudaError_t launch_commit_latent(const float* x, const int* slot_ids, float* pre
 cudaError_t launch_mimi_embed(const float* latents, const int* slot_ids, const float* emb_std,
                               const float* emb_mean, const float* w_q /*[C,ldim]*/,
                               const float* w_up /*[C,2S]*/, float* e_prev /*[slots,C]*/,
-                              float* xm /*[n*S,C]*/, int n, int C, int ldim, int S, cudaStream_t st);
+                              float* xm /*[n*frames*S,C]*/, int n, int C, int ldim, int S, int frames,
+                              cudaStream_t st);
 
 // rows of xm (fp32 [n*T, C]) -> buf[i][hist + t][c] (act type)
 cudaError_t launch_stage_rows(const float* xm, void* buf, int buf_type, int n, int T, int C,

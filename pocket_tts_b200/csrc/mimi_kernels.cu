@@ -7,50 +7,57 @@
 namespace ptts {
 
 // grid (n, C/128): one thread per channel; every weight row a thread needs (32 + 32 floats) is
-// fetched with 16-byte loads up front so the loads are in flight together
+// fetched with 16-byte loads up front so the loads are in flight together.  `frames` consecutive
+// latents of a stream (latents [frames][n][ldim]) are expanded in one launch: frame f uses the
+// projection of frame f-1 as its "previous input column" (resample.py:41-48 streaming state).
 __global__ void __launch_bounds__(128)
 mimi_embed_kernel(const float* __restrict__ latents, const int* __restrict__ slot_ids,
                   const float* __restrict__ emb_std, const float* __restrict__ emb_mean,
                   const float* __restrict__ w_q, const float* __restrict__ w_up,
-                  float* __restrict__ e_prev, float* __restrict__ xm, int C, int ldim, int S) {
+                  float* __restrict__ e_prev, float* __restrict__ xm, int n, int C, int ldim, int S, int frames) {
   pdl_launch_dependents();
   pdl_wait();
-  __shared__ float z[64];
+  __shared__ float z[8 * 64];
   const int i = blockIdx.x, slot = slot_ids[i];
-  if (threadIdx.x < ldim)
-    z[threadIdx.x] = latents[i * ldim + threadIdx.x] * emb_std[threadIdx.x] + emb_mean[threadIdx.x];
+  for (int e = threadIdx.x; e < frames * ldim; e += blockDim.x) {
+    const int f = e / ldim, j = e - f * ldim;
+    z[f * 64 + j] = latents[((long long)f * n + i) * ldim + j] * emb_std[j] + emb_mean[j];
+  }
   __syncthreads();
   const int c = blockIdx.y * blockDim.x + threadIdx.x;
   if (c >= C) return;
   const float* w = w_q + (long long)c * ldim;
-  float e = 0.0f;
-  for (int j = 0; j < ldim; j += 4) {
-    const float4 wv = load4(w + j);
-    e = fmaf(wv.x, z[j], e);
-    e = fmaf(wv.y, z[j + 1], e);
-    e = fmaf(wv.z, z[j + 2], e);
-    e = fmaf(wv.w, z[j + 3], e);
-  }
-  const float ep = e_prev[(long long)slot * C + c];
-  e_prev[(long long)slot * C + c] = e;
   const float* wu = w_up + (long long)c * 2 * S;
-  // out[t] = e * w[t] + e_prev * w[S + t]   (K = 2S transposed conv, stride S, depthwise)
-  for (int t = 0; t < S; t += 4) {
-    const float4 a = load4(wu + t), b = load4(wu + S + t);
-    float* o = xm + ((long long)i * S + t) * C + c;
-    o[0] = e * a.x + ep * b.x;
-    o[C] = e * a.y + ep * b.y;
-    o[2 * C] = e * a.z + ep * b.z;
-    o[3 * C] = e * a.w + ep * b.w;
+  float ep = e_prev[(long long)slot * C + c];
+  for (int f = 0; f < frames; ++f) {
+    float e = 0.0f;
+    for (int j = 0; j < ldim; j += 4) {
+      const float4 wv = load4(w + j);
+      e = fmaf(wv.x, z[f * 64 + j], e);
+      e = fmaf(wv.y, z[f * 64 + j + 1], e);
+      e = fmaf(wv.z, z[f * 64 + j + 2], e);
+      e = fmaf(wv.w, z[f * 64 + j + 3], e);
+    }
+    // out[t] = e * w[t] + e_prev * w[S + t]   (K = 2S transposed conv, stride S, depthwise)
+    for (int t = 0; t < S; t += 4) {
+      const float4 a = load4(wu + t), b = load4(wu + S + t);
+      float* o = xm + (((long long)i * frames + f) * S + t) * C + c;
+      o[0] = e * a.x + ep * b.x;
+      o[C] = e * a.y + ep * b.y;
+      o[2 * C] = e * a.z + ep * b.z;
+      o[3 * C] = e * a.w + ep * b.w;
+    }
+    ep = e;
   }
+  e_prev[(long long)slot * C + c] = ep;
 }
 
 cudaError_t launch_mimi_embed(const float* latents, const int* slot_ids, const float* emb_std,
                               const float* emb_mean, const float* w_q, const float* w_up,
-                              float* e_prev, float* xm, int n, int C, int ldim, int S, cudaStream_t st) {
-  if (ldim > 64 || ldim % 4 || S % 4) return cudaErrorInvalidValue;
+                              float* e_prev, float* xm, int n, int C, int ldim, int S, int frames, cudaStream_t st) {
+  if (ldim > 64 || ldim % 4 || S % 4 || frames < 1 || frames > 8) return cudaErrorInvalidValue;
   launch_k(mimi_embed_kernel, dim3(n, (C + 127) / 128), 128, 0, st, latents, slot_ids, emb_std, emb_mean, w_q, w_up,
-           e_prev, xm, C, ldim, S);
+           e_prev, xm, n, C, ldim, S, frames);
   return cudaGetLastError();
 }
 

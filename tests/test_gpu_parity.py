@@ -168,7 +168,7 @@ def test_pipelined_run_frames_equals_step_sequence(precision):
     latents and PCM must be bit-identical to the same frames issued one ptts_step at a time."""
     case = load_case("gen_2l")
     orc = oracle_for(2)
-    G, B = 6, 3
+    G, B = 13, 3          # group schedule 1, 1, 2, 4, 4, 1: every Mimi pass size up to the default maximum
     eng = make_engine(2, precision=precision)
     conds = [case["cond"][0]] * B
     toks = [case["tokens"][0]] * B
@@ -193,6 +193,42 @@ def test_pipelined_run_frames_equals_step_sequence(precision):
     eng.synchronize()
     assert torch.equal(pcm2, pcm_c.cpu())
     eng.close()
+
+
+def test_generate_frames_host_buffers_equal_device_loop():
+    """ptts_generate_frames (host noise in, host latents / EOS logits / PCM out, copies on the side stream)
+    returns exactly what the device-resident loop computes."""
+    case = load_case("gen_2l")
+    orc = oracle_for(2)
+    G, B = 9, 2
+    eng = make_engine(2, precision="bf16")
+    noise = torch.randn(G, B, 32, generator=torch.Generator().manual_seed(12)) * 0.7 ** 0.5
+    a = _prefill_streams(eng, orc, [case["cond"][0]] * B, [case["tokens"][0]] * B)
+    b = _prefill_streams(eng, orc, [case["cond"][0]] * B, [case["tokens"][0]] * B)
+    pcm_d = torch.empty(B, G * 1920, device="cuda")
+    lat_d = torch.empty(G, B, 32, device="cuda")
+    eng.run_frames(a, noise.cuda().contiguous(), out_pcm=pcm_d, out_latents=lat_d)
+    eng.synchronize()
+    pcm_h, lat_h, eos_h = eng.generate_frames(b, noise)
+    assert torch.equal(pcm_h, pcm_d.cpu()) and torch.equal(lat_h, lat_d.cpu())
+    assert bool(torch.isfinite(eos_h).all())
+    eng.close()
+
+
+def test_persistent_step_kernel_vs_reference_fixture(monkeypatch):
+    """PTTS_MEGA=1: the whole FlowLM step + flow head as one persistent kernel (flow_mega.cu) meets the same
+    bf16 gate as the kernel-per-op sequence and agrees with it closely."""
+    monkeypatch.setenv("PTTS_MEGA", "1")
+    _check_case("gen_2l", "bf16", teacher=True, tol=TOL_BF16, snr_min=None)
+    _check_case("gen_english_6l", "bf16", teacher=True, tol=TOL_BF16, snr_min=None)
+    case = load_case("gen_2l")
+    outs = []
+    for flag in ("1", "0"):
+        monkeypatch.setenv("PTTS_MEGA", flag)
+        eng = make_engine(2, precision="bf16")
+        outs.append(_run_engine_case(eng, case, teacher=True))
+        eng.close()
+    assert po.rel_l2(outs[0][0], outs[1][0]) <= 1e-2
 
 
 def test_error_conventions():
