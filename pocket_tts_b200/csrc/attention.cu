@@ -352,6 +352,9 @@ __device__ __forceinline__ float2 kv_word_pair(const uint32_t* row, int c, float
   return make_float2(__uint_as_float(row[2 * c]), __uint_as_float(row[2 * c + 1]));
 }
 
+__device__ __forceinline__ void cp_async4(uint32_t* smem_dst, const uint32_t* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src) : "memory");
+}
 template <typename TK> __device__ __forceinline__ void kv_smem_store(uint32_t* row, int lane, float2 v);
 template <> __device__ __forceinline__ void kv_smem_store<bf16>(uint32_t* row, int lane, float2 v) {
   const __nv_bfloat162 b = __floats2bfloat162_rn(v.x, v.y);
@@ -403,15 +406,15 @@ attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   for (int j = w; j < W; j += NW) {
     const int pj = lo + j;
     if (pj < off0) {
-      const TK* kr = kv_row<TK>(g, layer, slot, 0, h, pj);
-      const TK* vr = kv_row<TK>(g, layer, slot, 1, h, pj);
-      if (sizeof(TK) == 2) {
-        Ks[j * LD + lane] = reinterpret_cast<const uint32_t*>(kr)[lane];
-        Vs[j * LD + lane] = reinterpret_cast<const uint32_t*>(vr)[lane];
-      } else {
-        const uint2 kk = reinterpret_cast<const uint2*>(kr)[lane], vv = reinterpret_cast<const uint2*>(vr)[lane];
-        Ks[j * LD + 2 * lane] = kk.x; Ks[j * LD + 2 * lane + 1] = kk.y;
-        Vs[j * LD + 2 * lane] = vv.x; Vs[j * LD + 2 * lane + 1] = vv.y;
+      // asynchronous global -> shared copies: every row of the window is in flight at once (the register
+      // path exposed one L2 round trip per few rows)
+      const uint32_t* kr = reinterpret_cast<const uint32_t*>(kv_row<TK>(g, layer, slot, 0, h, pj));
+      const uint32_t* vr = reinterpret_cast<const uint32_t*>(kv_row<TK>(g, layer, slot, 1, h, pj));
+      constexpr int WPL = sizeof(TK) == 2 ? 1 : 2;   // 32-bit words per lane
+#pragma unroll
+      for (int q = 0; q < WPL; ++q) {
+        cp_async4(Ks + j * LD + WPL * lane + q, kr + WPL * lane + q);
+        cp_async4(Vs + j * LD + WPL * lane + q, vr + WPL * lane + q);
       }
     } else {
       const float* row = qkv + (long long)(r_pass + (pj - off0)) * 3 * d_model + h * 64 + 2 * lane;
@@ -425,6 +428,7 @@ attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
       }
     }
   }
+  asm volatile("cp.async.wait_all;" ::: "memory");
   __syncthreads();
 
   // phase 3: one warp per query

@@ -442,7 +442,7 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
       for (int j = 0; j < g; ++j) {
         if (per_frame_noise)
           PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_grp + j * fl, noise_any + (size_t)(f0 + j) * fl, fl * sizeof(float), cudaMemcpyDefault, stream));
-        if ((rc = flow_graph(n, lsd, par, j)) != PTTS_OK) return rc;
+        if (part != 4 && (rc = flow_graph(n, lsd, par, j)) != PTTS_OK) return rc;   // 4: Mimi passes only (profiling)
       }
       PTTS_CUDA_CHECK(cudaEventRecord(ev_lat[par], stream));
       if (copies) {

@@ -711,7 +711,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   static const bool old_rows = [] { const char* e = getenv("PTTS_TC_ROWS"); return e && e[0] == 'o'; }();
   // measured (ncu, B=64): the persistent kernel wins when a tile has >= 8 k-blocks of mainloop to hide its
   // epilogue behind; thin layers (K <= 384) do better as one tile per CTA with two CTAs per SM
-  if (!old_rows && p.N % 32 == 0 && P.num_kb >= 8) {
+  static const int rows_min_kb = [] { const char* e = getenv("PTTS_TC_ROWS_MINKB"); return e ? atoi(e) : 8; }();
+  if (!old_rows && p.N % 32 == 0 && P.num_kb >= rows_min_kb) {
     // at most 128 columns per accumulator (2 x 128 TMEM columns per CTA): a resident 512-column CTA would make
     // every tcgen05.alloc of the concurrent FlowLM branch on that SM wait until it retires
     int bn = std::min(pick_bn(p.N), 128);

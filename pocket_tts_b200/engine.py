@@ -219,20 +219,27 @@ class GenerationEngine:
         N.check(self.lib.ptts_run_frames(self._h, n, _i32(slots), F, _ptr(noise_dev), lsd_steps or self.lsd_steps,
                                          _ptr(out_pcm), _ptr(out_latents)))
 
+    def alloc_frame_outputs(self, n: int, F: int, *, want_latents: bool = True, pin: bool = True):
+        """Host buffers for `generate_frames` (pinned by default): (pcm [n, F*1920], latents [F, n, ldim] | None,
+        eos_logits [F, n]).  Allocate once and pass as `out=`: pinning memory costs milliseconds."""
+        kw = dict(dtype=torch.float32, pin_memory=pin)
+        pcm = torch.empty(n, F * self.cfg.frame_samples, **kw)
+        lat = torch.empty(F, n, self.cfg.ldim, **kw) if want_latents else None
+        eos = torch.empty(F, n, **kw)
+        return pcm, lat, eos
+
     def generate_frames(self, slots, noise: torch.Tensor, *, lsd_steps: int | None = None, want_latents: bool = True,
-                        pin: bool = True):
+                        pin: bool = True, out=None):
         """Streaming generation with HOST buffers: noise [F, n, ldim] (host) ->
-        (pcm [n, F*1920], latents [F, n, ldim] | None, eos_logits [F, n]) on the host.  FlowLM(f) and
-        Mimi(f-1) overlap on the device; copies ride the same stream (pinned buffers)."""
+        (pcm [n, F*1920], latents [F, n, ldim] | None, eos_logits [F, n]) on the host.  The FlowLM frames of a
+        group overlap the Mimi pass of the previous group on the device; result copies ride a side stream."""
         F, n, _ = noise.shape
         assert n == len(slots)
         noise = noise.detach().to(torch.float32).contiguous()
         if pin and not noise.is_pinned() and not noise.is_cuda:
             noise = noise.pin_memory()
-        kw = dict(dtype=torch.float32, pin_memory=pin)
-        pcm = torch.empty(n, F * self.cfg.frame_samples, **kw)
-        lat = torch.empty(F, n, self.cfg.ldim, **kw) if want_latents else None
-        eos = torch.empty(F, n, **kw)
+        pcm, lat, eos = out if out is not None else self.alloc_frame_outputs(n, F, want_latents=want_latents, pin=pin)
+        assert pcm.shape == (n, F * self.cfg.frame_samples) and eos.shape == (F, n)
         N.check(self.lib.ptts_generate_frames(self._h, n, _i32(slots), F, _ptr(noise), lsd_steps or self.lsd_steps,
                                               _ptr(pcm), _ptr(lat), _ptr(eos)))
         return pcm, lat, eos
