@@ -79,6 +79,7 @@ int Engine::mega_plan(int lsd, MegaPlan** out) {
     const LayerW& w = flow_layers[l];
     { MegaPhase p = rows(MR_RES_LN, 1); p.d = D; p.S = l == 0 ? 0 : SK; p.w = w.n1w; p.b = w.n1b; p.eps = 1e-5f; p.out_act = a_ln; ph.push_back(p); }
     gemm(w.in_proj, am_aln, 64, 2, MG_PARTIAL, ACT_NONE, nullptr, mega_part, 0);
+    ph.back().flag = 1; ph.back().idx = l;   // compute warps prefetch this layer's cached K/V into L2 meanwhile
     { MegaPhase p{}; p.type = MP_ATTN; p.n_items = -c.n_heads; p.S = 2; p.part = mega_part; p.idx = l; ph.push_back(p); }
     gemm(w.out_proj, am_ao, 64, SK, MG_PARTIAL, ACT_NONE, nullptr, mega_part, 0);
     { MegaPhase p = rows(MR_RES_LN, 1); p.d = D; p.S = SK; p.w = w.n2w; p.b = w.n2b; p.eps = 1e-5f; p.out_act = a_ln; ph.push_back(p); }

@@ -19,7 +19,9 @@
 namespace ptts {
 namespace {
 
-constexpr int MEGA_THREADS = 320;
+constexpr int MEGA_NCW = 4;                      // compute warps (192 threads / ~100 KB per CTA: an SM can host a Mimi CTA beside it)
+constexpr int MEGA_CT = 32 * MEGA_NCW;
+constexpr int MEGA_THREADS = 64 + MEGA_CT;
 constexpr int MEGA_W_BYTES = 64 * 128;          // weight block of a ring stage
 constexpr int MEGA_MAX_STAGES = 12;
 constexpr int MEGA_TMEM_COLS = 128;             // two accumulator buffers of 64 columns
@@ -95,7 +97,7 @@ __device__ __forceinline__ void decode_item(const MegaPhase* ph, int item, Item&
 // ------------------------------------------------------------------ TMA producer (warp 0)
 struct KCursor {          // walks this CTA's k-blocks through all GEMM phases of the program
   int p, item, kb;
-  int nkb, wmap, amap, n_tile, w_row, kcol;
+  int nkb, wmap, amap, n_tile, w_row, kb0, rot, kcol;
   bool valid;
 };
 __device__ __forceinline__ void cursor_load(KCursor& c, const MegaParams& P, bool prefetch_maps) {
@@ -105,7 +107,10 @@ __device__ __forceinline__ void cursor_load(KCursor& c, const MegaParams& P, boo
       Item it;
       decode_item(ph, c.item, it);
       c.nkb = it.nkb; c.wmap = it.g->wmap; c.amap = it.g->amap; c.n_tile = it.g->n_tile;
-      c.w_row = it.w_row; c.kcol = it.kb0 * 64; c.kb = 0;
+      // every CTA reads the same activation k-blocks: start each CTA at a different one so that the requests of a
+      // phase spread over the L2 slices instead of queueing on one block at a time (any order sums the same set)
+      c.w_row = it.w_row; c.kb0 = it.kb0; c.rot = (int)(blockIdx.x % (unsigned)it.nkb); c.kb = 0;
+      c.kcol = (c.kb0 + c.rot) * 64;
       c.valid = true;
       if (prefetch_maps && (threadIdx.x & 31) == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(P.maps + c.wmap) : "memory");
@@ -119,7 +124,12 @@ __device__ __forceinline__ void cursor_load(KCursor& c, const MegaParams& P, boo
   c.valid = false;
 }
 __device__ __forceinline__ void cursor_next(KCursor& c, const MegaParams& P, bool prefetch_maps) {
-  if (++c.kb < c.nkb) { c.kcol += 64; return; }
+  if (++c.kb < c.nkb) {
+    int k = c.kb + c.rot;
+    if (k >= c.nkb) k -= c.nkb;
+    c.kcol = (c.kb0 + k) * 64;
+    return;
+  }
   c.item += P.G;
   cursor_load(c, P, prefetch_maps);
 }
@@ -225,7 +235,7 @@ __device__ __forceinline__ void gemm_epilogue(const MegaParams& P, const Item& i
   const bool row_ok = r < P.n;
   const int n_tile = g->n_tile, mode = g->mode, act = g->act;
   const float* bias = g->bias;
-  for (int c = half * 16; c < n_tile; c += 32) {
+  for (int c = half * 16; c < n_tile; c += 16 * (MEGA_NCW / 4)) {
     float v[16];
     tmem_ld<16>(taddr + (uint32_t)c, v);   // warp-collective
     if (!row_ok) continue;
@@ -252,19 +262,20 @@ __device__ __forceinline__ void gemm_epilogue(const MegaParams& P, const Item& i
 }
 
 // ------------------------------------------------------------------ compute warps: row-wise phases
-// One stream row per CTA: the 8 compute warps (256 threads) split the row's columns, so every load of a
-// row op is issued at once (h + up to 8 partial slabs per thread), and reduce through shared memory.
-__device__ __forceinline__ void cta_sync_compute() { asm volatile("bar.sync 4, 256;" ::: "memory"); }
-__device__ __forceinline__ float block_sum8(float v, float* red, int cw, int lane) {
+// One stream row per CTA: the NCW compute warps split the row's columns, so every load of a row op is issued
+// at once (h + up to 8 partial slabs per thread), and reduce through shared memory.
+__device__ __forceinline__ void cta_sync_compute() { asm volatile("bar.sync 4, %0;" ::"n"(MEGA_CT) : "memory"); }
+__device__ __forceinline__ void cta_sync_phase() { asm volatile("bar.sync 1, %0;" ::"n"(MEGA_CT) : "memory"); }
+__device__ __forceinline__ void cta_sync_start() { asm volatile("bar.sync 5, %0;" ::"n"(MEGA_CT) : "memory"); }
+__device__ __forceinline__ float block_sum_c(float v, float* red, int cw, int lane) {
   v = warp_sum(v);
   if (lane == 0) red[cw] = v;
   cta_sync_compute();
   float t = 0.0f;
 #pragma unroll
-  for (int j = 0; j < 8; ++j) t += red[j];
+  for (int j = 0; j < MEGA_NCW; ++j) t += red[j];
   return t;
 }
-__device__ __forceinline__ float2 ldcg2(const float* p) { return __ldcg(reinterpret_cast<const float2*>(p)); }
 
 // NE consecutive output features c0.. of y = W x, W [*, 32] fp32 row-major, x[j] held by lane j of every warp
 template <int NE>
@@ -289,15 +300,17 @@ __device__ __forceinline__ void dot_rows32(const float* __restrict__ w, int c0, 
   }
 }
 
-// h = W_in where(isnan(prev), bos, prev)                                   flow_lm.py:121-122
-__device__ void row_embed(const MegaParams& P, int row, int tid_c, int lane) {
+// h = W_in where(isnan(prev), bos, prev)   (flow_lm.py:121-122).  One warp per (row, 128-feature chunk).
+__device__ void row_embed(const MegaParams& P, int item, int lane) {
+  const int chunks = P.D / 128;
+  const int row = item / chunks, chunk = item - row * chunks;
   const int slot = P.slot_ids[row];
   float xl = 0.0f;
   if (lane < P.Ld) {
     xl = __ldcg(P.prev_latent + (size_t)slot * P.Ld + lane);
     if (isnan(xl)) xl = P.bos[lane];
   }
-  const int c0 = tid_c * 4;
+  const int c0 = chunk * 128 + lane * 4;
   float o[4];
   dot_rows32<4>(P.w_in, c0, xl, o);
   *reinterpret_cast<float4*>(P.h + (size_t)row * P.D + c0) = make_float4(o[0], o[1], o[2], o[3]);
@@ -307,32 +320,60 @@ __device__ void row_embed(const MegaParams& P, int row, int tid_c, int lane) {
 // final variant: out_norm + EOS logit, then the stream's offset advances   flow_lm.py:128-129,153-154
 __device__ void row_res_ln(const MegaParams& P, const MegaPhase& ph, int row, int tid_c, int cw, int lane, float* red,
                            bool final_norm) {
-  const int d = ph.d;   // 1024: one float4 per thread
-  const int c = tid_c * 4;
-  const size_t ro = (size_t)row * d + c, slab = (size_t)P.rows_pad * d;
-  float4 x = ldcg4(P.h + ro);
-  float4 t[8];
+  constexpr int J = 1024 / (4 * MEGA_CT);   // float4s per thread (d == 1024)
+  const int d = ph.d;
+  const size_t ro = (size_t)row * d, slab = (size_t)P.rows_pad * d;
+  float4 x[J], t[8][J], wv[J], bv[J];
+#pragma unroll
+  for (int j = 0; j < J; ++j) x[j] = ldcg4(P.h + ro + (tid_c + MEGA_CT * j) * 4);
 #pragma unroll
   for (int s = 0; s < 8; ++s)
-    if (s < ph.S) t[s] = ldcg4(ph.part + (size_t)s * slab + ro);
-  const float4 wv = *reinterpret_cast<const float4*>(ph.w + c), bv = *reinterpret_cast<const float4*>(ph.b + c);
+    if (s < ph.S) {
+#pragma unroll
+      for (int j = 0; j < J; ++j) t[s][j] = ldcg4(ph.part + (size_t)s * slab + ro + (tid_c + MEGA_CT * j) * 4);
+    }
+#pragma unroll
+  for (int j = 0; j < J; ++j) {
+    wv[j] = *reinterpret_cast<const float4*>(ph.w + (tid_c + MEGA_CT * j) * 4);
+    bv[j] = *reinterpret_cast<const float4*>(ph.b + (tid_c + MEGA_CT * j) * 4);
+  }
 #pragma unroll
   for (int s = 0; s < 8; ++s)
-    if (s < ph.S) { x.x += t[s].x; x.y += t[s].y; x.z += t[s].z; x.w += t[s].w; }
-  if (!final_norm && ph.S > 0) *reinterpret_cast<float4*>(P.h + ro) = x;
-  const float mu = block_sum8(x.x + x.y + x.z + x.w, red, cw, lane) / (float)d;
-  const float a0 = x.x - mu, a1 = x.y - mu, a2 = x.z - mu, a3 = x.w - mu;
-  const float var = block_sum8(a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3, red + 8, cw, lane) / (float)d;
-  const float rstd = rsqrtf(var + ph.eps);
-  float4 o;
-  o.x = a0 * rstd * wv.x + bv.x;
-  o.y = a1 * rstd * wv.y + bv.y;
-  o.z = a2 * rstd * wv.z + bv.z;
-  o.w = a3 * rstd * wv.w + bv.w;
-  store4(reinterpret_cast<bf16*>(ph.out_act) + ro, o);
+    if (s < ph.S) {
+#pragma unroll
+      for (int j = 0; j < J; ++j) { x[j].x += t[s][j].x; x[j].y += t[s][j].y; x[j].z += t[s][j].z; x[j].w += t[s][j].w; }
+    }
+  float sum = 0.0f;
+#pragma unroll
+  for (int j = 0; j < J; ++j) {
+    if (!final_norm && ph.S > 0) *reinterpret_cast<float4*>(P.h + ro + (tid_c + MEGA_CT * j) * 4) = x[j];
+    sum += x[j].x + x[j].y + x[j].z + x[j].w;
+  }
+  const float mu = block_sum_c(sum, red, cw, lane) / (float)d;
+  float sq = 0.0f;
+#pragma unroll
+  for (int j = 0; j < J; ++j) {
+    x[j].x -= mu; x[j].y -= mu; x[j].z -= mu; x[j].w -= mu;
+    sq += x[j].x * x[j].x + x[j].y * x[j].y + x[j].z * x[j].z + x[j].w * x[j].w;
+  }
+  const float rstd = rsqrtf(block_sum_c(sq, red + 8, cw, lane) / (float)d + ph.eps);
+  float dot = 0.0f;
+#pragma unroll
+  for (int j = 0; j < J; ++j) {
+    const int c = (tid_c + MEGA_CT * j) * 4;
+    float4 o;
+    o.x = x[j].x * rstd * wv[j].x + bv[j].x;
+    o.y = x[j].y * rstd * wv[j].y + bv[j].y;
+    o.z = x[j].z * rstd * wv[j].z + bv[j].z;
+    o.w = x[j].w * rstd * wv[j].w + bv[j].w;
+    store4(reinterpret_cast<bf16*>(ph.out_act) + ro + c, o);
+    if (final_norm) {
+      const float4 ev = *reinterpret_cast<const float4*>(P.eos_w + c);
+      dot += o.x * ev.x + o.y * ev.y + o.z * ev.z + o.w * ev.w;
+    }
+  }
   if (final_norm) {
-    const float4 ev = *reinterpret_cast<const float4*>(P.eos_w + c);
-    const float dot = block_sum8(o.x * ev.x + o.y * ev.y + o.z * ev.z + o.w * ev.w, red + 16, cw, lane);
+    dot = block_sum_c(dot, red + 16, cw, lane);
     if (tid_c == 0) {
       P.eos_logit[row] = dot + P.eos_b[0];
       P.offsets[P.slot_ids[row]] += 1;   // every attention phase of this step has already read it
@@ -341,38 +382,40 @@ __device__ void row_res_ln(const MegaParams& P, const MegaPhase& ph, int row, in
 }
 
 // items [0, n): cemb = cond_embed(c) (+bias), sy = SiLU(cemb + (te(s)+te(t))/2) (mlp.py:203-208), x = noise on the
-// first LSD step (flow_lm.py:32-40); items [n, 2n): u = input_proj(x) (mlp.py:202).  Width 512: two floats per thread.
+// first LSD step (flow_lm.py:32-40); items [n, 2n): u = input_proj(x) (mlp.py:202).  Width 512: one float4 per thread.
+static_assert(MEGA_CT * 4 == 512, "flow-head row ops assume one float4 per compute thread");
 __device__ void row_sy(const MegaParams& P, const MegaPhase& ph, int item, int tid_c, int lane) {
   const int F = P.F;
-  const int c = tid_c * 2;
+  const int c = tid_c * 4;
   if (item < P.n) {
     const int row = item;
     const size_t ro = (size_t)row * F + c, slab = (size_t)P.rows_pad * F;
-    float2 x;
+    float4 x;
     if (ph.flag) {
-      float2 t[8];
+      float4 t[8];
 #pragma unroll
       for (int s = 0; s < 8; ++s)
-        if (s < ph.S) t[s] = ldcg2(ph.part + (size_t)s * slab + ro);
-      x = *reinterpret_cast<const float2*>(P.cond_b + c);
+        if (s < ph.S) t[s] = ldcg4(ph.part + (size_t)s * slab + ro);
+      x = *reinterpret_cast<const float4*>(P.cond_b + c);
 #pragma unroll
       for (int s = 0; s < 8; ++s)
-        if (s < ph.S) { x.x += t[s].x; x.y += t[s].y; }
-      *reinterpret_cast<float2*>(P.cemb + ro) = x;
+        if (s < ph.S) { x.x += t[s].x; x.y += t[s].y; x.z += t[s].z; x.w += t[s].w; }
+      *reinterpret_cast<float4*>(P.cemb + ro) = x;
       if (tid_c < P.Ld / 4) *reinterpret_cast<float4*>(P.x_lat + (size_t)row * P.Ld + tid_c * 4) = ldcg4(P.noise + (size_t)row * P.Ld + tid_c * 4);
     } else {
-      x = ldcg2(P.cemb + ro);
+      x = ldcg4(P.cemb + ro);
     }
-    const float2 tc = *reinterpret_cast<const float2*>(P.tcomb + (size_t)ph.idx * F + c);
-    store2(reinterpret_cast<bf16*>(ph.out_act) + ro, make_float2(silu_f(x.x + tc.x), silu_f(x.y + tc.y)));
+    const float4 tc = *reinterpret_cast<const float4*>(P.tcomb + (size_t)ph.idx * F + c);
+    store4(reinterpret_cast<bf16*>(ph.out_act) + ro,
+           make_float4(silu_f(x.x + tc.x), silu_f(x.y + tc.y), silu_f(x.z + tc.z), silu_f(x.w + tc.w)));
   } else {
     const int row = item - P.n;
     const float* xs = ph.flag ? P.noise : P.x_lat;
     const float xl = lane < P.Ld ? __ldcg(xs + (size_t)row * P.Ld + lane) : 0.0f;
-    float o[2];
-    dot_rows32<2>(P.w_ip, c, xl, o);
-    const float2 b2 = *reinterpret_cast<const float2*>(P.b_ip + c);
-    *reinterpret_cast<float2*>(P.u + (size_t)row * F + c) = make_float2(o[0] + b2.x, o[1] + b2.y);
+    float o[4];
+    dot_rows32<4>(P.w_ip, c, xl, o);
+    const float4 b4 = *reinterpret_cast<const float4*>(P.b_ip + c);
+    *reinterpret_cast<float4*>(P.u + (size_t)row * F + c) = make_float4(o[0] + b4.x, o[1] + b4.y, o[2] + b4.z, o[3] + b4.w);
   }
 }
 
@@ -380,37 +423,38 @@ __device__ void row_sy(const MegaParams& P, const MegaPhase& ph, int item, int t
 // (mlp.py:49-55) and modulate(x, shift, scale) (mlp.py:16-17) -> bf16 operand of the next GEMM
 __device__ void row_lnmod(const MegaParams& P, const MegaPhase& ph, int row, int tid_c, int cw, int lane, float* red) {
   const int F = P.F;
-  const int c = tid_c * 2;
+  const int c = tid_c * 4;
   const size_t ro = (size_t)row * F + c, slab = (size_t)P.rows_pad * F, mo = (size_t)row * ph.mod_ld + c;
-  float2 x = ldcg2(P.u + ro);
-  const float2 sh = ldcg2(ph.shift + mo), sc = ldcg2(ph.scale + mo);
+  float4 x = ldcg4(P.u + ro);
+  const float4 sh = ldcg4(ph.shift + mo), sc = ldcg4(ph.scale + mo);
   if (ph.flag) {
-    float2 t[8];
+    float4 t[8];
 #pragma unroll
     for (int s = 0; s < 8; ++s)
-      if (s < ph.S) t[s] = ldcg2(ph.part + (size_t)s * slab + ro);
-    const float2 gt = ldcg2(ph.gate + mo);
-    float2 y = *reinterpret_cast<const float2*>(ph.bias + c);
+      if (s < ph.S) t[s] = ldcg4(ph.part + (size_t)s * slab + ro);
+    const float4 gt = ldcg4(ph.gate + mo);
+    float4 y = *reinterpret_cast<const float4*>(ph.bias + c);
 #pragma unroll
     for (int s = 0; s < 8; ++s)
-      if (s < ph.S) { y.x += t[s].x; y.y += t[s].y; }
-    x.x = fmaf(gt.x, y.x, x.x);
-    x.y = fmaf(gt.y, y.y, x.y);
-    *reinterpret_cast<float2*>(P.u + ro) = x;
+      if (s < ph.S) { y.x += t[s].x; y.y += t[s].y; y.z += t[s].z; y.w += t[s].w; }
+    x.x = fmaf(gt.x, y.x, x.x); x.y = fmaf(gt.y, y.y, x.y);
+    x.z = fmaf(gt.z, y.z, x.z); x.w = fmaf(gt.w, y.w, x.w);
+    *reinterpret_cast<float4*>(P.u + ro) = x;
   }
-  const float mu = block_sum8(x.x + x.y, red, cw, lane) / (float)F;
-  const float a0 = x.x - mu, a1 = x.y - mu;
-  const float var = block_sum8(a0 * a0 + a1 * a1, red + 8, cw, lane) / (float)F;
+  const float mu = block_sum_c(x.x + x.y + x.z + x.w, red, cw, lane) / (float)F;
+  const float a0 = x.x - mu, a1 = x.y - mu, a2 = x.z - mu, a3 = x.w - mu;
+  const float var = block_sum_c(a0 * a0 + a1 * a1 + a2 * a2 + a3 * a3, red + 8, cw, lane) / (float)F;
   const float den = sqrtf(var + ph.eps);
-  float2 o = make_float2(a0 / den, a1 / den);
+  float4 o = make_float4(a0 / den, a1 / den, a2 / den, a3 / den);
   if (ph.w) {
-    const float2 wv = *reinterpret_cast<const float2*>(ph.w + c), bv = *reinterpret_cast<const float2*>(ph.b + c);
-    o.x = o.x * wv.x + bv.x;
-    o.y = o.y * wv.y + bv.y;
+    const float4 wv = *reinterpret_cast<const float4*>(ph.w + c), bv = *reinterpret_cast<const float4*>(ph.b + c);
+    o.x = o.x * wv.x + bv.x; o.y = o.y * wv.y + bv.y; o.z = o.z * wv.z + bv.z; o.w = o.w * wv.w + bv.w;
   }
   o.x = o.x * (1.0f + sc.x) + sh.x;
   o.y = o.y * (1.0f + sc.y) + sh.y;
-  store2(reinterpret_cast<bf16*>(ph.out_act) + ro, o);
+  o.z = o.z * (1.0f + sc.z) + sh.z;
+  o.w = o.w * (1.0f + sc.w) + sh.w;
+  store4(reinterpret_cast<bf16*>(ph.out_act) + ro, o);
 }
 
 // Euler step x += (final_layer partials + bias) / lsd (flow_lm.py:36-39); last step: the latent is fed back
@@ -620,6 +664,23 @@ __device__ void attn_item(const MegaParams& P, const MegaPhase& ph, int item, in
   }
 }
 
+// While a QKV GEMM phase streams its weights, the compute warps pull the K/V rows their attention items of the same
+// layer will read into L2 (the cached positions do not depend on this step): the attention phase then reads L2.
+__device__ void kv_prefetch_l2(const MegaParams& P, int layer, int n_items, int cw, int lane) {
+  const KvGeom& g = P.kv;
+  for (int item = blockIdx.x + P.G * cw; item < n_items; item += P.G * MEGA_NCW) {
+    const int i = item / P.H, h = item - i * P.H;
+    const int slot = P.slot_ids[i];
+    const int L = P.offsets[slot];
+    const char* k0 = reinterpret_cast<const char*>(g.base) + ((((size_t)layer * g.n_slots + slot) * 2) * P.H + h) * (size_t)g.cap * 128;
+    const char* v0 = k0 + (size_t)P.H * g.cap * 128;
+    for (int p = lane; p < L; p += 32) {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(k0 + (size_t)p * 128));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(v0 + (size_t)p * 128));
+    }
+  }
+}
+
 // ------------------------------------------------------------------ compute warps: phase loop
 __device__ __forceinline__ void phase_prefetch(const MegaParams& P, MegaPhase* sph, int p, int tid_c) {
   // asynchronous 16-byte copies of phase p's descriptor into its shared-memory slot (completed by cp.async.wait_all)
@@ -633,15 +694,15 @@ __device__ __forceinline__ void phase_prefetch(const MegaParams& P, MegaPhase* s
 
 __device__ void compute_role(const MegaParams& P, uint32_t tfull_a, uint32_t tempty_a, uint32_t tmem_base, float* red,
                              MegaPhase* sph, int warp, int lane) {
-  const int cw = warp - 2;                  // 0..7
-  const int tid_c = cw * 32 + lane;         // 0..255
-  const int q = warp & 3, half = cw >> 2;   // TMEM lane quarter of this warp, column half
+  const int cw = warp - 2;                       // 0..NCW-1
+  const int tid_c = cw * 32 + lane;
+  const int q = warp & 3, half = cw >> 2;        // TMEM lane quarter of this warp, column interleave among its peers
   uint32_t acc = 0;
   int done_upto = 0;
   if (P.trace && tid_c == 0) P.trace[(size_t)blockIdx.x * (P.n_phases + 1)] = globaltimer_ns();
   phase_prefetch(P, sph, 0, tid_c);
   asm volatile("cp.async.wait_all;" ::: "memory");
-  asm volatile("bar.sync 1, 256;" ::: "memory");
+  cta_sync_phase();
   for (int p = 0; p < P.n_phases; ++p) {
     // the descriptor of this phase sits in shared memory (fetched during the previous phase); fetch the next one
     const MegaPhase& ph = sph[p & 1];
@@ -649,6 +710,7 @@ __device__ void compute_role(const MegaParams& P, uint32_t tfull_a, uint32_t tem
     const int type = ph.type;
     const int n_items = ph.n_items >= 0 ? ph.n_items : -ph.n_items * P.n;   // negative: items per stream row
     if (type == MP_GEMM) {
+      if (ph.flag) kv_prefetch_l2(P, ph.idx, P.H * P.n, cw, lane);
       for (int item = blockIdx.x; item < n_items; item += P.G, ++acc) {
         Item it;
         decode_item(&ph, item, it);
@@ -661,35 +723,38 @@ __device__ void compute_role(const MegaParams& P, uint32_t tfull_a, uint32_t tem
         __syncwarp();
         if (lane == 0) mbar_arrive_a(tempty_a + 8u * buf);
       }
+    } else if (type == MP_ROWS && ph.op == MR_EMBED) {
+      const int first = blockIdx.x + P.G * cw;
+      if (first < n_items) {
+        grid_wait(P, p, done_upto, lane, 0x50000u + (unsigned)p);
+        for (int item = first; item < n_items; item += P.G * MEGA_NCW) row_embed(P, item, lane);
+      }
     } else if (type == MP_ROWS) {
       if ((int)blockIdx.x < n_items) {
         if (cw == 0) grid_wait(P, p, done_upto, lane, 0x50000u + (unsigned)p);
-        asm volatile("bar.sync 5, 256;" ::: "memory");
+        cta_sync_start();
         done_upto = p;
         for (int item = blockIdx.x; item < n_items; item += P.G) {
           switch (ph.op) {
-            case MR_EMBED: row_embed(P, item, tid_c, lane); break;
             case MR_RES_LN: row_res_ln(P, ph, item, tid_c, cw, lane, red, false); break;
             case MR_FINAL: row_res_ln(P, ph, item, tid_c, cw, lane, red, true); break;
             case MR_SY: row_sy(P, ph, item, tid_c, lane); break;
             case MR_LNMOD: row_lnmod(P, ph, item, tid_c, cw, lane, red); break;
             default: row_commit(P, ph, item, tid_c); break;
           }
-          if (item + P.G < n_items) asm volatile("bar.sync 5, 256;" ::: "memory");   // reduction scratch reuse
+          if (item + P.G < n_items) cta_sync_start();   // reduction scratch reuse
         }
       }
     } else {
-      if ((int)blockIdx.x < n_items) {
-        // item, slot and position of this warp's first item do not depend on this step: fetch them before the wait
-        int item = blockIdx.x + P.G * cw;
-        int slot = 0, pos = 0;
-        if (item < n_items) { slot = P.slot_ids[item / P.H]; pos = P.offsets[slot]; }
-        if (cw == 0) grid_wait(P, p, done_upto, lane, 0x60000u + (unsigned)p);
-        asm volatile("bar.sync 5, 256;" ::: "memory");
-        done_upto = p;
-        for (; item < n_items; item += P.G * 8) {
+      // item, slot and position of this warp's first item do not depend on this step: fetch them before the wait
+      int item = blockIdx.x + P.G * cw;
+      if (item < n_items) {
+        int slot = P.slot_ids[item / P.H];
+        int pos = P.offsets[slot];
+        grid_wait(P, p, done_upto, lane, 0x60000u + (unsigned)p);
+        for (; item < n_items; item += P.G * MEGA_NCW) {
           attn_item(P, ph, item, slot, pos, lane);
-          const int nx = item + P.G * 8;
+          const int nx = item + P.G * MEGA_NCW;
           if (nx < n_items) { slot = P.slot_ids[nx / P.H]; pos = P.offsets[slot]; }
         }
       }
@@ -697,16 +762,15 @@ __device__ void compute_role(const MegaParams& P, uint32_t tfull_a, uint32_t tem
     // phase p of this CTA is done: the CTA barrier orders every compute thread's writes before thread 0's
     // gpu-scope release (cumulative), which counts the CTA in
     asm volatile("cp.async.wait_all;" ::: "memory");
-    asm volatile("bar.sync 1, 256;" ::: "memory");
+    cta_sync_phase();
     if (tid_c == 0) {
-      __threadfence();
       red_release_u32(P.sync + p);
       if (P.trace) P.trace[(size_t)blockIdx.x * (P.n_phases + 1) + p + 1] = globaltimer_ns();
     }
   }
 }
 
-__global__ void __launch_bounds__(MEGA_THREADS, 1) flow_mega_kernel(const __grid_constant__ MegaParams P) {
+__global__ void __launch_bounds__(MEGA_THREADS, 2) flow_mega_kernel(const __grid_constant__ MegaParams P) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const uint32_t stage_bytes = (uint32_t)P.a_bytes + MEGA_W_BYTES;
@@ -721,7 +785,7 @@ __global__ void __launch_bounds__(MEGA_THREADS, 1) flow_mega_kernel(const __grid
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < P.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], 8); }
+    for (int b = 0; b < 2; ++b) { mbar_init(&tfull_bar[b], 1); mbar_init(&tempty_bar[b], MEGA_NCW); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {

@@ -730,7 +730,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     R.tiles_n = (p.N + bn - 1) / bn;
     R.n_tiles = tiles_m * R.tiles_n;
     const size_t stage = (size_t)(BM_TC + bn) * 128;
-    const size_t budget = (2 * stage + EPI_SMEM_BYTES <= TC_ROWS_SMEM) ? TC_ROWS_SMEM : TC_SMEM_LIMIT;
+    static const size_t rows_smem = [] { const char* e = getenv("PTTS_TC_ROWS_SMEM_KB"); return e ? (size_t)atoi(e) * 1024 : TC_ROWS_SMEM; }();
+    const size_t budget = (2 * stage + EPI_SMEM_BYTES <= rows_smem) ? rows_smem : TC_SMEM_LIMIT;
     R.stages = (int)std::max<size_t>(2, std::min<size_t>(6, (budget - EPI_SMEM_BYTES) / stage));
     if (!tc_make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, BM_TC)) return cudaErrorUnknown;
     if (!tc_make_map(&tw, p.W, p.N, p.K, p.K, bn)) return cudaErrorUnknown;
