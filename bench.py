@@ -186,6 +186,26 @@ def run_ours(args, rank, world, local_rank):
     h2d = B * dims.ldim * 4
     d2h = B * (dims.ldim * 4 + 4 + dims.frame_samples * 4)
 
+    # ---------------- first-chunk latency: text prefill + first FlowLM step + first Mimi frame, PCM on the host ------
+    # (the voice prefix is already in the slot, as with the reference's built-in voice states; tts_model.py:718-779)
+    first_chunk = {}
+    if rank == 0:
+        for label, nb in (("batch", B), ("single", 1)):
+            times = []
+            for trial in range(7):
+                tokens, voice, noise = synth_inputs(dims, nb, 1, 50 + trial)
+                sl = [eng.open_stream() for _ in range(nb)]
+                eng.prefill(sl, [torch.cat([bos, voice[i]]) for i in range(nb)])
+                text = [emb[tokens[i]] for i in range(nb)]
+                nz = noise[0].pin_memory()
+                eng.synchronize()
+                t0 = time.perf_counter()
+                eng.prefill(sl, text)
+                eng.step(sl, nz)                                   # returns latents, EOS logits and PCM on the host
+                times.append((time.perf_counter() - t0) * 1e3)
+                close(sl)
+            first_chunk[f"p50_ms_{label}_{nb}"] = round(statistics.median(times[2:]), 3)
+
     # ---------------- per-kernel CUDA-event pass (roofline of the dominant kernel) ----------------
     prof = {}
     if rank == 0:
@@ -252,6 +272,7 @@ def run_ours(args, rank, world, local_rank):
                 "ms_per_step": round(e2e_ms / K, 4),
                 "api": "ptts_generate_frames (pinned host noise in; latents, EOS logits, PCM out per frame) via GenerationEngine.generate_frames",
                 "blocking_step_api_ms_per_step": round(step_api_ms, 4)},
+        "first_chunk": first_chunk,
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
         "step_roofline": {"bound": "hbm", "algorithmic_bytes_per_step": int(step_bytes), "frac_of_hbm_peak": round(step_frac, 4)},
         "cpu_baseline": cpu,

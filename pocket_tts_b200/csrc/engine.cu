@@ -50,6 +50,9 @@ Engine::~Engine() {
       if (e) cudaEventDestroy(e);
   }
   if (copy_stream) cudaStreamDestroy(copy_stream);
+  if (ev_side_fork) cudaEventDestroy(ev_side_fork);
+  if (ev_side_join) cudaEventDestroy(ev_side_join);
+  if (side_stream) cudaStreamDestroy(side_stream);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream) cudaStreamDestroy(stream);
 }
@@ -101,6 +104,10 @@ int Engine::init() {
   if (const char* f = getenv("PTTS_FORCE_SIMT")) use_tc = !(f[0] == '1');
   if (const char* f = getenv("PTTS_MIMI_GROUP")) mimi_gmax = std::max(1, std::min(8, atoi(f)));
   PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&copy_stream, cudaStreamNonBlocking, prio_lo));
+  PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&side_stream, cudaStreamNonBlocking, prio_hi));
+  PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_fork, cudaEventDisableTiming));
+  PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_join, cudaEventDisableTiming));
+  if (const char* f = getenv("PTTS_SIDE")) use_side_branch = !(f[0] == '0');
   for (int k = 0; k < 2; ++k) {
     for (cudaEvent_t* e : {&ev_lat[k], &ev_mimi[k], &ev_copied_lat[k], &ev_copied_pcm[k]})
       PTTS_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));

@@ -171,6 +171,7 @@ class Engine {
   std::vector<LayerW> flow_layers, mimi_layers;
   Mat cond_embed, input_proj, mod_all, final_lin;
   float *cond_b, *inproj_b, *mod_b, *final_b;
+  float* cond_b_t0 = nullptr;   // cond_embed bias + (te(s)+te(t))/2 of LSD step 0: lsd_steps == 1 folds SiLU into the GEMM
   std::vector<FlowBlockW> flow_blocks;
   float *wq, *wup;
   Mat conv0; float* conv0_b;
@@ -217,6 +218,9 @@ class Engine {
   float* noise_grp = nullptr;                // [mimi_gmax][S][ldim]
   float* eos_grp[2] = {nullptr, nullptr};    // [mimi_gmax][S]
   int mimi_gmax = 4;                         // frames per Mimi pass in the pipelined loop (PTTS_MIMI_GROUP)
+  cudaStream_t side_stream = nullptr;        // side branch of the FlowLM graph (input_proj of the first Euler step)
+  cudaEvent_t ev_side_fork = nullptr, ev_side_join = nullptr;
+  bool use_side_branch = true;               // PTTS_SIDE=0 disables
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph
   cudaEvent_t ev_lat[2] = {}, ev_mimi[2] = {}, ev_copied_lat[2] = {}, ev_copied_pcm[2] = {};
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)

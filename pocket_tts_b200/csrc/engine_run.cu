@@ -92,27 +92,48 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
   const int modld = (c.flow_depth * 3 + 2) * F;
   int rc;
   if (mega_eligible(n)) return flow_sequence_mega(n, lsd, noise, eos_out);
+  // u = input_proj(x_0) of the first Euler step depends on nothing but the noise: it runs on a side branch beside
+  // the transformer layers instead of sitting in the dependent chain of the flow head
+  const bool side_u = use_side_branch && side_stream != nullptr;
+  if (side_u) {
+    PTTS_CUDA_CHECK(cudaEventRecord(ev_side_fork, stream));
+    PTTS_CUDA_CHECK(cudaStreamWaitEvent(side_stream, ev_side_fork, 0));
+    cudaStream_t main_stream = stream;
+    stream = side_stream;
+    GemmEpilogue ep; ep.bias = inproj_b; ep.out = u; ep.out_map = plain(F);
+    rc = gemm("head.input_proj", noise, false, plain(Ld), input_proj, n, ep, false);
+    stream = main_stream;
+    if (rc != PTTS_OK) return rc;
+    PTTS_CUDA_CHECK(cudaEventRecord(ev_side_join, side_stream));
+  }
   LAUNCH("flow.embed", launch_flow_embed(prev_latent, d_slot_ids, bos_emb, w_in, h, n, D, Ld, stream));
   for (int l = 0; l < c.n_layers; ++l)
     if ((rc = transformer_layer_common(flow_layers[l], h, n, D, c.ffn, a_ln, qkv, attn_o, mid, false, l, n)) != PTTS_OK)
       return rc;
-  LAUNCH("flow.final_norm_eos", launch_final_norm_eos(h, out_norm_w, out_norm_b, 1e-5f, eos_w, eos_b, c_cond, act_type, eos_out, n, D, stream));
-  LAUNCH("advance", launch_advance(offsets, d_slot_ids, nullptr, 1, n, stream));
-  // LSD / Euler integration from the injected noise (flow_lm.py:32-40)
-  PTTS_CUDA_CHECK(cudaMemcpyAsync(x_lat, noise, (size_t)n * Ld * sizeof(float), cudaMemcpyDeviceToDevice, stream));
-  {
+  // out_norm + EOS logit; the stream offsets advance here (every attention kernel of the step has read them)
+  LAUNCH("flow.final_norm_eos", launch_final_norm_eos(h, out_norm_w, out_norm_b, 1e-5f, eos_w, eos_b, c_cond, act_type, eos_out, n, D, stream, offsets, d_slot_ids));
+  // LSD / Euler integration from the injected noise (flow_lm.py:32-40).  x_0 = noise is read in place: the first
+  // input_proj takes `noise` as its operand and the first Euler update writes x_lat = noise + v / lsd.
+  const bool fused_sy = lsd == 1 && cond_b_t0 != nullptr;
+  if (fused_sy) {   // sy = SiLU(cond_embed(c) + b + (te(s)+te(t))/2) straight out of the GEMM epilogue (mlp.py:203-208)
+    GemmEpilogue ep; ep.bias = cond_b_t0; ep.act_pre = ACT_SILU; ep.out = sy; ep.out_map = plain(F);
+    if ((rc = gemm("head.cond_embed", c_cond, true, plain(D), cond_embed, n, ep, true)) != PTTS_OK) return rc;
+  } else {
     GemmEpilogue ep; ep.bias = cond_b; ep.out = cemb; ep.out_map = plain(F);
     if ((rc = gemm("head.cond_embed", c_cond, true, plain(D), cond_embed, n, ep, false)) != PTTS_OK) return rc;
   }
   for (int s = 0; s < lsd; ++s) {
-    LAUNCH("head.silu_add", launch_silu_add(cemb, tcomb + (size_t)s * F, sy, act_type, n, F, stream));
+    const float* x_in = s == 0 ? noise : x_lat;
+    if (!fused_sy) LAUNCH("head.silu_add", launch_silu_add(cemb, tcomb + (size_t)s * F, sy, act_type, n, F, stream));
     {
       GemmEpilogue ep; ep.bias = mod_b; ep.out = mod; ep.out_map = plain(modld);
       if ((rc = gemm("head.adaln_mod", sy, true, plain(F), mod_all, n, ep, false)) != PTTS_OK) return rc;
     }
-    {
+    if (s == 0 && side_u) {
+      PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_side_join, 0));
+    } else {
       GemmEpilogue ep; ep.bias = inproj_b; ep.out = u; ep.out_map = plain(F);
-      if ((rc = gemm("head.input_proj", x_lat, false, plain(Ld), input_proj, n, ep, false)) != PTTS_OK) return rc;
+      if ((rc = gemm("head.input_proj", x_in, false, plain(Ld), input_proj, n, ep, false)) != PTTS_OK) return rc;
     }
     for (int j = 0; j < c.flow_depth; ++j) {
       const FlowBlockW& w = flow_blocks[j];
@@ -132,7 +153,7 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
     LAUNCH("head.ln_modulate", launch_ln_modulate(u, nullptr, nullptr, mf, mf + F, modld, g, act_type, n, F, stream));
     {
       GemmEpilogue ep; ep.bias = final_b; ep.alpha = 1.0f / (float)lsd;
-      ep.res = x_lat; ep.res_map = plain(Ld); ep.out = x_lat; ep.out_map = plain(Ld);
+      ep.res = x_in; ep.res_map = plain(Ld); ep.out = x_lat; ep.out_map = plain(Ld);
       if ((rc = gemm("head.final", g, true, plain(F), final_lin, n, ep, false)) != PTTS_OK) return rc;
     }
   }

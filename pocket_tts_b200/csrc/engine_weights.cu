@@ -81,6 +81,13 @@ int Engine::finalize() {
   const std::string fp = "flow_lm.flow_net.";
   GETM(cond_embed, fp + "cond_embed.weight", F, D);
   GETV(cond_b, fp + "cond_embed.bias", F);
+  {
+    std::vector<float> bt(host_w[fp + "cond_embed.bias"].data);
+    const std::vector<float>& tc = host_w["flow.tcomb"].data;
+    for (int64_t j = 0; j < F; ++j) bt[j] += tc[j];
+    cond_b_t0 = upload(bt);
+    if (!cond_b_t0) PTTS_FAIL(PTTS_ECUDA, "upload failed");
+  }
   GETM(input_proj, fp + "input_proj.weight", F, L, false);  // A operand is the fp32 latent
   GETV(inproj_b, fp + "input_proj.bias", F);
   GETM(final_lin, fp + "final_layer.linear.weight", L, F);

@@ -106,7 +106,8 @@ __global__ void __launch_bounds__(128)
 final_norm_eos_kernel(const float* __restrict__ h, const float* __restrict__ w,
                       const float* __restrict__ b, float eps, const float* __restrict__ w_eos,
                       const float* __restrict__ b_eos, TO* __restrict__ c,
-                      float* __restrict__ eos_logit, int d) {
+                      float* __restrict__ eos_logit, int d, int* __restrict__ offsets,
+                      const int* __restrict__ slot_ids) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float scratch[33];
@@ -147,17 +148,22 @@ final_norm_eos_kernel(const float* __restrict__ h, const float* __restrict__ w,
     }
   }
   dot = block_sum(dot, scratch);
-  if (threadIdx.x == 0) eos_logit[row] = dot + b_eos[0];
+  if (threadIdx.x == 0) {
+    eos_logit[row] = dot + b_eos[0];
+    // the step's attention kernels have all read the stream's offset: advance it (tts_model.py:342-345)
+    if (offsets) offsets[slot_ids[row]] += 1;
+  }
 }
 
 cudaError_t launch_final_norm_eos(const float* h, const float* w, const float* b, float eps,
                                   const float* w_eos, const float* b_eos, void* c, int c_type,
-                                  float* eos_logit, int n, int d, cudaStream_t st) {
+                                  float* eos_logit, int n, int d, cudaStream_t st, int* offsets,
+                                  const int* slot_ids) {
   if (d % 4 || d > 1024) return cudaErrorInvalidValue;
   if (c_type == 0)
-    launch_k(final_norm_eos_kernel<float>, n, 128, 0, st, h, w, b, eps, w_eos, b_eos, (float*)c, eos_logit, d);
+    launch_k(final_norm_eos_kernel<float>, n, 128, 0, st, h, w, b, eps, w_eos, b_eos, (float*)c, eos_logit, d, offsets, slot_ids);
   else
-    launch_k(final_norm_eos_kernel<bf16>, n, 128, 0, st, h, w, b, eps, w_eos, b_eos, (bf16*)c, eos_logit, d);
+    launch_k(final_norm_eos_kernel<bf16>, n, 128, 0, st, h, w, b, eps, w_eos, b_eos, (bf16*)c, eos_logit, d, offsets, slot_ids);
   return cudaGetLastError();
 }
 

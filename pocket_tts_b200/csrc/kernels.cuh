@@ -50,7 +50,8 @@ cudaError_t launch_advance(int* offsets, const int* slot_ids, const int* inc, in
 // flow_lm.py:128-129,153-154
 cudaError_t launch_final_norm_eos(const float* h, const float* w, const float* b, float eps,
                                   const float* w_eos, const float* b_eos, void* c, int c_type,
-                                  float* eos_logit, int n, int d, cudaStream_t st);
+                                  float* eos_logit, int n, int d, cudaStream_t st, int* offsets = nullptr,
+                                  const int* slot_ids = nullptr);
 
 // sy = silu(cemb + tcomb_row) (mlp.py:209, 99-100 SiLU of adaLN_modulation)
 cudaError_t launch_silu_add(const float* cemb, const float* tcomb_row, void* sy, int sy_type,
