@@ -6,6 +6,8 @@
 // (2*lane, 2*lane+1) of the 64-wide head, so a K or V row is one coalesced 256 B (fp32) /
 // 128 B (bf16) warp load, the rotation needs no shuffles, and the score is a 5-step
 // butterfly.  Warps split the positions and are merged with a log-sum-exp combine.
+#include <cstdlib>
+
 #include "kernels.cuh"
 
 namespace ptts {
@@ -487,6 +489,10 @@ attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   }
 }
 
+}  // namespace ptts
+#include "attn_window_mma.cuh"
+namespace ptts {
+
 cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets, const int* slot_ids,
                                KvGeom kv, int layer, int context, int T, void* out, int out_type, int n,
                                cudaStream_t st, int frames) {
@@ -494,6 +500,21 @@ cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const 
   if (context + frames * T > kv.cap) return cudaErrorInvalidValue;   // a pass must not wrap onto keys it still reads
   const int maxw = ((context + T - 1 + 7) / 8) * 8;
   if (maxw > 288 || maxw > kv.cap) return cudaErrorInvalidValue;
+  const char* env_mma = getenv("PTTS_WIN_MMA");   // read per call: the tests compare both kernels in one process
+  const bool use_mma = !env_mma || atoi(env_mma) != 0;
+  const int NQ = frames * T;
+  if (use_mma && kv.type == 1 && out_type == 1 && T == 16 && NQ <= 64 && context - 1 + NQ <= WM_MAXW) {
+    static bool attr = false;
+    if (!attr) {
+      cudaError_t e = cudaFuncSetAttribute(attn_window_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)attn_window_mma_smem());
+      if (e != cudaSuccess) return e;
+      attr = true;
+    }
+    launch_k(attn_window_mma_kernel, dim3(kv.H, n), WM_THREADS, attn_window_mma_smem(), st, qkv, rope_freqs, offsets,
+             slot_ids, kv, layer, context, NQ, (bf16*)out);
+    return cudaGetLastError();
+  }
   dim3 grid(kv.H, n, frames);
   const int ld = kv.type == 1 ? KvWords<bf16>::LD : KvWords<float>::LD;
   const size_t smem = ((size_t)2 * maxw * ld + (size_t)16 * maxw + 16 * 64) * 4;

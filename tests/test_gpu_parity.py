@@ -88,6 +88,24 @@ def test_mimi_20_frames_vs_reference_fixture():
     eng.close()
 
 
+def test_mimi_bf16_tensor_core_window_attention(monkeypatch):
+    """bf16 Mimi: the mma.sync window attention (default) against the fixture and against the SIMT kernel
+    (PTTS_WIN_MMA=0) on the same 20 frames — 320 tokens, so the 250-token window and the ring wrap are exercised."""
+    g = np.load("tests/golden/mimi_20f.npz")
+    lat = torch.from_numpy(g["latents"])
+    ref = torch.from_numpy(g["pcm"])
+    snr = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("PTTS_WIN_MMA", mode)
+        eng = make_engine(1, precision="bf16")
+        s = eng.open_stream()
+        pcm = torch.cat([eng.mimi_decode([s], lat[i][None]) for i in range(lat.shape[0])], dim=1)[0]
+        snr[mode] = po.snr_db(ref, pcm)
+        eng.close()
+    print(f"bf16 mimi 20 frames: SNR tensor-core attention {snr['1']:.1f} dB, SIMT attention {snr['0']:.1f} dB")
+    assert snr["1"] >= 20.0 and snr["1"] >= snr["0"] - 3.0
+
+
 def test_voice_kv_export_matches_reference_cache():
     case = load_case("gen_2l")
     orc = oracle_for(2)
@@ -185,13 +203,23 @@ def test_pipelined_run_frames_equals_step_sequence(precision):
     eng.run_frames(b, noise.cuda().contiguous(), out_pcm=pcm_b, out_latents=lat_b)
     eng.synchronize()
     assert torch.equal(lat_a, lat_b.cpu())
-    assert torch.equal(pcm_a, pcm_b.cpu())
+    if precision == "fp32":
+        assert torch.equal(pcm_a, pcm_b.cpu())
+    else:
+        # the bf16 window attention splits the keys among warps by pass size (1 frame: 4 key splits, 4 frames:
+        # none), so grouped passes differ from single-frame ones in the last bits of the fp32 accumulation
+        snr = min(po.snr_db(pcm_a[i], pcm_b.cpu()[i]) for i in range(B))
+        print(f"bf16 grouped vs single-frame Mimi passes: min SNR {snr:.1f} dB")
+        assert snr >= 35.0
     # a second call continues the same streams (pipeline was drained at the end of the first)
     lat2, _, pcm2 = eng.step(a, noise[0])
     pcm_c = torch.empty(B, 1920, device="cuda")
     eng.run_frames(b, noise[:1].cuda().contiguous(), out_pcm=pcm_c)
     eng.synchronize()
-    assert torch.equal(pcm2, pcm_c.cpu())
+    if precision == "fp32":
+        assert torch.equal(pcm2, pcm_c.cpu())
+    else:
+        assert min(po.snr_db(pcm2[i], pcm_c.cpu()[i]) for i in range(B)) >= 35.0
     eng.close()
 
 
