@@ -40,3 +40,14 @@ def load_case(name: str):
 
 def oracle_for(n_layers: int, lsd=1):
     return po.Oracle(po.ModelDims(n_layers=n_layers), weights(n_layers), lsd_steps=lsd)
+
+
+class CharTokenizer:
+    """Reversible toy tokenizer for the API-level fixtures (one id per character, ids < n_bins):
+    stands in for the sentencepiece model, which is a network download in the reference."""
+
+    def encode(self, text: str) -> list:
+        return [ord(c) % 4000 for c in text]
+
+    def decode(self, ids) -> str:
+        return "".join(chr(int(i)) for i in ids)
