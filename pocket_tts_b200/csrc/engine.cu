@@ -108,6 +108,7 @@ int Engine::init() {
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_fork, cudaEventDisableTiming));
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_join, cudaEventDisableTiming));
   if (const char* f = getenv("PTTS_SIDE")) use_side_branch = !(f[0] == '0');
+  if (const char* f = getenv("PTTS_HEAD")) use_head_cluster = !(f[0] == '0');
   for (int k = 0; k < 2; ++k) {
     for (cudaEvent_t* e : {&ev_lat[k], &ev_mimi[k], &ev_copied_lat[k], &ev_copied_pcm[k]})
       PTTS_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));

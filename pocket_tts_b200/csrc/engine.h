@@ -221,6 +221,7 @@ class Engine {
   cudaStream_t side_stream = nullptr;        // side branch of the FlowLM graph (input_proj of the first Euler step)
   cudaEvent_t ev_side_fork = nullptr, ev_side_join = nullptr;
   bool use_side_branch = true;               // PTTS_SIDE=0 disables
+  bool use_head_cluster = true;              // PTTS_HEAD=0: flow head as separate launches instead of the cluster kernel (flow_head.cu)
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph
   cudaEvent_t ev_lat[2] = {}, ev_mimi[2] = {}, ev_copied_lat[2] = {}, ev_copied_pcm[2] = {};
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)

@@ -94,7 +94,9 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
   if (mega_eligible(n)) return flow_sequence_mega(n, lsd, noise, eos_out);
   // u = input_proj(x_0) of the first Euler step depends on nothing but the noise: it runs on a side branch beside
   // the transformer layers instead of sitting in the dependent chain of the flow head
-  const bool side_u = use_side_branch && side_stream != nullptr;
+  // bf16 mode: everything after the AdaLN modulation GEMM of an Euler step is one cluster kernel (flow_head.cu)
+  const bool head_cluster = use_head_cluster && act_type == 1 && use_tc && flow_head_cluster_supported(F, Ld, c.flow_depth);
+  const bool side_u = use_side_branch && side_stream != nullptr && !head_cluster;
   if (side_u) {
     PTTS_CUDA_CHECK(cudaEventRecord(ev_side_fork, stream));
     PTTS_CUDA_CHECK(cudaStreamWaitEvent(side_stream, ev_side_fork, 0));
@@ -129,6 +131,22 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
       GemmEpilogue ep; ep.bias = mod_b; ep.out = mod; ep.out_map = plain(modld);
       if ((rc = gemm("head.adaln_mod", sy, true, plain(F), mod_all, n, ep, false)) != PTTS_OK) return rc;
     }
+    if (head_cluster) {
+      FlowHeadParams hp{};
+      for (int j = 0; j < c.flow_depth; ++j) {
+        const FlowBlockW& w = flow_blocks[j];
+        hp.blk[j] = FlowHeadBlock{w.mlp0.b16, w.mlp2.b16, w.b0, w.b2, w.lnw, w.lnb};
+      }
+      hp.depth = c.flow_depth; hp.n = n; hp.ldim = Ld; hp.mod_ld = modld;
+      hp.x_in = x_in; hp.w_in = input_proj.f32; hp.b_in = inproj_b; hp.mod = mod;
+      hp.w_final = final_lin.b16; hp.b_final = final_b; hp.alpha = 1.0f / (float)lsd; hp.x_out = x_lat;
+      hp.slot_ids = d_slot_ids;
+      const bool last = s == lsd - 1;
+      hp.prev_latent = last ? prev_latent : nullptr;
+      hp.commit_out = last ? commit_out : nullptr;
+      LAUNCH("head.cluster", launch_flow_head_cluster(hp, stream));
+      continue;
+    }
     if (s == 0 && side_u) {
       PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_side_join, 0));
     } else {
@@ -157,7 +175,7 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
       if ((rc = gemm("head.final", g, true, plain(F), final_lin, n, ep, false)) != PTTS_OK) return rc;
     }
   }
-  LAUNCH("head.commit", launch_commit_latent(x_lat, d_slot_ids, prev_latent, commit_out, n, Ld, stream));
+  if (!head_cluster) LAUNCH("head.commit", launch_commit_latent(x_lat, d_slot_ids, prev_latent, commit_out, n, Ld, stream));
   return PTTS_OK;
 }
 

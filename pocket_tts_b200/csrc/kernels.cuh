@@ -62,6 +62,31 @@ cudaError_t launch_ln_modulate(const float* u, const float* w, const float* b, c
                                const float* scale, int mod_ld, void* g, int g_type, int n, int d,
                                cudaStream_t st);
 
+// One Euler step of the flow head after the AdaLN modulation GEMM, as a single cluster kernel (flow_head.cu,
+// bf16 mode, flow_dim 512, ldim 32): input_proj, the ResBlocks, the final layer and the latent commit.
+#define PTTS_HEAD_MAX_DEPTH 8
+struct FlowHeadBlock {
+  const bf16 *w0, *w2;                   // mlp.0 / mlp.2 weights [512, 512] bf16
+  const float *b0, *b2, *lnw, *lnb;
+};
+struct FlowHeadParams {
+  FlowHeadBlock blk[PTTS_HEAD_MAX_DEPTH];
+  int depth, n, ldim, mod_ld;
+  const float* x_in;                     // [n, ldim] fp32: x of this Euler step
+  const float* w_in;                     // input_proj weight [512, ldim] fp32
+  const float* b_in;
+  const float* mod;                      // [n, mod_ld] fp32: (shift | scale | gate) x depth, then shift | scale
+  const bf16* w_final;                   // [ldim, 512] bf16
+  const float* b_final;
+  float alpha;                           // 1 / lsd_steps
+  float* x_out;                          // [n, ldim]: x + alpha * v
+  const int* slot_ids;                   // commit (last Euler step): prev_latent[slot] = x_out row, optional copy
+  float* prev_latent;                    // nullable
+  float* commit_out;                     // nullable
+};
+bool flow_head_cluster_supported(int flow_dim, int ldim, int depth);
+cudaError_t launch_flow_head_cluster(const FlowHeadParams& p, cudaStream_t st);
+
 // x[i,:] -> prev_latent[slot] and out (nullable)
 cudaError_t launch_commit_latent(const float* x, const int* slot_ids, float* prev_latent,
                                  float* out, int n, int ldim, cudaStream_t st);
