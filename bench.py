@@ -264,7 +264,7 @@ def run_ours(args, rank, world, local_rank):
         "metric": "audio-sec generated per sec (RTFx), batched", "value": round(value, 1), "unit": "audio-s/s",
         "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": round(ms / K, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": prec, "data": "synthetic",
-        "config": {"workload": f"default english model ({dims.n_layers}L FlowLM), {B} concurrent streams per GPU, "
+        "config": {"workload": f"{'default english' if PRESET == 'english' else PRESET} model ({dims.n_layers}L FlowLM), {B} concurrent streams per GPU, "
                                f"voice prefix {VOICE_P} + {TEXT_T} text tokens, lsd_steps 1, frame step = FlowLM + flow head + Mimi decode",
                    "streams_per_gpu": B, "precision": prec, "parallelism": f"streams sharded x{world}, no collective",
                    "l2_policy": "working set per step (weights + KV, >= 0.6 GB) exceeds the 126 MB L2; no flush"},
@@ -379,7 +379,7 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": "audio-sec generated per sec (RTFx), batched", "value": round(value, 2),
             "unit": "audio-s/s", "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": round(dt / K * 1e3, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"default english model ({dims.n_layers}L FlowLM), {STREAMS} concurrent streams per GPU, "
+            "config": {"workload": f"{'default english' if PRESET == 'english' else PRESET} model ({dims.n_layers}L FlowLM), {STREAMS} concurrent streams per GPU, "
                                    f"voice prefix {VOICE_P} + {TEXT_T} text tokens (CPU arm: {Bs}-stream sample per step)"},
             "cpu_baseline": {"value": round(value, 2), "unit": "audio-s/s", "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": round(value, 2), "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -394,7 +394,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3"],
+                    help="cfg2: english 6L, 64 streams per GPU (the headline line); cfg3: italian_24l, 256 streams per GPU")
     args = ap.parse_args()
+    if args.workload == "cfg3":
+        global STREAMS, PRESET, N_LAYERS
+        STREAMS, PRESET, N_LAYERS = 256, "italian_24l", 24
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -87,6 +87,16 @@ __device__ __forceinline__ void attend4(OnlineSm& s, const TK* __restrict__ kbas
 template <typename TK> struct KvVec;
 template <> struct KvVec<bf16> {
   static constexpr int EPL = 8;   // elements per lane
+  typedef uint4 Raw;
+  __device__ static Raw zero() { return make_uint4(0u, 0u, 0u, 0u); }
+  __device__ static void unpack(const Raw& r, float* f) {
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 t = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[i]));
+      f[2 * i] = t.x; f[2 * i + 1] = t.y;
+    }
+  }
   __device__ static void load(const bf16* p, float* f) {
     const uint4 r = *reinterpret_cast<const uint4*>(p);
     const uint32_t w[4] = {r.x, r.y, r.z, r.w};
@@ -108,6 +118,9 @@ template <> struct KvVec<bf16> {
 };
 template <> struct KvVec<float> {
   static constexpr int EPL = 4;
+  typedef float4 Raw;
+  __device__ static Raw zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+  __device__ static void unpack(const Raw& r, float* f) { f[0] = r.x; f[1] = r.y; f[2] = r.z; f[3] = r.w; }
   __device__ static void load(const float* p, float* f) {
     const float4 r = *reinterpret_cast<const float4*>(p);
     f[0] = r.x; f[1] = r.y; f[2] = r.z; f[3] = r.w;
@@ -121,7 +134,6 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
                    const int* __restrict__ offsets, const int* __restrict__ slot_ids, KvGeom g,
                    int layer, TO* __restrict__ out) {
   pdl_launch_dependents();
-  pdl_wait();
   constexpr int NW = 4;
   constexpr int EPL = KvVec<TK>::EPL;      // dims per lane
   constexpr int LPR = 64 / EPL;            // lanes per row: 8 / 16
@@ -131,10 +143,22 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   __shared__ float sm_acc[NW][32][EPL];
   const int h = blockIdx.x, i = blockIdx.y;
   const int slot = slot_ids[i];
-  const int pos = offsets[slot];
+  const int pos = offsets[slot];           // advanced only by the last kernel of the step: stable here
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int sub = lane / LPR, ch = lane % LPR;   // row within a load, 16-byte chunk of the row
   const int d_model = g.H * 64;
+  if (g.prefetch) {
+    // The cached positions [0, pos) were written by earlier steps, not by the kernel this one waits for: pull
+    // them into L2 now, while the QKV projection (latency-bound, HBM nearly idle) is still running.
+    const char* kb = reinterpret_cast<const char*>(kv_row<TK>(g, layer, slot, 0, h, 0));
+    const char* vb = reinterpret_cast<const char*>(kv_row<TK>(g, layer, slot, 1, h, 0));
+    const int bytes = pos * 64 * (int)sizeof(TK);
+    for (int off = threadIdx.x * 128; off < bytes; off += 128 * 128) {
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(kb + off));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(vb + off));
+    }
+  }
+  pdl_wait();
   const float* row = qkv + (long long)i * 3 * d_model + h * 64 + ch * EPL;
 
   // rotate this lane's slice of q (interleaved pairs, rope.py:36-58); lanes with sub == 0 of
@@ -242,10 +266,228 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   }
 }
 
+// =====================================================================================
+// decode, bulk-copy form (default): one (stream, head) per WARP.  The warp streams the cached K and V rows of
+// its pair — two contiguous runs of pos * 128 bytes (bf16) — through a private shared-memory ring with
+// cp.async.bulk (4 KB of K + 4 KB of V per chunk, completion on an mbarrier), so the whole cache read is a
+// handful of TMA requests per warp instead of hundreds of per-lane loads, and it is issued BEFORE the kernel
+// waits for the QKV projection: cached rows do not depend on it (offsets advance only in the last kernel of a
+// step, and steps are separated by a graph / copy boundary), so under programmatic dependent launch the KV
+// stream overlaps the latency-bound GEMM in front of it.  The new position is folded in from registers (rounded
+// through the cache type, as if re-read) and appended to the cache.  No block-level synchronisation at all.
+// =====================================================================================
+constexpr int AD_CHUNK = 4096;   // bytes of K (and of V) per ring slot
+constexpr int AD_SLOTS = 2;
+
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void ad_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok = 0;
+  for (uint32_t spin = 0; spin < (1u << 22) && !ok; ++spin)
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  if (!ok) __trap();
+}
+
+template <typename TK, typename TO, int W>
+__global__ void __launch_bounds__(W * 32)
+attn_decode_bulk_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs,
+                        const int* __restrict__ offsets, const int* __restrict__ slot_ids, KvGeom g,
+                        int layer, TO* __restrict__ out, int n_tasks) {
+  constexpr int EPL = KvVec<TK>::EPL;      // dims per lane
+  constexpr int LPR = 64 / EPL;            // lanes per row: 8 / 16
+  constexpr int RPL = 32 / LPR;            // rows per warp load: 4 / 2
+  constexpr int U = 4;
+  constexpr int ROWB = 64 * (int)sizeof(TK);
+  constexpr int CR = AD_CHUNK / ROWB;      // rows per chunk: 32 / 16
+  typedef typename KvVec<TK>::Raw Raw;
+  extern __shared__ __align__(128) uint8_t ad_smem[];   // [W][AD_SLOTS][K | V][AD_CHUNK]
+  __shared__ __align__(8) uint64_t bars[W][AD_SLOTS];
+  pdl_launch_dependents();
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int task = blockIdx.x * W + w;
+  if (task >= n_tasks) return;             // whole warp; nothing below synchronises across warps
+  const int i = task / g.H, h = task - i * g.H;
+  const int slot = slot_ids[i];
+  const int pos = offsets[slot];
+  const int sub = lane / LPR, ch = lane % LPR;
+  const int d_model = g.H * 64;
+  const uint32_t ring = (uint32_t)__cvta_generic_to_shared(ad_smem) + (uint32_t)w * AD_SLOTS * 2 * AD_CHUNK;
+  const uint32_t bar0 = (uint32_t)__cvta_generic_to_shared(&bars[w][0]);
+  const char* kg = reinterpret_cast<const char*>(kv_row<TK>(g, layer, slot, 0, h, 0));
+  const char* vg = reinterpret_cast<const char*>(kv_row<TK>(g, layer, slot, 1, h, 0));
+  const int n_chunks = (pos + CR - 1) / CR;
+  auto issue = [&](int c) {                // lane 0: chunk c -> ring slot c % AD_SLOTS
+    const int s = c % AD_SLOTS;
+    const uint32_t bytes = (uint32_t)min(CR, pos - c * CR) * ROWB;
+    const uint32_t dst = ring + (uint32_t)s * 2 * AD_CHUNK, bar = bar0 + 8u * s;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(2 * bytes) : "memory");
+    bulk_g2s(dst, kg + (size_t)c * AD_CHUNK, bytes, bar);
+    bulk_g2s(dst + AD_CHUNK, vg + (size_t)c * AD_CHUNK, bytes, bar);
+  };
+  if (lane == 0) {
+    for (int s = 0; s < AD_SLOTS; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8u * s));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    for (int c = 0; c < AD_SLOTS && c < n_chunks; ++c) issue(c);
+  }
+  __syncwarp();
+  pdl_wait();
+
+  // rotate this lane's slice of q and of the new k (interleaved pairs, rope.py:36-58); lane group 0 appends
+  const float* row = qkv + (long long)i * 3 * d_model + h * 64 + ch * EPL;
+  float q[EPL], kn[EPL], vn[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; e += 2) {
+    const float fr = freqs[(ch * EPL + e) >> 1];
+    const float2 qq = rope_pair(load2(row + e), (float)pos, fr);
+    q[e] = qq.x * 0.125f; q[e + 1] = qq.y * 0.125f;   // fold the 1/sqrt(64) softmax scale into q
+    const float2 kk = rope_pair(load2(row + d_model + e), (float)pos, fr);
+    const float2 vv = load2(row + 2 * d_model + e);
+    kn[e] = to_f(from_f<TK>(kk.x)); kn[e + 1] = to_f(from_f<TK>(kk.y));   // as stored in the cache
+    vn[e] = to_f(from_f<TK>(vv.x)); vn[e + 1] = to_f(from_f<TK>(vv.y));
+  }
+  if (sub == 0) {
+    KvVec<TK>::store(kv_row<TK>(g, layer, slot, 0, h, pos) + ch * EPL, kn);
+    KvVec<TK>::store(kv_row<TK>(g, layer, slot, 1, h, pos) + ch * EPL, vn);
+  }
+
+  float m = -INFINITY, l = 0.0f, acc[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) acc[e] = 0.0f;
+  for (int c = 0; c < n_chunks; ++c) {
+    const int s = c % AD_SLOTS;
+    ad_wait(bar0 + 8u * s, (uint32_t)(c / AD_SLOTS) & 1u);
+    const int rows = min(CR, pos - c * CR);
+    const uint8_t* kb = ad_smem + ((size_t)w * AD_SLOTS + s) * 2 * AD_CHUNK + ch * 16;
+    const uint8_t* vb = kb + AD_CHUNK;
+#pragma unroll
+    for (int it = 0; it < CR / (U * RPL); ++it) {
+      if (it * U * RPL >= rows) break;     // uniform
+      float sc[U];
+      Raw vr[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int r = it * U * RPL + u * RPL + sub;
+        float a = 0.0f;
+        if (r < rows) {
+          float kf[EPL];
+          KvVec<TK>::unpack(*reinterpret_cast<const Raw*>(kb + r * ROWB), kf);
+          vr[u] = *reinterpret_cast<const Raw*>(vb + r * ROWB);
+#pragma unroll
+          for (int e = 0; e < EPL; ++e) a = fmaf(q[e], kf[e], a);
+        } else {
+          vr[u] = KvVec<TK>::zero();
+        }
+        sc[u] = a;
+      }
+#pragma unroll
+      for (int o = 1; o < LPR; o <<= 1) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) sc[u] += __shfl_xor_sync(0xffffffffu, sc[u], o);
+      }
+      float mx = m;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (it * U * RPL + u * RPL + sub >= rows) sc[u] = -INFINITY;
+        mx = fmaxf(mx, sc[u]);
+      }
+      if (mx > -INFINITY) {
+        const float corr = expf(m - mx);
+        l *= corr;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) acc[e] *= corr;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const float pr = expf(sc[u] - mx);
+          l += pr;
+          float vf[EPL];
+          KvVec<TK>::unpack(vr[u], vf);
+#pragma unroll
+          for (int e = 0; e < EPL; ++e) acc[e] = fmaf(pr, vf[e], acc[e]);
+        }
+        m = mx;
+      }
+    }
+    __syncwarp();                          // every lane is done with this slot
+    if (lane == 0 && c + AD_SLOTS < n_chunks) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue(c + AD_SLOTS);
+    }
+  }
+  {  // the new position: lane group 0 takes it into its state
+    float a = 0.0f;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) a = fmaf(q[e], kn[e], a);
+#pragma unroll
+    for (int o = 1; o < LPR; o <<= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if (sub == 0) {
+      const float mx = fmaxf(m, a);
+      const float corr = expf(m - mx), pr = expf(a - mx);
+      l = l * corr + pr;
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) acc[e] = fmaf(pr, vn[e], acc[e] * corr);
+      m = mx;
+    }
+  }
+  // merge the RPL lane groups (they hold the same dims for different positions)
+#pragma unroll
+  for (int o = LPR; o < 32; o <<= 1) {
+    const float m2 = __shfl_xor_sync(0xffffffffu, m, o), l2 = __shfl_xor_sync(0xffffffffu, l, o);
+    const float mx = fmaxf(m, m2);
+    const float c1 = (m > -INFINITY) ? expf(m - mx) : 0.0f, c2 = (m2 > -INFINITY) ? expf(m2 - mx) : 0.0f;
+    l = l * c1 + l2 * c2;
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      const float a2 = __shfl_xor_sync(0xffffffffu, acc[e], o);
+      acc[e] = acc[e] * c1 + a2 * c2;
+    }
+    m = mx;
+  }
+  if (sub == 0) {
+    const float inv = 1.0f / l;
+    TO* o = out + (long long)i * d_model + h * 64 + ch * EPL;
+#pragma unroll
+    for (int e = 0; e < EPL; e += 2) store2(o + e, make_float2(acc[e] * inv, acc[e + 1] * inv));
+  }
+}
+
+template <typename TK, typename TO, int W>
+static cudaError_t launch_attn_decode_bulk_w(const float* qkv, const float* rope_freqs, const int* offsets, const int* slot_ids,
+                                             KvGeom kv, int layer, TO* out, int n, cudaStream_t st) {
+  const int tasks = n * kv.H;
+  const size_t smem = (size_t)W * AD_SLOTS * 2 * AD_CHUNK;
+  auto kern = attn_decode_bulk_kernel<TK, TO, W>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  launch_k(kern, dim3((tasks + W - 1) / W), dim3(W * 32), smem, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, out, tasks);
+  return cudaGetLastError();
+}
+template <typename TK, typename TO>
+static cudaError_t launch_attn_decode_bulk(const float* qkv, const float* rope_freqs, const int* offsets, const int* slot_ids,
+                                           KvGeom kv, int layer, TO* out, int n, cudaStream_t st) {
+  // warps (= (stream, head) pairs) per CTA: 7 puts the 1024 pairs of 64 streams on 147 CTAs, one per SM
+  static const int w = [] { const char* e = getenv("PTTS_ATTN_W"); return e ? atoi(e) : 7; }();
+  if (w == 2) return launch_attn_decode_bulk_w<TK, TO, 2>(qkv, rope_freqs, offsets, slot_ids, kv, layer, out, n, st);
+  if (w == 4) return launch_attn_decode_bulk_w<TK, TO, 4>(qkv, rope_freqs, offsets, slot_ids, kv, layer, out, n, st);
+  return launch_attn_decode_bulk_w<TK, TO, 7>(qkv, rope_freqs, offsets, slot_ids, kv, layer, out, n, st);
+}
+
 cudaError_t launch_attn_decode(const float* qkv, const float* rope_freqs, const int* offsets,
                                const int* slot_ids, KvGeom kv, int layer, void* out, int out_type,
                                int n, cudaStream_t st) {
   if (kv.D != 64) return cudaErrorInvalidValue;
+  if (kv.prefetch == 2 && !kv.ring) {
+    if (kv.type == 0 && out_type == 0) return launch_attn_decode_bulk<float, float>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out, n, st);
+    if (kv.type == 1 && out_type == 1) return launch_attn_decode_bulk<bf16, bf16>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out, n, st);
+    if (kv.type == 0 && out_type == 1) return launch_attn_decode_bulk<float, bf16>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out, n, st);
+    return cudaErrorInvalidValue;
+  }
   dim3 grid(kv.H, n);
   if (kv.type == 0 && out_type == 0)
     launch_k(attn_decode_kernel<float, float>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out);

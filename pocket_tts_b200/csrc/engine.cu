@@ -108,7 +108,8 @@ int Engine::init() {
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_fork, cudaEventDisableTiming));
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_join, cudaEventDisableTiming));
   if (const char* f = getenv("PTTS_SIDE")) use_side_branch = !(f[0] == '0');
-  if (const char* f = getenv("PTTS_HEAD")) use_head_cluster = !(f[0] == '0');
+  if (const char* f = getenv("PTTS_LNFOLD")) use_ln_fold = !(f[0] == '0');
+  if (const char* f = getenv("PTTS_HEAD")) head_mode = f[0] >= '0' && f[0] <= '2' ? f[0] - '0' : 2;
   for (int k = 0; k < 2; ++k) {
     for (cudaEvent_t* e : {&ev_lat[k], &ev_mimi[k], &ev_copied_lat[k], &ev_copied_pcm[k]})
       PTTS_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
@@ -119,12 +120,13 @@ int Engine::init() {
   const int U = c.upsample_stride;
 
   // ---- per-slot state
-  kv_flow = KvGeom{nullptr, S, c.n_heads, c.kv_capacity, 64, act_type, 0};
+  kv_flow = KvGeom{nullptr, S, c.n_heads, c.kv_capacity, 64, act_type, 0, 1};
+  if (const char* f = getenv("PTTS_ATTN")) kv_flow.prefetch = f[0] >= '0' && f[0] <= '2' ? f[0] - '0' : 1;   // 0 per-lane loads, 1 + L2 prefetch before the wait, 2 bulk-copy kernel
   const size_t kvf = (size_t)c.n_layers * S * 2 * c.n_heads * c.kv_capacity * 64;
   kv_flow.base = act_alloc(kvf);
   int ring = 256;
   while (ring < c.mimi_context + U) ring *= 2;
-  kv_mimi = KvGeom{nullptr, S, c.mimi_heads, ring, 64, act_type, 1};
+  kv_mimi = KvGeom{nullptr, S, c.mimi_heads, ring, 64, act_type, 1, 0};
   kv_mimi.base = act_alloc((size_t)c.mimi_layers * S * 2 * c.mimi_heads * ring * 64);
   offsets = dmalloc<int>(allocs, S, stream);
   mimi_offsets = dmalloc<int>(allocs, S, stream);
@@ -148,6 +150,11 @@ int Engine::init() {
   qkv = dmalloc<float>(allocs, (size_t)max_rows * 3 * D, stream);
   a_ln = act_alloc((size_t)max_rows * D);
   attn_o = act_alloc((size_t)max_rows * D);
+  if (act_type == 1) {
+    h16 = dmalloc<bf16>(allocs, (size_t)S * D, stream);
+    ln_part = dmalloc<float2>(allocs, (size_t)S * (D / 16), stream);
+    if (!h16 || !ln_part) PTTS_FAIL(PTTS_ECUDA, "out of device memory for activations");
+  }
   mid = act_alloc((size_t)max_rows * c.ffn);
   eos_logit = dmalloc<float>(allocs, S, stream);
   noise_buf = dmalloc<float>(allocs, (size_t)S * c.ldim, stream);

@@ -38,6 +38,9 @@ struct LayerW {
   float *n1w, *n1b, *n2w, *n2b;
   Mat in_proj, out_proj, lin1, lin2;
   float *ls1 = nullptr, *ls2 = nullptr;  // Mimi LayerScale
+  // LayerNorm folded into the decode GEMMs (bf16 mode, FlowLM): W diag(gamma) in bf16, c1 = its row sums, c2 = W beta
+  Mat in_proj_ln, lin1_ln;
+  float *qkv_c1 = nullptr, *qkv_c2 = nullptr, *ffn_c1 = nullptr, *ffn_c2 = nullptr;
 };
 
 struct FlowBlockW {
@@ -130,6 +133,9 @@ class Engine {
            bool out_is_act);
   void prof_begin(const char* tag);
   void prof_end();
+  int make_ln_folded(const std::string& wname, const std::string& gname, const std::string& bname, int N, int K, Mat* m,
+                     float** c1, float** c2);
+  int flow_layer_decode_folded(int l, int n);
   int transformer_layer_common(const LayerW& L, float* h, int rows, int d, int ffn, void* a,
                                float* qkv, void* ao, void* mid, bool mimi, int li, int n);
   int flow_sequence(int n, int lsd, const float* noise = nullptr, float* eos_out = nullptr);
@@ -192,6 +198,8 @@ class Engine {
   int *d_slot_ids, *d_row_start, *d_lens, *d_mimi_row_start, *d_mimi_lens;
   float *h, *qkv, *eos_logit, *noise_buf, *x_lat, *cemb, *mod, *u, *pcm, *lat_in;
   void *a_ln, *attn_o, *mid, *c_cond, *sy, *g, *g1;
+  bf16* h16 = nullptr;                       // bf16 copy of the residual stream (operand of the LayerNorm-folded GEMMs)
+  float2* ln_part = nullptr;                 // [rows][d_model / 16] (sum, M2) partials of the residual rows
   float *xm, *mqkv;
   void *m_ln, *m_attn, *m_mid;
   // conv chain buffers
@@ -221,7 +229,8 @@ class Engine {
   cudaStream_t side_stream = nullptr;        // side branch of the FlowLM graph (input_proj of the first Euler step)
   cudaEvent_t ev_side_fork = nullptr, ev_side_join = nullptr;
   bool use_side_branch = true;               // PTTS_SIDE=0 disables
-  bool use_head_cluster = true;              // PTTS_HEAD=0: flow head as separate launches instead of the cluster kernel (flow_head.cu)
+  bool use_ln_fold = true;                   // PTTS_LNFOLD=0: separate LayerNorm launches in the FlowLM decode layers
+  int head_mode = 2;                         // PTTS_HEAD: 0 flow head as separate launches, 1 cluster kernel on mma.sync (flow_head.cu), 2 on tcgen05 (flow_head_tc.cu)
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph
   cudaEvent_t ev_lat[2] = {}, ev_mimi[2] = {}, ev_copied_lat[2] = {}, ev_copied_pcm[2] = {};
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)

@@ -2,6 +2,8 @@
 #include "engine.h"
 
 #include <climits>
+#include <cstdlib>
+#include <cstring>
 
 namespace ptts {
 
@@ -11,8 +13,20 @@ static const char* kC1Tag[3] = {"seanet.res0.conv1", "seanet.res1.conv1", "seane
 static inline RowMap plain(int ld) { return RowMap{0, 1 << 30, 1 << 30, ld}; }
 static inline RowMap batched(long long bs, int rpb, int valid, int ld) { return RowMap{bs, rpb, valid, ld}; }
 
+// developer timing probe: PTTS_SKIP_TAGS="flow.attn_decode,flow.ffn1" drops those launches (results are garbage;
+// the change in step time is the in-graph cost of the kernel on the dependent chain)
+static bool skip_tag(const char* tag) {
+  static const char* list = getenv("PTTS_SKIP_TAGS");
+  if (!list) return false;
+  const size_t n = strlen(tag);
+  for (const char* p = strstr(list, tag); p; p = strstr(p + 1, tag))
+    if ((p == list || p[-1] == ',') && (p[n] == 0 || p[n] == ',')) return true;
+  return false;
+}
+
 #define LAUNCH(tag, expr)       \
   do {                          \
+    if (skip_tag(tag)) break;   \
     prof_begin(tag);            \
     PTTS_CUDA_CHECK(expr);      \
     prof_end();                 \
@@ -25,6 +39,14 @@ int Engine::gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, con
                  GemmEpilogue ep, bool out_is_act) {
   GemmProblem p;
   p.A = A; p.a_map = amap; p.M = M; p.N = W.N; p.K = W.K; p.ep = ep;
+  {  // developer override of the split-K factor per tag: PTTS_SPLITS="flow.ffn1:2,flow.qkv:4"
+    static const char* list = getenv("PTTS_SPLITS");
+    if (list) {
+      const size_t n = strlen(tag);
+      for (const char* q = strstr(list, tag); q; q = strstr(q + 1, tag))
+        if ((q == list || q[-1] == ',') && q[n] == ':') { p.max_splits = atoi(q + n + 1); break; }
+    }
+  }
   const int in_type = a_is_act ? act_type : 0;
   const int out_type = out_is_act ? act_type : 0;
   if (in_type == 1) {
@@ -83,6 +105,43 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
   return PTTS_OK;
 }
 
+// FlowLM decode layer (one new position per stream, bf16 mode) with both LayerNorms folded into the GEMMs around
+// them: the residual GEMMs (out_proj, linear2) also emit a bf16 copy of the new residual row and per-block
+// (sum, M2) partials; the next GEMM (linear1 / the next layer's in_proj) runs on that copy with gamma folded into
+// its weights and applies rstd * (acc - mean * c1) + c2 in its epilogue.  5 launches per layer instead of 7.
+// Layer 0 still normalises the embedding rows with ln_rows (their producer is not a GEMM).
+int Engine::flow_layer_decode_folded(int l, int n) {
+  const LayerW& L = flow_layers[l];
+  const int d = cfg.d_model, ffn = cfg.ffn, np = d / 16;
+  int rc;
+  if (l == 0) {
+    LAUNCH("flow.ln", launch_ln_rows(h, L.n1w, L.n1b, 1e-5f, a_ln, act_type, n, d, stream));
+    GemmEpilogue ep; ep.out = qkv; ep.out_map = plain(3 * d);
+    if ((rc = gemm("flow.qkv", a_ln, true, plain(d), L.in_proj, n, ep, false)) != PTTS_OK) return rc;
+  } else {
+    GemmEpilogue ep; ep.out = qkv; ep.out_map = plain(3 * d);
+    ep.ln_part_in = ln_part; ep.ln_nparts = np; ep.ln_c1 = L.qkv_c1; ep.ln_c2 = L.qkv_c2;
+    if ((rc = gemm("flow.qkv", h16, true, plain(d), L.in_proj_ln, n, ep, false)) != PTTS_OK) return rc;
+  }
+  LAUNCH("flow.attn_decode", launch_attn_decode(qkv, rope_freqs, offsets, d_slot_ids, kv_flow, l, attn_o, act_type, n, stream));
+  {
+    GemmEpilogue ep; ep.out = h; ep.out_map = plain(d); ep.res = h; ep.res_map = plain(d);
+    ep.ln_raw = h16; ep.ln_part_out = ln_part;
+    if ((rc = gemm("flow.out_proj", attn_o, true, plain(d), L.out_proj, n, ep, false)) != PTTS_OK) return rc;
+  }
+  {
+    GemmEpilogue ep; ep.out = mid; ep.out_map = plain(ffn); ep.act_pre = ACT_GELU;
+    ep.ln_part_in = ln_part; ep.ln_nparts = np; ep.ln_c1 = L.ffn_c1; ep.ln_c2 = L.ffn_c2;
+    if ((rc = gemm("flow.ffn1", h16, true, plain(d), L.lin1_ln, n, ep, true)) != PTTS_OK) return rc;
+  }
+  {
+    GemmEpilogue ep; ep.out = h; ep.out_map = plain(d); ep.res = h; ep.res_map = plain(d);
+    if (l + 1 < cfg.n_layers) { ep.ln_raw = h16; ep.ln_part_out = ln_part; }
+    if ((rc = gemm("flow.ffn2", mid, true, plain(ffn), L.lin2, n, ep, false)) != PTTS_OK) return rc;
+  }
+  return PTTS_OK;
+}
+
 // FlowLM step + flow head for the n streams in d_slot_ids; noise in noise_buf.
 int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
   if (!noise) noise = noise_buf;
@@ -95,7 +154,7 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
   // u = input_proj(x_0) of the first Euler step depends on nothing but the noise: it runs on a side branch beside
   // the transformer layers instead of sitting in the dependent chain of the flow head
   // bf16 mode: everything after the AdaLN modulation GEMM of an Euler step is one cluster kernel (flow_head.cu)
-  const bool head_cluster = use_head_cluster && act_type == 1 && use_tc && flow_head_cluster_supported(F, Ld, c.flow_depth);
+  const bool head_cluster = head_mode != 0 && act_type == 1 && use_tc && flow_head_cluster_supported(F, Ld, c.flow_depth);
   const bool side_u = use_side_branch && side_stream != nullptr && !head_cluster;
   if (side_u) {
     PTTS_CUDA_CHECK(cudaEventRecord(ev_side_fork, stream));
@@ -109,8 +168,10 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
     PTTS_CUDA_CHECK(cudaEventRecord(ev_side_join, side_stream));
   }
   LAUNCH("flow.embed", launch_flow_embed(prev_latent, d_slot_ids, bos_emb, w_in, h, n, D, Ld, stream));
+  const bool ln_fold = use_ln_fold && act_type == 1 && use_tc && n <= 128 && D % 64 == 0;
   for (int l = 0; l < c.n_layers; ++l)
-    if ((rc = transformer_layer_common(flow_layers[l], h, n, D, c.ffn, a_ln, qkv, attn_o, mid, false, l, n)) != PTTS_OK)
+    if ((rc = ln_fold ? flow_layer_decode_folded(l, n)
+                      : transformer_layer_common(flow_layers[l], h, n, D, c.ffn, a_ln, qkv, attn_o, mid, false, l, n)) != PTTS_OK)
       return rc;
   // out_norm + EOS logit; the stream offsets advance here (every attention kernel of the step has read them)
   LAUNCH("flow.final_norm_eos", launch_final_norm_eos(h, out_norm_w, out_norm_b, 1e-5f, eos_w, eos_b, c_cond, act_type, eos_out, n, D, stream, offsets, d_slot_ids));
@@ -144,7 +205,14 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
       const bool last = s == lsd - 1;
       hp.prev_latent = last ? prev_latent : nullptr;
       hp.commit_out = last ? commit_out : nullptr;
-      LAUNCH("head.cluster", launch_flow_head_cluster(hp, stream));
+      if (head_mode == 2) {
+        FlowHeadTcParams tp;
+        tp.h = hp;
+        if (!flow_head_tc_prepare(&tp)) PTTS_FAIL(PTTS_ECUDA, "tensor map encode failed (flow head)");
+        LAUNCH("head.cluster", launch_flow_head_tc(tp, stream));
+      } else {
+        LAUNCH("head.cluster", launch_flow_head_cluster(hp, stream));
+      }
       continue;
     }
     if (s == 0 && side_u) {

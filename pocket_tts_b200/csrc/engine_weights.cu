@@ -3,6 +3,7 @@
 #include "engine.h"
 
 #include <algorithm>
+#include <cstring>
 
 namespace ptts {
 
@@ -30,6 +31,44 @@ static std::vector<float> convtr_to_gemm(const HostTensor& w, int S) {
         g[row * 2 * ci + ci + c] = w.data[((size_t)c * co + o) * k + r];
       }
   return g;
+}
+
+static inline float bf16_round_host(float x) {   // round-to-nearest-even, as __float2bfloat16_rn (finite inputs)
+  uint32_t u;
+  memcpy(&u, &x, 4);
+  u += 0x7FFFu + ((u >> 16) & 1u);
+  u &= 0xFFFF0000u;
+  float r;
+  memcpy(&r, &u, 4);
+  return r;
+}
+
+// W [N, K], LayerNorm gamma / beta [K]  ->  m = W diag(gamma) (bf16 copy is what the GEMM reads),
+// c1[n] = sum_k bf16(W[n,k] gamma[k]),  c2[n] = sum_k W[n,k] beta[k]      
+int Engine::make_ln_folded(const std::string& wname, const std::string& gname, const std::string& bname, int N, int K,
+                           Mat* m, float** c1, float** c2) {
+  auto iw = host_w.find(wname), ig = host_w.find(gname), ib = host_w.find(bname);
+  if (iw == host_w.end() || ig == host_w.end() || ib == host_w.end() || iw->second.numel() != (int64_t)N * K ||
+      ig->second.numel() != K || ib->second.numel() != K)
+    PTTS_FAIL(PTTS_EINVAL, "missing/malformed tensors for the folded LayerNorm of %s", wname.c_str());
+  const std::vector<float>&W = iw->second.data, &G = ig->second.data, &Bt = ib->second.data;
+  std::vector<float> wf((size_t)N * K), v1(N), v2(N);
+  for (int n = 0; n < N; ++n) {
+    double s1 = 0.0, s2 = 0.0;
+    for (int k = 0; k < K; ++k) {
+      const float w = W[(size_t)n * K + k], wg = w * G[k];
+      wf[(size_t)n * K + k] = wg;
+      s1 += (double)bf16_round_host(wg);
+      s2 += (double)w * (double)Bt[k];
+    }
+    v1[n] = (float)s1; v2[n] = (float)s2;
+  }
+  int rc;
+  if ((rc = make_mat_from(wf, N, K, m)) != PTTS_OK) return rc;
+  *c1 = upload(v1);
+  *c2 = upload(v2);
+  if (!*c1 || !*c2) PTTS_FAIL(PTTS_ECUDA, "upload failed");
+  return PTTS_OK;
 }
 
 int Engine::finalize() {
@@ -76,6 +115,12 @@ int Engine::finalize() {
     GETM(w.out_proj, p + "self_attn.out_proj.weight", D, D);
     GETM(w.lin1, p + "linear1.weight", c.ffn, D);
     GETM(w.lin2, p + "linear2.weight", D, c.ffn);
+    if (act_type == 1) {
+      if ((rc = make_ln_folded(p + "self_attn.in_proj.weight", p + "norm1.weight", p + "norm1.bias", 3 * (int)D, (int)D,
+                               &w.in_proj_ln, &w.qkv_c1, &w.qkv_c2)) != PTTS_OK) return rc;
+      if ((rc = make_ln_folded(p + "linear1.weight", p + "norm2.weight", p + "norm2.bias", c.ffn, (int)D, &w.lin1_ln,
+                               &w.ffn_c1, &w.ffn_c2)) != PTTS_OK) return rc;
+    }
   }
   // ---- flow head (mlp.py:134-215)
   const std::string fp = "flow_lm.flow_net.";

@@ -27,6 +27,18 @@ struct GemmEpilogue {
   RowMap out_map{0, 1 << 30, 1 << 30, 0};
   void* out2 = nullptr;             // optional pre-act_post copy
   RowMap out2_map{0, 1 << 30, 1 << 30, 0};
+  // LayerNorm folded into a producer / consumer GEMM pair (skinny tcgen05 path only):
+  //  producer (residual GEMM writing the fp32 stream h): also stores v as bf16 in ln_raw [M, N] and, per row and
+  //  per block of 16 features, (sum, M2) of v in ln_part_out [M][N/16];
+  //  consumer (GEMM on ln_raw with gamma folded into the weights): acc -> rstd * (acc - mean * ln_c1[n]) + ln_c2[n]
+  //  before bias / activation, with mean / rstd of each row combined from ln_part_in [M][ln_nparts].
+  bf16* ln_raw = nullptr;
+  float2* ln_part_out = nullptr;
+  const float2* ln_part_in = nullptr;
+  int ln_nparts = 0;                // partials per row (consumer K / 16)
+  float ln_eps = 1e-5f;
+  const float* ln_c1 = nullptr;     // [N] sum_k bf16(W[n,k] gamma[k])
+  const float* ln_c2 = nullptr;     // [N] sum_k W[n,k] beta[k]
 };
 
 struct GemmProblem {
@@ -35,6 +47,7 @@ struct GemmProblem {
   const void* W = nullptr;  // [N, K] row-major
   int M = 0, N = 0, K = 0;
   GemmEpilogue ep;
+  int max_splits = 8;       // skinny tcgen05 path: upper bound of the cluster split-K factor
 };
 
 // element types: 0 = float, 1 = bf16

@@ -154,7 +154,7 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, int M, int
 // streams m.  out / res / out2 / gate are plain row-major [M, ld] (checked on the host).
 template <int BN, typename TO>
 __device__ __forceinline__ void epilogue_cols(const GemmEpilogue& ep, const TcParams& P, uint32_t taddr, int n,
-                                              int m_base, int half) {
+                                              int m_base, int half, const float2* ln_stat) {
   constexpr int CH = BN >= 32 ? 32 : 16;
   constexpr int NCH = BN / CH;
   const bool n_ok = n < P.N;
@@ -172,6 +172,12 @@ __device__ __forceinline__ void epilogue_cols(const GemmEpilogue& ep, const TcPa
     tmem_ld<CH>(taddr + c, v);
     if (n_ok) {
       const int cnt = min(CH, P.M - m0);
+      if (ep.ln_part_in) {
+        const float lc1 = ep.ln_c1[n], lc2 = ep.ln_c2[n];
+#pragma unroll
+        for (int j = 0; j < CH; ++j)
+          if (j < cnt) { const float2 st = ln_stat[m0 + j]; v[j] = fmaf(st.y, v[j] - st.x * lc1, lc2); }
+      }
 #pragma unroll
       for (int j = 0; j < CH; ++j) v[j] += bias;
       act_inplace<CH>(v, ep.act_pre);
@@ -225,7 +231,7 @@ __device__ __forceinline__ void partial_push(const TcParams& P, uint32_t taddr, 
 // epilogue on features [rank*F, rank*F + F) of the tile with row-contiguous 16-byte accesses.
 template <int BN, typename TO>
 __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcParams& P, const float* slab, int S,
-                                               int rank, int row0, int et) {
+                                               int rank, int row0, int et, const float2* ln_stat) {
   const int F = BM_TC / S, FV = F >> 2;
   const int fv = et % FV, mstep = 256 / FV;
   const int n = row0 + rank * F + fv * 4;
@@ -234,12 +240,20 @@ __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcP
   if (ep.bias) bias = ld4f(ep.bias + n);
   if (ep.colscale) cs = ld4f(ep.colscale + n);
   cs.x *= ep.alpha; cs.y *= ep.alpha; cs.z *= ep.alpha; cs.w *= ep.alpha;
+  float4 lc1 = make_float4(0.f, 0.f, 0.f, 0.f), lc2 = lc1;
+  if (ep.ln_part_in) { lc1 = ld4f(ep.ln_c1 + n); lc2 = ld4f(ep.ln_c2 + n); }
+  const unsigned grp_mask = 0xFu << ((threadIdx.x & 31) & ~3);   // the 4 lanes that share a row and a 16-feature block
   const float* src = slab + fv * 4;
   for (int m = et / FV; m < P.M; m += mstep) {
     float v[4] = {bias.x, bias.y, bias.z, bias.w};
     for (int s = 0; s < S; ++s) {
       const float4 t = ld4f(src + (s * BN + m) * F);
       v[0] += t.x; v[1] += t.y; v[2] += t.z; v[3] += t.w;
+    }
+    if (ep.ln_part_in) {   // folded LayerNorm of the operand row (mean, rstd from the producer's partials)
+      const float2 st = ln_stat[m];
+      v[0] = fmaf(st.y, v[0] - st.x * lc1.x, lc2.x); v[1] = fmaf(st.y, v[1] - st.x * lc1.y, lc2.y);
+      v[2] = fmaf(st.y, v[2] - st.x * lc1.z, lc2.z); v[3] = fmaf(st.y, v[3] - st.x * lc1.w, lc2.w);
     }
     act_inplace<4>(v, ep.act_pre);
     if (ep.gate) {
@@ -252,9 +266,59 @@ __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcP
       v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
     }
     if (ep.out2) store4(reinterpret_cast<TO*>(ep.out2) + (long long)m * ep.out2_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
+    if (ep.ln_part_out) {   // producer side of a folded LayerNorm: bf16 copy + (sum, M2) over this 16-feature block
+      store4(ep.ln_raw + (long long)m * P.N + n, make_float4(v[0], v[1], v[2], v[3]));
+      float sum = (v[0] + v[1]) + (v[2] + v[3]);
+      sum += __shfl_xor_sync(grp_mask, sum, 1);
+      sum += __shfl_xor_sync(grp_mask, sum, 2);
+      const float mu = sum * (1.0f / 16.0f);
+      const float d0 = v[0] - mu, d1 = v[1] - mu, d2 = v[2] - mu, d3 = v[3] - mu;
+      float m2 = fmaf(d0, d0, fmaf(d1, d1, fmaf(d2, d2, d3 * d3)));
+      m2 += __shfl_xor_sync(grp_mask, m2, 1);
+      m2 += __shfl_xor_sync(grp_mask, m2, 2);
+      if ((fv & 3) == 0) ep.ln_part_out[(long long)m * (P.N >> 4) + (n >> 4)] = make_float2(sum, m2);
+    }
     act_inplace<4>(v, ep.act_post);
     store4(reinterpret_cast<TO*>(ep.out) + (long long)m * ep.out_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
   }
+}
+
+// Consumer side of a folded LayerNorm: the 8 epilogue warps combine the per-block (sum, M2) partials of every
+// operand row into (mean, rstd) in shared memory while the mainloop runs (parallel-variance formula).
+__device__ __forceinline__ void ln_combine(const GemmEpilogue& ep, int M, float2* ln_stat, int et) {
+  const int np = ep.ln_nparts;
+  const float inv_d = 1.0f / (16.0f * (float)np);
+  const unsigned mask = 0xFu << ((threadIdx.x & 31) & ~3);
+  const int j = et & 3;
+  for (int m = et >> 2; m < M; m += 64) {
+    const float2* pr = ep.ln_part_in + (long long)m * np;
+    float tot = 0.0f, q = 0.0f, mu;
+    if (np == 64) {   // d_model 1024: 16 partials per lane, all loads in flight at once
+      float4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = ld4f(reinterpret_cast<const float*>(pr + 16 * j) + 4 * i);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) tot += v[i].x + v[i].z;
+      tot += __shfl_xor_sync(mask, tot, 1);
+      tot += __shfl_xor_sync(mask, tot, 2);
+      mu = tot * inv_d;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d0 = v[i].x * (1.0f / 16.0f) - mu, d1 = v[i].z * (1.0f / 16.0f) - mu;
+        q += (v[i].y + 16.0f * d0 * d0) + (v[i].w + 16.0f * d1 * d1);
+      }
+    } else {
+      for (int i = j; i < np; i += 4) tot += pr[i].x;
+      tot += __shfl_xor_sync(mask, tot, 1);
+      tot += __shfl_xor_sync(mask, tot, 2);
+      mu = tot * inv_d;
+      for (int i = j; i < np; i += 4) { const float2 p = pr[i]; const float dm = p.x * (1.0f / 16.0f) - mu; q += p.y + 16.0f * dm * dm; }
+    }
+    q += __shfl_xor_sync(mask, q, 1);
+    q += __shfl_xor_sync(mask, q, 2);
+    if (j == 0) ln_stat[m] = make_float2(mu, rsqrtf(q * inv_d + ep.ln_eps));
+  }
+  asm volatile("bar.sync 2, 256;" ::: "memory");   // the 8 epilogue warps
 }
 
 template <int BN, bool SWAP, typename TO>
@@ -270,6 +334,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
+  __shared__ float2 ln_stat[SWAP ? (BN < 128 ? BN : 128) : 1];   // folded LayerNorm: (mean, rstd) per operand row (M <= 128)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 2) TC_TRACE(4);
@@ -369,6 +434,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     // split its column chunks =====
     const int q = warp & 3, half = (warp - 2) >> 2;
     if (warp == 2) TC_TRACE(1);
+    if (SWAP && ep.ln_part_in) ln_combine(ep, P.M, ln_stat, (int)threadIdx.x - 64);
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
     if (warp == 2) TC_TRACE(2);
@@ -378,7 +444,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
       cluster_wait_acquire();                        // every peer CTA has started
       partial_push<BN>(P, taddr, slab, P.cluster, (int)blockIdx.z, q * 32 + lane, half);
     } else if (nkb > 0) {
-      if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half);
+      if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half, ln_stat);
       else epilogue_rows<BN, TO>(ep, P.M, P.N, taddr, row0, col0, q, half, lane, tiles);
     }
     tc_fence_before();
@@ -388,7 +454,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     cluster_arrive_release();                 // this CTA's pushes are done ...
     cluster_wait_acquire();                   // ... and so are everybody else's into this CTA
     if (warp == 2) TC_TRACE(5);
-    if (warp >= 2) epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64);
+    if (warp >= 2) epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64, ln_stat);
     if (warp == 2) TC_TRACE(6);
   }
   __syncthreads();
@@ -560,7 +626,7 @@ bool tc_make_map(CUtensorMap* out, const void* base, long long rows, int K, long
   return true;
 }
 
-constexpr size_t TC_SMEM_LIMIT = 225 * 1024;
+constexpr size_t TC_SMEM_LIMIT = 224 * 1024;
 constexpr size_t TC_CORESIDENT_SMEM = 108 * 1024;   // two CTAs per SM
 constexpr size_t TC_ROWS_SMEM = 112 * 1024;         // persistent row-major kernel: leaves ~85 KB per SM to the other branch
 
@@ -668,6 +734,7 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
   const bool plain_out = p.ep.out_map.rows_per_batch >= (1 << 30) && p.ep.res_map.rows_per_batch >= (1 << 30) &&
                          p.ep.out2_map.rows_per_batch >= (1 << 30);
   const bool swap = plain_a && plain_out && p.M <= 256;
+  if (!swap && (p.ep.ln_part_in || p.ep.ln_part_out)) return cudaErrorInvalidValue;   // folded LayerNorm: skinny path only
   if (!swap && p.N % 32 != 0 && p.N != 16) return cudaErrorInvalidValue;   // row-major epilogue works in 32-column chunks
   TcParams P{};
   P.M = p.M; P.N = p.N; P.num_kb = p.K / BK_TC;
@@ -682,11 +749,13 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
     // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix
     int splits = 1;
-    while (splits < 8 && splits * 2 <= P.num_kb && tiles * splits * 2 <= n_sms) splits *= 2;
+    while (splits < 8 && splits * 2 <= p.max_splits && splits * 2 <= P.num_kb && tiles * splits * 2 <= n_sms) splits *= 2;
     if (p.N % 4 != 0) splits = 1;   // the slab epilogue works on 4-feature vectors
     P.kb_per_split = (P.num_kb + splits - 1) / splits;
     if ((P.num_kb + P.kb_per_split - 1) / P.kb_per_split != splits) { splits = 1; P.kb_per_split = P.num_kb; }
     P.cluster = splits;
+    if (ep.ln_part_out && (splits == 1 || p.N % 16 != 0 || !ep.ln_raw)) return cudaErrorInvalidValue;   // partials come from the slab epilogue
+    if (ep.ln_part_in && (ep.ln_nparts * 16 != p.K || !ep.ln_c1 || !ep.ln_c2 || p.M > 128)) return cudaErrorInvalidValue;
     const size_t stage = (size_t)(BM_TC + bn) * 128, slab = splits > 1 ? (size_t)bn * BM_TC * sizeof(float) : 0;
     // keep a CTA under ~half an SM's shared memory when possible: kernels of the two graph branches
     // (FlowLM chain || Mimi chain) and consecutive waves can then share an SM

@@ -1,6 +1,8 @@
 // Launchers for the non-GEMM kernels of the frame step.  Element types are passed as
 // 0 = float, 1 = bf16 ("act" = activation storage feeding GEMMs, "kv" = KV-cache storage).
 #pragma once
+#include <cuda.h>
+
 #include "common.cuh"
 
 namespace ptts {
@@ -12,6 +14,7 @@ struct KvGeom {
   int n_slots, H, cap, D;
   int type;        // 0 float, 1 bf16
   int ring;        // 1: pos stored at pos & (cap-1) (Mimi sliding window), 0: linear
+  int prefetch;    // decode attention form (PTTS_ATTN): 0 per-lane loads, 1 + L2 prefetch before the producer wait, 2 bulk-copy kernel
 };
 
 // h[i,:] = input_linear(where(isnan(prev), bos, prev))            flow_lm.py:121-122
@@ -86,6 +89,15 @@ struct FlowHeadParams {
 };
 bool flow_head_cluster_supported(int flow_dim, int ldim, int depth);
 cudaError_t launch_flow_head_cluster(const FlowHeadParams& p, cudaStream_t st);
+// tcgen05 form (flow_head_tc.cu): the same step with TMEM accumulators, a TMA weight ring and bulk DSMEM operand
+// exchange.  `maps`: one SWIZZLE_128B tensor map per matrix (mlp.0 / mlp.2 of every block, then the final layer).
+struct FlowHeadTcParams {
+  FlowHeadParams h;
+  alignas(64) CUtensorMap maps[2 * PTTS_HEAD_MAX_DEPTH + 1];
+  int trace = 0;                         // developer timing stamps (PTTS_HEAD_TRACE=1)
+};
+bool flow_head_tc_prepare(FlowHeadTcParams* p);   // fills `maps` from h (cached driver encodes)
+cudaError_t launch_flow_head_tc(const FlowHeadTcParams& p, cudaStream_t st);
 
 // x[i,:] -> prev_latent[slot] and out (nullable)
 cudaError_t launch_commit_latent(const float* x, const int* slot_ids, float* prev_latent,
