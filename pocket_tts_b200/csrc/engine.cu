@@ -151,6 +151,8 @@ int Engine::init() {
   a_ln = act_alloc((size_t)max_rows * D);
   attn_o = act_alloc((size_t)max_rows * D);
   if (act_type == 1) {
+    head_xchg = dmalloc<bf16>(allocs, (size_t)((S + 63) / 64) * 2 * 8 * 64 * 64, stream);
+    if (const char* f = getenv("PTTS_HEAD_XCHG")) head_l2_exchange = !(f[0] == 'd');
     h16 = dmalloc<bf16>(allocs, (size_t)S * D, stream);
     ln_part = dmalloc<float2>(allocs, (size_t)S * (D / 16), stream);
     if (!h16 || !ln_part) PTTS_FAIL(PTTS_ECUDA, "out of device memory for activations");

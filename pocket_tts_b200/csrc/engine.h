@@ -198,6 +198,8 @@ class Engine {
   int *d_slot_ids, *d_row_start, *d_lens, *d_mimi_row_start, *d_mimi_lens;
   float *h, *qkv, *eos_logit, *noise_buf, *x_lat, *cemb, *mod, *u, *pcm, *lat_in;
   void *a_ln, *attn_o, *mid, *c_cond, *sy, *g, *g1;
+  bf16* head_xchg = nullptr;                 // flow-head cluster kernel: operand exchange scratch (flow_head_tc.cu)
+  bool head_l2_exchange = true;              // PTTS_HEAD_XCHG=dsmem: exchange through DSMEM bulk copies instead
   bf16* h16 = nullptr;                       // bf16 copy of the residual stream (operand of the LayerNorm-folded GEMMs)
   float2* ln_part = nullptr;                 // [rows][d_model / 16] (sum, M2) partials of the residual rows
   float *xm, *mqkv;

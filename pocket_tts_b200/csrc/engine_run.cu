@@ -208,6 +208,7 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
       if (head_mode == 2) {
         FlowHeadTcParams tp;
         tp.h = hp;
+        tp.xchg = head_l2_exchange ? head_xchg : nullptr;
         if (!flow_head_tc_prepare(&tp)) PTTS_FAIL(PTTS_ECUDA, "tensor map encode failed (flow head)");
         LAUNCH("head.cluster", launch_flow_head_tc(tp, stream));
       } else {

@@ -67,6 +67,13 @@ __device__ __forceinline__ void bulk_smem_to_cluster(uint32_t dst_cluster, uint3
   asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(bar_cluster) : "memory");
 }
+// one TMA tile (64 k x 64 rows, SWIZZLE_128B) from global memory into the same shared-memory offset of every CTA
+// in `mask`, completing on the mbarrier at the same offset in each of them
+__device__ __forceinline__ void tma_load_2d_mcast(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, uint16_t mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
 __device__ __forceinline__ void st_async_f2(uint32_t dst_cluster, float x, float y, uint32_t bar_cluster) {
   asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];"
                ::"r"(dst_cluster), "f"(x), "f"(y), "r"(bar_cluster) : "memory");
@@ -265,6 +272,26 @@ flow_head_tc_kernel(const __grid_constant__ FlowHeadTcParams P) {
     // g[32] (this thread's row, features fl0..fl0+31) -> bf16, swizzled k-block layout in loc[buf] -> k-block c of
     // operand buffer `buf` in all 8 CTAs
     auto publish = [&](const float* gv, int buf) {
+      if (P.xchg) {
+        // through L2: the slice goes to a global scratch block as plain rows, then ONE multicast TMA load brings
+        // it (swizzled by the tensor map) into k-block c of the operand buffer of all 8 CTAs.  DSMEM pushes of
+        // the same 8 x 8 KB measured ~4 us per exchange; an L2 round trip with multicast is ~1.5 us.
+        const int blk_row = (((blockIdx.x / HT_CL) * 2 + buf) * HT_CL + (int)c) * HT_ROWS;
+        bf16* dstg = P.xchg + (size_t)(blk_row + s) * HT_FS + fl0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 v;
+          v.x = pack2(gv[8 * j], gv[8 * j + 1]); v.y = pack2(gv[8 * j + 2], gv[8 * j + 3]);
+          v.z = pack2(gv[8 * j + 4], gv[8 * j + 5]); v.w = pack2(gv[8 * j + 6], gv[8 * j + 7]);
+          *reinterpret_cast<uint4*>(dstg + 8 * j) = v;
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        epi_bar();
+        if (et == 0)
+          tma_load_2d_mcast(sm_a + OFF_X + buf * HT_XBYTES + c * HT_BLK, &P.xmap, xfull_a + 8u * buf, 0, blk_row, (uint16_t)0xFF);
+        return;
+      }
       uint8_t* loc = sm + OFF_LOC + buf * HT_BLK + s * 128;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -387,6 +414,10 @@ flow_head_tc_kernel(const __grid_constant__ FlowHeadTcParams P) {
 
 bool flow_head_tc_prepare(FlowHeadTcParams* p) {
   const FlowHeadParams& h = p->h;
+  if (p->xchg) {
+    const long long rows = (long long)((h.n + HT_ROWS - 1) / HT_ROWS) * 2 * HT_CL * HT_ROWS;
+    if (!tc_make_map(&p->xmap, p->xchg, rows, HT_FS, HT_FS, HT_ROWS)) return false;
+  }
   for (int m = 0; m < 2 * h.depth; ++m) {
     const bf16* w = (m & 1) ? h.blk[m >> 1].w2 : h.blk[m >> 1].w0;
     if (!tc_make_map(&p->maps[m], w, HT_F, HT_F, HT_F, HT_FS)) return false;

@@ -94,6 +94,8 @@ cudaError_t launch_flow_head_cluster(const FlowHeadParams& p, cudaStream_t st);
 struct FlowHeadTcParams {
   FlowHeadParams h;
   alignas(64) CUtensorMap maps[2 * PTTS_HEAD_MAX_DEPTH + 1];
+  alignas(64) CUtensorMap xmap;          // operand exchange scratch as [blocks * 64 rows, 64] bf16
+  bf16* xchg = nullptr;                  // [clusters][2 buffers][8 blocks][64 rows][64] bf16 global scratch (nullptr: exchange through DSMEM)
   int trace = 0;                         // developer timing stamps (PTTS_HEAD_TRACE=1)
 };
 bool flow_head_tc_prepare(FlowHeadTcParams* p);   // fills `maps` from h (cached driver encodes)
