@@ -12,6 +12,8 @@
 
 namespace ptts {
 
+PTTS_TL_ENABLE_FN(attention)
+
 template <typename TK>
 __device__ __forceinline__ TK* kv_row(const KvGeom& g, int layer, int slot, int kv, int h, int pos) {
   const int p = g.ring ? (pos & (g.cap - 1)) : pos;
@@ -129,7 +131,7 @@ template <> struct KvVec<float> {
 };
 
 template <typename TK, typename TO>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128)   // 72 registers: 7 CTAs per SM (64 registers spills and is slower, measured)
 attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs,
                    const int* __restrict__ offsets, const int* __restrict__ slot_ids, KvGeom g,
                    int layer, TO* __restrict__ out) {
@@ -158,7 +160,9 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
       asm volatile("prefetch.global.L2 [%0];" ::"l"(vb + off));
     }
   }
+  const unsigned tl = tl_begin(2);
   pdl_wait();
+  tl_mark(tl, 2);
   const float* row = qkv + (long long)i * 3 * d_model + h * 64 + ch * EPL;
 
   // rotate this lane's slice of q (interleaved pairs, rope.py:36-58); lanes with sub == 0 of
@@ -264,6 +268,8 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
 #pragma unroll
     for (int e = 0; e < EPL; e += 2) store2(o + e, make_float2(a[e] * inv, a[e + 1] * inv));
   }
+  tl_mark(tl, 3);
+  if (tl_buf_dev && threadIdx.x == 0) atomicMax(tl_buf_dev + 1, tl_now());   // latest exit of any CTA of any launch
 }
 
 // =====================================================================================

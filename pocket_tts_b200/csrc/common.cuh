@@ -67,6 +67,34 @@ __device__ __forceinline__ void store2(bf16* p, float2 v) {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ---- developer timeline (PTTS_TIMELINE=1): thread 0 of CTA (0,0,0) of every instrumented kernel records its
+// entry, the return of its programmatic-dependent-launch wait and its exit (globaltimer, ns) into a ring of
+// records; the engine prints the last records when it is destroyed.  Each translation unit has its own copy
+// of the buffer pointer (set through tl_enable_<unit>), so no relocatable device code is needed.
+constexpr unsigned TL_MAX = 4096;        // records; buffer = 2 header words + TL_W words per record
+constexpr unsigned TL_W = 8;             // kind, entry, wait returned, exit, 4 kernel-specific marks
+static __device__ unsigned long long* tl_buf_dev = nullptr;
+__device__ __forceinline__ unsigned long long tl_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ unsigned tl_begin(int kind) {
+  unsigned long long* b = tl_buf_dev;
+  if (!b || threadIdx.x != 0 || (blockIdx.x | blockIdx.y | blockIdx.z) != 0) return ~0u;
+  const unsigned s = (unsigned)(atomicAdd(b, 1ull) % TL_MAX);
+  b[2 + TL_W * s] = (unsigned long long)kind;
+  b[2 + TL_W * s + 1] = tl_now();
+#pragma unroll
+  for (unsigned i = 2; i < TL_W; ++i) b[2 + TL_W * s + i] = 0;
+  return s;
+}
+__device__ __forceinline__ void tl_mark(unsigned s, int which) {   // which: 2 = wait returned, 3 = exit, 4..7 free
+  if (s != ~0u) tl_buf_dev[2 + TL_W * s + which] = tl_now();
+}
+#define PTTS_TL_ENABLE_FN(unit) \
+  void tl_enable_##unit(unsigned long long* p) { cudaMemcpyToSymbol(tl_buf_dev, &p, sizeof p); }
+
 // ---- reductions
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

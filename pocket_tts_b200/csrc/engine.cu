@@ -37,7 +37,33 @@ bool pdl_enabled() {
   return v == 1;
 }
 
+static void tl_dump(unsigned long long* dev) {
+  std::vector<unsigned long long> b(2 + TL_W * TL_MAX);
+  cudaDeviceSynchronize();
+  if (cudaMemcpy(b.data(), dev, b.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return;
+  const unsigned long long total = b[0];
+  const unsigned n = (unsigned)std::min<unsigned long long>(total, 160);
+  fprintf(stderr, "[timeline] %llu records, last %u (us relative to the first shown: entry / wait returned / exit of CTA 0)\n", total, n);
+  unsigned long long t0 = 0;
+  const unsigned long long last_attn_exit = b[1];
+  for (unsigned k = 0; k < n; ++k) {
+    const unsigned s = (unsigned)((total - n + k) % TL_MAX);
+    const unsigned long long* r = &b[2 + TL_W * s];
+    const unsigned long long kind = r[0], te = r[1], tw = r[2], tx = r[3];
+    if (k == 0) t0 = te;
+    char name[64];
+    if (kind >> 28) snprintf(name, sizeof name, "gemm N=%llu kb=%llu", (kind >> 8) & 0xFFFFF, kind & 0xFF);
+    else snprintf(name, sizeof name, "%s", kind == 2 ? "attn_decode" : kind == 3 ? "ln_rows" : kind == 4 ? "final_norm_eos" : kind == 5 ? "flow_embed" : kind == 6 ? "head_cluster" : "?");
+    fprintf(stderr, "[timeline] %-22s entry %9.2f  wait %9.2f  exit %9.2f |", name, (double)(te - t0) / 1e3,
+            tw ? (double)(tw - t0) / 1e3 : -1.0, tx ? (double)(tx - t0) / 1e3 : -1.0);
+    for (unsigned i = 4; i < TL_W; ++i) fprintf(stderr, " %8.2f", r[i] ? (double)(r[i] - t0) / 1e3 : -1.0);
+    fprintf(stderr, "\n");
+  }
+  if (last_attn_exit) fprintf(stderr, "[timeline] latest exit of any decode-attention CTA: %9.2f\n", (double)(last_attn_exit - t0) / 1e3);
+}
+
 Engine::~Engine() {
+  if (tl_buf) { tl_dump(tl_buf); tl_enable_kernels(nullptr); tl_enable_gemm_tc(nullptr); tl_enable_attention(nullptr); tl_enable_head_tc(nullptr); }
   for (auto& kv : graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (void* p : allocs) cudaFree(p);
@@ -108,6 +134,12 @@ int Engine::init() {
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_fork, cudaEventDisableTiming));
   PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_side_join, cudaEventDisableTiming));
   if (const char* f = getenv("PTTS_SIDE")) use_side_branch = !(f[0] == '0');
+  if (const char* f = getenv("PTTS_TIMELINE")) {
+    if (f[0] == '1') {
+      tl_buf = dmalloc<unsigned long long>(allocs, 2 + TL_W * TL_MAX, stream);
+      if (tl_buf) { tl_enable_kernels(tl_buf); tl_enable_gemm_tc(tl_buf); tl_enable_attention(tl_buf); tl_enable_head_tc(tl_buf); }
+    }
+  }
   if (const char* f = getenv("PTTS_LNFOLD")) use_ln_fold = !(f[0] == '0');
   if (const char* f = getenv("PTTS_HEAD")) head_mode = f[0] >= '0' && f[0] <= '2' ? f[0] - '0' : 2;
   for (int k = 0; k < 2; ++k) {

@@ -60,6 +60,10 @@ struct MegaPlan {            // phase program of the persistent FlowLM step kern
   int n_phases = 0;
 };
 const unsigned* mega_diag_words();
+void tl_enable_kernels(unsigned long long*);
+void tl_enable_gemm_tc(unsigned long long*);
+void tl_enable_attention(unsigned long long*);
+void tl_enable_head_tc(unsigned long long*);
 bool make_sm_partition(int device, int flow_sms, int prio_flow, int prio_mimi, cudaStream_t* s_flow, cudaStream_t* s_mimi,
                        int* n_flow, int* n_mimi);
 
@@ -198,6 +202,7 @@ class Engine {
   int *d_slot_ids, *d_row_start, *d_lens, *d_mimi_row_start, *d_mimi_lens;
   float *h, *qkv, *eos_logit, *noise_buf, *x_lat, *cemb, *mod, *u, *pcm, *lat_in;
   void *a_ln, *attn_o, *mid, *c_cond, *sy, *g, *g1;
+  unsigned long long* tl_buf = nullptr;      // developer timeline ring (PTTS_TIMELINE=1), dumped by the destructor
   bf16* head_xchg = nullptr;                 // flow-head cluster kernel: operand exchange scratch (flow_head_tc.cu)
   bool head_l2_exchange = true;              // PTTS_HEAD_XCHG=dsmem: exchange through DSMEM bulk copies instead
   bf16* h16 = nullptr;                       // bf16 copy of the residual stream (operand of the LayerNorm-folded GEMMs)

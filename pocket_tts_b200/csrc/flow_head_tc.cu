@@ -25,6 +25,8 @@
 
 namespace ptts {
 
+PTTS_TL_ENABLE_FN(head_tc)
+
 namespace {
 
 constexpr int HT_CL = 8;             // CTAs per cluster
@@ -113,6 +115,7 @@ flow_head_tc_kernel(const __grid_constant__ FlowHeadTcParams P) {
   const uint32_t xfull_a = smem_u32(&bars.xfull[0]), accfull_a = smem_u32(&bars.accfull), stat_a = smem_u32(&bars.stat);
 
   pdl_launch_dependents();
+  const unsigned tl = tl_begin(6);
   HT_TRACE(0);
   // ---- prologue: nothing here depends on the previous kernel
   for (int m = 0; m < n_gemm; ++m) {                // this CTA's 64 KB slice of every 512 x 512 matrix -> L2
@@ -211,6 +214,7 @@ flow_head_tc_kernel(const __grid_constant__ FlowHeadTcParams P) {
     const uint32_t taddr = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)fl0;
     uint32_t accph = 0, statph = 0;
     pdl_wait();                                      // x_in / mod come from the previous kernels
+    tl_mark(tl, 2);
     HT_TRACE(2);
 
     float u[32];
@@ -404,6 +408,7 @@ flow_head_tc_kernel(const __grid_constant__ FlowHeadTcParams P) {
   cluster_arrive_release();
   cluster_wait_acquire();
   HT_TRACE(61);
+  tl_mark(tl, 3);
   if (warp == 3) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(HT_TMEM_COLS) : "memory");

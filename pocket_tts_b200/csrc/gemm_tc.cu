@@ -38,6 +38,8 @@
 
 namespace ptts {
 
+PTTS_TL_ENABLE_FN(gemm_tc)
+
 constexpr int BM_TC = 128;   // TMEM lanes / UMMA M
 constexpr int BK_TC = 64;    // bf16 elements per 128-byte swizzle row
 constexpr int MAX_STAGES = 8;
@@ -49,6 +51,8 @@ struct TcParams {
   int kb_per_split;    // k-blocks handled by one blockIdx.z
   int stages;
   int cluster;         // SWAP split-K: CTAs per cluster along z (partials reduced through DSMEM)
+  const bf16* w_base;  // SWAP: weight matrix [N, w_ld] for the L2 prefetch of this CTA's slice (nullptr: none)
+  int w_ld;
   long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
 };
 #define TC_TRACE(slot) do { if (P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) P.trace[slot] = clock64(); } while (0)
@@ -229,19 +233,33 @@ __device__ __forceinline__ void partial_push(const TcParams& P, uint32_t taddr, 
 
 // Phase 2 (after the cluster barrier): sum the S slabs of this CTA in rank order and run the full
 // epilogue on features [rank*F, rank*F + F) of the tile with row-contiguous 16-byte accesses.
+// per-feature vectors of the slab epilogue (bias, LayerScale * alpha, folded-LayerNorm c1 / c2): weights, so they are
+// loaded before the accumulator wait instead of after the cluster barrier (a cold HBM round trip each)
+struct SlabVecs {
+  float4 bias, cs, lc1, lc2;
+};
+__device__ __forceinline__ SlabVecs slab_vecs_load(const GemmEpilogue& ep, const TcParams& P, int S, int rank, int row0, int et) {
+  const int F = BM_TC / S, FV = F >> 2;
+  const int n = row0 + rank * F + (et % FV) * 4;
+  SlabVecs v;
+  v.bias = make_float4(0.f, 0.f, 0.f, 0.f); v.cs = make_float4(1.f, 1.f, 1.f, 1.f); v.lc1 = v.bias; v.lc2 = v.bias;
+  if (n < P.N) {
+    if (ep.bias) v.bias = ld4f(ep.bias + n);
+    if (ep.colscale) v.cs = ld4f(ep.colscale + n);
+    if (ep.ln_part_in) { v.lc1 = ld4f(ep.ln_c1 + n); v.lc2 = ld4f(ep.ln_c2 + n); }
+  }
+  v.cs.x *= ep.alpha; v.cs.y *= ep.alpha; v.cs.z *= ep.alpha; v.cs.w *= ep.alpha;
+  return v;
+}
+
 template <int BN, typename TO>
 __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcParams& P, const float* slab, int S,
-                                               int rank, int row0, int et, const float2* ln_stat) {
+                                               int rank, int row0, int et, const float2* ln_stat, const SlabVecs& sv) {
   const int F = BM_TC / S, FV = F >> 2;
   const int fv = et % FV, mstep = 256 / FV;
   const int n = row0 + rank * F + fv * 4;
   if (n >= P.N) return;
-  float4 bias = make_float4(0.f, 0.f, 0.f, 0.f), cs = make_float4(1.f, 1.f, 1.f, 1.f);
-  if (ep.bias) bias = ld4f(ep.bias + n);
-  if (ep.colscale) cs = ld4f(ep.colscale + n);
-  cs.x *= ep.alpha; cs.y *= ep.alpha; cs.z *= ep.alpha; cs.w *= ep.alpha;
-  float4 lc1 = make_float4(0.f, 0.f, 0.f, 0.f), lc2 = lc1;
-  if (ep.ln_part_in) { lc1 = ld4f(ep.ln_c1 + n); lc2 = ld4f(ep.ln_c2 + n); }
+  const float4 bias = sv.bias, cs = sv.cs, lc1 = sv.lc1, lc2 = sv.lc2;
   const unsigned grp_mask = 0xFu << ((threadIdx.x & 31) & ~3);   // the 4 lanes that share a row and a 16-feature block
   const float* src = slab + fv * 4;
   for (int m = et / FV; m < P.M; m += mstep) {
@@ -276,7 +294,7 @@ __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcP
       float m2 = fmaf(d0, d0, fmaf(d1, d1, fmaf(d2, d2, d3 * d3)));
       m2 += __shfl_xor_sync(grp_mask, m2, 1);
       m2 += __shfl_xor_sync(grp_mask, m2, 2);
-      if ((fv & 3) == 0) ep.ln_part_out[(long long)m * (P.N >> 4) + (n >> 4)] = make_float2(sum, m2);
+      if ((fv & 3) == 0) ep.ln_part_out[(long long)(n >> 4) * P.M + m] = make_float2(sum, m2);   // [block][row]: full-sector runs
     }
     act_inplace<4>(v, ep.act_post);
     store4(reinterpret_cast<TO*>(ep.out) + (long long)m * ep.out_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
@@ -291,28 +309,25 @@ __device__ __forceinline__ void ln_combine(const GemmEpilogue& ep, int M, float2
   const unsigned mask = 0xFu << ((threadIdx.x & 31) & ~3);
   const int j = et & 3;
   for (int m = et >> 2; m < M; m += 64) {
-    const float2* pr = ep.ln_part_in + (long long)m * np;
+    const float2* pr = ep.ln_part_in + m;               // partial i of row m at pr[i * M]
     float tot = 0.0f, q = 0.0f, mu;
     if (np == 64) {   // d_model 1024: 16 partials per lane, all loads in flight at once
-      float4 v[8];
+      float2 v[16];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = ld4f(reinterpret_cast<const float*>(pr + 16 * j) + 4 * i);
+      for (int i = 0; i < 16; ++i) v[i] = pr[(long long)(16 * j + i) * M];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) tot += v[i].x + v[i].z;
+      for (int i = 0; i < 16; ++i) tot += v[i].x;
       tot += __shfl_xor_sync(mask, tot, 1);
       tot += __shfl_xor_sync(mask, tot, 2);
       mu = tot * inv_d;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float d0 = v[i].x * (1.0f / 16.0f) - mu, d1 = v[i].z * (1.0f / 16.0f) - mu;
-        q += (v[i].y + 16.0f * d0 * d0) + (v[i].w + 16.0f * d1 * d1);
-      }
+      for (int i = 0; i < 16; ++i) { const float dm = v[i].x * (1.0f / 16.0f) - mu; q += v[i].y + 16.0f * dm * dm; }
     } else {
-      for (int i = j; i < np; i += 4) tot += pr[i].x;
+      for (int i = j; i < np; i += 4) tot += pr[(long long)i * M].x;
       tot += __shfl_xor_sync(mask, tot, 1);
       tot += __shfl_xor_sync(mask, tot, 2);
       mu = tot * inv_d;
-      for (int i = j; i < np; i += 4) { const float2 p = pr[i]; const float dm = p.x * (1.0f / 16.0f) - mu; q += p.y + 16.0f * dm * dm; }
+      for (int i = j; i < np; i += 4) { const float2 p = pr[(long long)i * M]; const float dm = p.x * (1.0f / 16.0f) - mu; q += p.y + 16.0f * dm * dm; }
     }
     q += __shfl_xor_sync(mask, q, 1);
     q += __shfl_xor_sync(mask, q, 2);
@@ -339,6 +354,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 2) TC_TRACE(4);
   pdl_launch_dependents();               // the next kernel may start its own prologue / weight stream
+  __shared__ unsigned tl_slot;
+  const unsigned tl = tl_begin((1 << 28) | (P.N << 8) | P.num_kb);
+  if (threadIdx.x == 0) tl_slot = tl;
   const int row0 = blockIdx.x * BM_TC;   // UMMA-M operand row offset
   const int col0 = blockIdx.y * BN;      // UMMA-N operand row offset
   const int kb0 = blockIdx.z * P.kb_per_split;
@@ -352,6 +370,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   const int w_row = SWAP ? row0 : col0, a_row = SWAP ? col0 : row0;
   const uint32_t w_off = SWAP ? 0u : A_BYTES, a_off = SWAP ? A_BYTES : 0u;
 
+  if (SWAP && P.w_base && nkb > n_pre) {
+    // the ring holds only n_pre k-blocks before the producer kernel is done: pull the rest of this CTA's weight
+    // slice into L2 now (weights depend on nothing), so the later ring passes are L2 hits instead of HBM round trips
+    const int lines = nkb - n_pre;                       // 128-byte lines per weight row still to come
+    const char* wb = reinterpret_cast<const char*>(P.w_base + (size_t)row0 * P.w_ld + (size_t)(kb0 + n_pre) * BK_TC);
+    const int rows = min(BM_TC, P.N - row0);
+    for (int idx = threadIdx.x; idx < rows * lines; idx += TC_THREADS) {
+      const int r = idx / lines, l = idx - r * lines;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(wb + (size_t)r * P.w_ld * 2 + (size_t)l * 128));
+    }
+  }
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_row) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_col) : "memory");
@@ -377,11 +406,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   __syncthreads();
   tc_fence_after();
   pdl_wait();                            // everything below may read the previous kernel's outputs
+  tl_mark(tl, 2);
   if (clustered) cluster_arrive_relaxed();   // "this CTA runs": peers may write its slabs after the matching wait
   const uint32_t tmem_base = tmem_base_smem;
   if (warp == 2) TC_TRACE(0);
 
   const uint32_t tiles_a = smem_u32(tiles), full_a = smem_u32(&full_bar[0]), empty_a = smem_u32(&empty_bar[0]);
+  SlabVecs sv{};
   if (warp == 0) {
     // ===== TMA producer: the whole warp walks the ring, one lane issues.  Stage / phase are
     // tracked incrementally: a runtime i % stages costs more than the two TMA issues. =====
@@ -411,6 +442,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     for (int i = 0; i < nkb; ++i) {
       mbar_wait_a(full_a + 8u * s, ph);
       tc_fence_after();
+      if (i == 0 && lane == 0 && blockIdx.x + blockIdx.y + blockIdx.z == 0) tl_mark(tl_slot, 4);   // first operands landed
       TC_TRACE(8 + i * 4 + 1);
       if (lane == 0) {
         const uint64_t soff = (uint64_t)((s * STAGE_BYTES) >> 4);   // stage offset in the 16-byte address field
@@ -435,8 +467,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     const int q = warp & 3, half = (warp - 2) >> 2;
     if (warp == 2) TC_TRACE(1);
     if (SWAP && ep.ln_part_in) ln_combine(ep, P.M, ln_stat, (int)threadIdx.x - 64);
+    if (clustered) sv = slab_vecs_load(ep, P, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64);
+    const bool tl_me = warp == 2 && lane == 0 && blockIdx.x + blockIdx.y + blockIdx.z == 0;
+    if (tl_me) tl_mark(tl_slot, 5);                  // epilogue warps ready (LayerNorm statistics combined)
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
+    if (tl_me) tl_mark(tl_slot, 6);                  // accumulator complete
     if (warp == 2) TC_TRACE(2);
     const int r = row0 + q * 32 + lane;             // UMMA-M index owned by this thread
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
@@ -453,11 +489,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   if (clustered) {
     cluster_arrive_release();                 // this CTA's pushes are done ...
     cluster_wait_acquire();                   // ... and so are everybody else's into this CTA
+    if (warp == 2 && lane == 0 && blockIdx.x + blockIdx.y + blockIdx.z == 0) tl_mark(tl_slot, 7);   // partial slabs exchanged
     if (warp == 2) TC_TRACE(5);
-    if (warp >= 2) epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64, ln_stat);
+    if (warp >= 2) epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64, ln_stat, sv);
     if (warp == 2) TC_TRACE(6);
   }
   __syncthreads();
+  tl_mark(tl, 3);
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
@@ -746,10 +784,18 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     const int bn = pick_bn(p.M);
     if (!tc_make_map(&tw, p.W, p.N, p.K, p.K, BM_TC)) return cudaErrorUnknown;
     if (!tc_make_map(&ta, p.A, a_rows_alloc, p.K, p.a_map.ld, bn)) return cudaErrorUnknown;
+    static const bool w_prefetch = [] { const char* e = getenv("PTTS_W_PREFETCH"); return !(e && e[0] == '0'); }();
+    P.w_base = w_prefetch ? reinterpret_cast<const bf16*>(p.W) : nullptr;
+    P.w_ld = p.K;
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
     // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix
     int splits = 1;
     while (splits < 8 && splits * 2 <= p.max_splits && splits * 2 <= P.num_kb && tiles * splits * 2 <= n_sms) splits *= 2;
+    // wide matrices (80 tiles of the AdaLN modulation) run the column epilogue for ~10 us (timeline); a 2-way split with the
+    // slab epilogue halves CTA 0's time but its 160 CTAs no longer fit one wave beside the early-launched kernels: 13 -> 22 us
+    // on the chain (measured), so it stays opt-in
+    static const bool wide_split = [] { const char* e = getenv("PTTS_WIDE_SPLIT"); return e && e[0] == '1'; }();
+    if (wide_split && splits == 1 && p.max_splits >= 2 && tiles <= n_sms && P.num_kb >= 4) splits = 2;
     if (p.N % 4 != 0) splits = 1;   // the slab epilogue works on 4-feature vectors
     P.kb_per_split = (P.num_kb + splits - 1) / splits;
     if ((P.num_kb + P.kb_per_split - 1) / P.kb_per_split != splits) { splits = 1; P.kb_per_split = P.num_kb; }

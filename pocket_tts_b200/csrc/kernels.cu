@@ -5,6 +5,8 @@
 
 namespace ptts {
 
+PTTS_TL_ENABLE_FN(kernels)
+
 // =====================================================================================
 // FlowLM input embedding                                              flow_lm.py:121-122
 // =====================================================================================
@@ -13,7 +15,9 @@ flow_embed_kernel(const float* __restrict__ prev, const int* __restrict__ slot_i
                   const float* __restrict__ bos, const float* __restrict__ w_in,
                   float* __restrict__ h, int d, int ldim) {
   pdl_launch_dependents();
+  const unsigned tl = tl_begin(5);
   pdl_wait();
+  tl_mark(tl, 2);
   __shared__ float seq[64];
   const int i = blockIdx.x, slot = slot_ids[i];
   if (threadIdx.x < ldim) {
@@ -51,7 +55,9 @@ __global__ void __launch_bounds__(128)
 ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                float eps, TO* __restrict__ y, int d) {
   pdl_launch_dependents();
+  const unsigned tl = tl_begin(3);
   pdl_wait();
+  tl_mark(tl, 2);
   __shared__ float scratch[33];
   const long long row = blockIdx.x;
   const float* xr = x + row * d;
@@ -109,7 +115,9 @@ final_norm_eos_kernel(const float* __restrict__ h, const float* __restrict__ w,
                       float* __restrict__ eos_logit, int d, int* __restrict__ offsets,
                       const int* __restrict__ slot_ids) {
   pdl_launch_dependents();
+  const unsigned tl = tl_begin(4);
   pdl_wait();
+  tl_mark(tl, 2);
   __shared__ float scratch[33];
   const long long row = blockIdx.x;
   const float* xr = h + row * d;
