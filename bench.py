@@ -129,6 +129,7 @@ def run_ours(args, rank, world, local_rank):
     dist = world > 1
     if dist:
         import torch.distributed as td
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's version banner / debug lines must not land on stdout
         td.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     def barrier():
@@ -287,7 +288,7 @@ def ncu_traffic_bytes(tag):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` summary
     (profiles/), taken at the start of the generation (context 166-172); None when no capture exists."""
     import csv
-    f = {"flow.attn_decode": ROOT / "profiles" / "r01_attn_decode_ncu_full_summary.csv"}.get(tag)
+    f = {"flow.attn_decode": ROOT / "profiles" / "r01_attn_head_ncu_full_summary.csv"}.get(tag)
     if not f or not f.exists():
         return None
     rows = list(csv.reader(open(f)))

@@ -516,7 +516,10 @@ __global__ void __launch_bounds__(256)
 attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
                   const int* __restrict__ offsets, const int* __restrict__ slot_ids,
                   const int* __restrict__ row_start, const int* __restrict__ lens, KvGeom g, int layer,
-                  int context, TO* __restrict__ out) {
+                  int context, TO* __restrict__ out, int mode) {
+  // mode 0: rotate / append, block barrier, attend (one CTA per (head, stream)); mode 1: rotate / append only;
+  // mode 2: attend only, query t = blockIdx.z * 8 + warp (launched after a mode-1 pass: every query of a long
+  // chunk gets its own warp somewhere on the machine instead of queueing behind 8 warps of one CTA)
   pdl_launch_dependents();
   pdl_wait();
   constexpr int NW = 8;
@@ -528,6 +531,7 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
   const int d_model = g.H * 64;
   const float fr = freqs[lane];
 
+  if (mode != 2)
   for (int t = w; t < T; t += NW) {
     float* row = qkv + (long long)(r0 + t) * 3 * d_model + h * 64 + 2 * lane;
     const float pos = (float)(off + t);
@@ -537,11 +541,14 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
     store2(kv_row<TK>(g, layer, slot, 0, h, off + t) + 2 * lane, k);
     store2(kv_row<TK>(g, layer, slot, 1, h, off + t) + 2 * lane, v);
   }
+  if (mode == 1) return;
   __syncthreads();
 
   const TK* kbase = kv_row<TK>(g, layer, slot, 0, h, 0);
   const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0);
-  for (int t = w; t < T; t += NW) {
+  const int t_first = mode == 2 ? (int)blockIdx.z * NW + w : w;
+  const int t_step = mode == 2 ? T : NW;        // mode 2: exactly one query per warp
+  for (int t = t_first; t < T; t += t_step) {
     const float* row = qkv + (long long)(r0 + t) * 3 * d_model + h * 64 + 2 * lane;
     const float2 q = load2(row);
     const int pq = off + t;
@@ -569,18 +576,23 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
 
 cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* offsets,
                               const int* slot_ids, const int* row_start, const int* lens, KvGeom kv,
-                              int layer, int context, void* out, int out_type, int n, cudaStream_t st) {
+                              int layer, int context, void* out, int out_type, int n, cudaStream_t st, int max_len) {
   if (kv.D != 64) return cudaErrorInvalidValue;
   if (kv.ring && (kv.cap & (kv.cap - 1))) return cudaErrorInvalidValue;
-  dim3 grid(kv.H, n);
-  if (kv.type == 0 && out_type == 0)
-    launch_k(attn_chunk_kernel<float, float>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (float*)out);
-  else if (kv.type == 1 && out_type == 1)
-    launch_k(attn_chunk_kernel<bf16, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
-  else if (kv.type == 0 && out_type == 1)
-    launch_k(attn_chunk_kernel<float, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out);
-  else
-    return cudaErrorInvalidValue;
+  // chunks longer than one query per warp: an append pass, then an attend pass with one warp per query
+  static const bool split_on = [] { const char* e = getenv("PTTS_PREFILL_SPLIT"); return !(e && e[0] == '0'); }();
+  const bool split = split_on && max_len > 8 && !kv.ring;
+  for (int pass = split ? 1 : 0; pass <= (split ? 2 : 0); ++pass) {
+    dim3 grid(kv.H, n, pass == 2 ? (max_len + 7) / 8 : 1);
+    if (kv.type == 0 && out_type == 0)
+      launch_k(attn_chunk_kernel<float, float>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (float*)out, pass);
+    else if (kv.type == 1 && out_type == 1)
+      launch_k(attn_chunk_kernel<bf16, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out, pass);
+    else if (kv.type == 0 && out_type == 1)
+      launch_k(attn_chunk_kernel<float, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out, pass);
+    else
+      return cudaErrorInvalidValue;
+  }
   return cudaGetLastError();
 }
 

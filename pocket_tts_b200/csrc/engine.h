@@ -227,6 +227,7 @@ class Engine {
 
   std::map<GraphKey, GraphEntry> graphs;
   std::vector<int> cur_slots;
+  int prefill_max_len = 0;                   // longest chunk of the current prefill batch (selects the two-pass attention)
   float* h_pinned = nullptr;
   float* lat_ring[2] = {nullptr, nullptr};   // latents [mimi_gmax][S][ldim] handed from the FlowLM branch to the Mimi branch
   float* pcm_ring[2] = {nullptr, nullptr};   // PCM [S][mimi_gmax * 1920] of the group decoded by the Mimi branch

@@ -171,6 +171,8 @@ int Engine::prefill(int n, const int* slots, const int* lens, const float* embed
     rows += lens[i];
   }
   if (rows > max_rows) PTTS_FAIL(PTTS_EINVAL, "prefill: %d rows exceed max_prefill_rows %d", rows, max_rows);
+  prefill_max_len = 0;
+  for (int i = 0; i < n; ++i) prefill_max_len = std::max(prefill_max_len, lens[i]);
   if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
   PTTS_CUDA_CHECK(cudaMemcpyAsync(d_row_start, rs.data(), n * sizeof(int), cudaMemcpyHostToDevice, stream));
   PTTS_CUDA_CHECK(cudaMemcpyAsync(d_lens, lens, n * sizeof(int), cudaMemcpyHostToDevice, stream));

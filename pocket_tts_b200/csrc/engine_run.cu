@@ -85,7 +85,7 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
     LAUNCH("flow.attn_decode", launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, kv_flow, li, ao, act_type, n, stream));
   } else {
     LAUNCH("flow.attn_prefill", launch_attn_chunk(qkvb, rope_freqs, offsets, d_slot_ids, d_row_start, d_lens, kv_flow, li,
-                             INT_MAX / 2, ao, act_type, n, stream));
+                             INT_MAX / 2, ao, act_type, n, stream, prefill_max_len));
   }
   {
     GemmEpilogue ep; ep.out = hbuf; ep.out_map = plain(d); ep.res = hbuf; ep.res_map = plain(d);

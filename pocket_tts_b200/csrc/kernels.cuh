@@ -37,7 +37,8 @@ cudaError_t launch_attn_decode(const float* qkv /*[n,3*H*D]*/, const float* rope
 // q is rotated in place inside qkv.
 cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* offsets,
                               const int* slot_ids, const int* row_start, const int* lens, KvGeom kv,
-                              int layer, int context, void* out, int out_type, int n, cudaStream_t st);
+                              int layer, int context, void* out, int out_type, int n, cudaStream_t st,
+                              int max_len = 0 /* longest chunk of the batch (host-known); > 8 selects the two-pass form */);
 
 // Mimi decoder attention: exactly T (<= 16) new tokens per stream (rows i*T.. of qkv), sliding
 // window `context` over the ring cache; the visible window is staged once in shared memory.
