@@ -140,6 +140,7 @@ int Engine::init() {
       if (tl_buf) { tl_enable_kernels(tl_buf); tl_enable_gemm_tc(tl_buf); tl_enable_attention(tl_buf); tl_enable_head_tc(tl_buf); }
     }
   }
+  if (const char* f = getenv("PTTS_KV_SIDE")) use_kv_side_prefetch = f[0] == '1';
   if (const char* f = getenv("PTTS_LNFOLD")) use_ln_fold = !(f[0] == '0');
   if (const char* f = getenv("PTTS_HEAD")) head_mode = f[0] >= '0' && f[0] <= '2' ? f[0] - '0' : 2;
   for (int k = 0; k < 2; ++k) {

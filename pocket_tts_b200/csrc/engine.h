@@ -134,7 +134,8 @@ class Engine {
   int make_mat_from(const std::vector<float>& host, int N, int K, Mat* m, bool want_b16 = true);
   float* upload(const std::vector<float>& host);
   int gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, const Mat& W, int M, GemmEpilogue ep,
-           bool out_is_act);
+           bool out_is_act, const KvPrefetchJob* kv_prefetch = nullptr);
+  KvPrefetchJob flow_kv_prefetch_job(int layer, int n) const;
   void prof_begin(const char* tag);
   void prof_end();
   int make_ln_folded(const std::string& wname, const std::string& gname, const std::string& bname, int N, int K, Mat* m,
@@ -237,6 +238,7 @@ class Engine {
   cudaStream_t side_stream = nullptr;        // side branch of the FlowLM graph (input_proj of the first Euler step)
   cudaEvent_t ev_side_fork = nullptr, ev_side_join = nullptr;
   bool use_side_branch = true;               // PTTS_SIDE=0 disables
+  bool use_kv_side_prefetch = false;         // PTTS_KV_SIDE=1: the QKV GEMM's idle epilogue warps prefetch the layer's K/V rows for the attention kernel (measured: attention 13.2 -> 12.8 us but the GEMM 8.5 -> 10.6 us on the chain, so off)
   bool use_ln_fold = true;                   // PTTS_LNFOLD=0: separate LayerNorm launches in the FlowLM decode layers
   int head_mode = 2;                         // PTTS_HEAD: 0 flow head as separate launches, 1 cluster kernel on mma.sync (flow_head.cu), 2 on tcgen05 (flow_head_tc.cu)
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph

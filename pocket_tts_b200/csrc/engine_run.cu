@@ -35,9 +35,25 @@ static bool skip_tag(const char* tag) {
 
 // D = epilogue(A W^T).  a_is_act: A stored in the activation type (else fp32);
 // out_is_act: out / out2 / res stored in the activation type (else fp32).
+// K/V rows of FlowLM layer `layer` for the n streams in d_slot_ids: (k|v, head) regions of kv_capacity rows each
+KvPrefetchJob Engine::flow_kv_prefetch_job(int layer, int n) const {
+  KvPrefetchJob j;
+  if (!use_kv_side_prefetch || kv_flow.ring) return j;
+  const long long region = (long long)kv_flow.cap * kv_flow.D * (long long)act_size;
+  j.regions = 2 * kv_flow.H;
+  j.region_stride = region;
+  j.slot_stride = region * j.regions;
+  j.base = reinterpret_cast<const char*>(kv_flow.base) + (long long)layer * kv_flow.n_slots * j.slot_stride;
+  j.slot_ids = d_slot_ids; j.offsets = offsets;
+  j.row_bytes = kv_flow.D * (int)act_size;
+  j.n = n;
+  return j;
+}
+
 int Engine::gemm(const char* tag, const void* A, bool a_is_act, RowMap amap, const Mat& W, int M,
-                 GemmEpilogue ep, bool out_is_act) {
+                 GemmEpilogue ep, bool out_is_act, const KvPrefetchJob* kv_prefetch) {
   GemmProblem p;
+  if (kv_prefetch) p.kv_prefetch = *kv_prefetch;
   p.A = A; p.a_map = amap; p.M = M; p.N = W.N; p.K = W.K; p.ep = ep;
   {  // developer override of the split-K factor per tag: PTTS_SPLITS="flow.ffn1:2,flow.qkv:4"
     static const char* list = getenv("PTTS_SPLITS");
@@ -113,15 +129,16 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
 int Engine::flow_layer_decode_folded(int l, int n) {
   const LayerW& L = flow_layers[l];
   const int d = cfg.d_model, ffn = cfg.ffn, np = d / 16;
+  const KvPrefetchJob pf = flow_kv_prefetch_job(l, n);
   int rc;
   if (l == 0) {
     LAUNCH("flow.ln", launch_ln_rows(h, L.n1w, L.n1b, 1e-5f, a_ln, act_type, n, d, stream));
     GemmEpilogue ep; ep.out = qkv; ep.out_map = plain(3 * d);
-    if ((rc = gemm("flow.qkv", a_ln, true, plain(d), L.in_proj, n, ep, false)) != PTTS_OK) return rc;
+    if ((rc = gemm("flow.qkv", a_ln, true, plain(d), L.in_proj, n, ep, false, &pf)) != PTTS_OK) return rc;
   } else {
     GemmEpilogue ep; ep.out = qkv; ep.out_map = plain(3 * d);
     ep.ln_part_in = ln_part; ep.ln_nparts = np; ep.ln_c1 = L.qkv_c1; ep.ln_c2 = L.qkv_c2;
-    if ((rc = gemm("flow.qkv", h16, true, plain(d), L.in_proj_ln, n, ep, false)) != PTTS_OK) return rc;
+    if ((rc = gemm("flow.qkv", h16, true, plain(d), L.in_proj_ln, n, ep, false, &pf)) != PTTS_OK) return rc;
   }
   LAUNCH("flow.attn_decode", launch_attn_decode(qkv, rope_freqs, offsets, d_slot_ids, kv_flow, l, attn_o, act_type, n, stream));
   {

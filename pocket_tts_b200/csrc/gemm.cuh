@@ -41,6 +41,18 @@ struct GemmEpilogue {
   const float* ln_c2 = nullptr;     // [N] sum_k W[n,k] beta[k]
 };
 
+// Optional side job of a skinny GEMM: while it is resident ahead of its producer (programmatic dependent launch),
+// its epilogue warps pull the cached K/V rows that the NEXT kernel (decode attention of the same layer) will read
+// into L2.  Region r of stream i starts at base + slot_ids[i] * slot_stride + r * region_stride and holds
+// offsets[slot] rows of row_bytes.
+struct KvPrefetchJob {
+  const char* base = nullptr;
+  const int* slot_ids = nullptr;
+  const int* offsets = nullptr;
+  long long slot_stride = 0, region_stride = 0;
+  int row_bytes = 0, regions = 0, n = 0;
+};
+
 struct GemmProblem {
   const void* A = nullptr;
   RowMap a_map{0, 1 << 30, 1 << 30, 0};
@@ -48,6 +60,7 @@ struct GemmProblem {
   int M = 0, N = 0, K = 0;
   GemmEpilogue ep;
   int max_splits = 8;       // skinny tcgen05 path: upper bound of the cluster split-K factor
+  KvPrefetchJob kv_prefetch;
 };
 
 // element types: 0 = float, 1 = bf16

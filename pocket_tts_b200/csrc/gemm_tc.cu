@@ -53,6 +53,7 @@ struct TcParams {
   int cluster;         // SWAP split-K: CTAs per cluster along z (partials reduced through DSMEM)
   const bf16* w_base;  // SWAP: weight matrix [N, w_ld] for the L2 prefetch of this CTA's slice (nullptr: none)
   int w_ld;
+  KvPrefetchJob pf;    // SWAP: K/V rows of the following decode attention -> L2 (base == nullptr: none)
   long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
 };
 #define TC_TRACE(slot) do { if (P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) P.trace[slot] = clock64(); } while (0)
@@ -379,6 +380,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     for (int idx = threadIdx.x; idx < rows * lines; idx += TC_THREADS) {
       const int r = idx / lines, l = idx - r * lines;
       asm volatile("prefetch.global.L2 [%0];" ::"l"(wb + (size_t)r * P.w_ld * 2 + (size_t)l * 128));
+    }
+  }
+  if (SWAP && P.pf.base && warp >= 2) {
+    // side job (KvPrefetchJob): one (stream, k|v, head) region per epilogue warp at a time
+    const int G = (int)(gridDim.x * gridDim.z) * 8, wid = ((int)(blockIdx.z * gridDim.x + blockIdx.x)) * 8 + (warp - 2);
+    const int R = P.pf.n * P.pf.regions;
+    for (int r = wid; r < R; r += G) {
+      const int i = r / P.pf.regions, q = r - i * P.pf.regions;
+      const int slot = P.pf.slot_ids[i];
+      const int bytes = P.pf.offsets[slot] * P.pf.row_bytes;
+      const char* p = P.pf.base + (long long)slot * P.pf.slot_stride + (long long)q * P.pf.region_stride;
+      for (int off = lane * 128; off < bytes; off += 32 * 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(p + off));
     }
   }
   if (warp == 0 && lane == 0) {
@@ -787,6 +800,7 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     static const bool w_prefetch = [] { const char* e = getenv("PTTS_W_PREFETCH"); return !(e && e[0] == '0'); }();
     P.w_base = w_prefetch ? reinterpret_cast<const bf16*>(p.W) : nullptr;
     P.w_ld = p.K;
+    P.pf = p.kv_prefetch;
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
     // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix
     int splits = 1;
