@@ -54,6 +54,8 @@ struct TcParams {
   const bf16* w_base;  // SWAP: weight matrix [N, w_ld] for the L2 prefetch of this CTA's slice (nullptr: none)
   int w_ld;
   KvPrefetchJob pf;    // SWAP: K/V rows of the following decode attention -> L2 (base == nullptr: none)
+  int slab1;           // SWAP, cluster == 1: still go through the slab epilogue (transpose in this CTA's shared memory,
+                       // row-contiguous 16-byte stores) instead of the column epilogue (one 4-byte store per stream row)
   long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
 };
 #define TC_TRACE(slot) do { if (P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) P.trace[slot] = clock64(); } while (0)
@@ -364,7 +366,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   const int nkb = min(P.kb_per_split, P.num_kb - kb0);
   const int n_pre = min(P.stages, nkb);  // stages filled before the set-up barrier
   constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
-  const bool clustered = SWAP && P.cluster > 1;
+  const bool clustered = SWAP && (P.cluster > 1 || P.slab1);
   // weights are the UMMA-M operand in the swapped orientation, the UMMA-N operand otherwise
   const CUtensorMap* tm_w = SWAP ? &tm_row : &tm_col;
   const CUtensorMap* tm_a = SWAP ? &tm_col : &tm_row;
@@ -493,7 +495,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
       cluster_wait_acquire();                        // every peer CTA has started
       partial_push<BN>(P, taddr, slab, P.cluster, (int)blockIdx.z, q * 32 + lane, half);
     } else if (nkb > 0) {
-      if (SWAP) epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half, ln_stat);
+      if (SWAP) {
+        epilogue_cols<BN, TO>(ep, P, taddr, r, col0, half, ln_stat);
+        if (tl_me) tl_mark(tl_slot, 7);              // column epilogue of warp 2 done
+      }
       else epilogue_rows<BN, TO>(ep, P.M, P.N, taddr, row0, col0, q, half, lane, tiles);
     }
     tc_fence_before();
@@ -684,7 +689,7 @@ constexpr size_t TC_ROWS_SMEM = 112 * 1024;         // persistent row-major kern
 template <int BN, bool SWAP, typename TO>
 static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, const TcParams& P, const GemmEpilogue& ep,
                               dim3 grid, bool pdl, cudaStream_t st) {
-  const bool clustered = SWAP && P.cluster > 1;
+  const bool clustered = SWAP && (P.cluster > 1 || P.slab1);
   size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + (clustered ? (size_t)BN * BM_TC * sizeof(float) : 0);
   if (!SWAP) smem = std::max(smem, EPI_SMEM_BYTES);   // the epilogue staging reuses the (drained) pipeline buffers
   smem += 1024;
@@ -703,7 +708,7 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   int na = 0;
-  if (clustered) {
+  if (clustered && P.cluster > 1) {
     attr[na].id = cudaLaunchAttributeClusterDimension;
     attr[na].val.clusterDim.x = 1;
     attr[na].val.clusterDim.y = 1;
@@ -816,7 +821,9 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     P.cluster = splits;
     if (ep.ln_part_out && (splits == 1 || p.N % 16 != 0 || !ep.ln_raw)) return cudaErrorInvalidValue;   // partials come from the slab epilogue
     if (ep.ln_part_in && (ep.ln_nparts * 16 != p.K || !ep.ln_c1 || !ep.ln_c2 || p.M > 128)) return cudaErrorInvalidValue;
-    const size_t stage = (size_t)(BM_TC + bn) * 128, slab = splits > 1 ? (size_t)bn * BM_TC * sizeof(float) : 0;
+    static const bool cols_slab = [] { const char* e = getenv("PTTS_COLS_SLAB"); return !(e && e[0] == '0'); }();
+    P.slab1 = (cols_slab && splits == 1 && p.N % 4 == 0 && !ep.ln_part_out) ? 1 : 0;
+    const size_t stage = (size_t)(BM_TC + bn) * 128, slab = (splits > 1 || P.slab1) ? (size_t)bn * BM_TC * sizeof(float) : 0;
     // keep a CTA under ~half an SM's shared memory when possible: kernels of the two graph branches
     // (FlowLM chain || Mimi chain) and consecutive waves can then share an SM
     const size_t budget = (stage + slab <= TC_CORESIDENT_SMEM) ? TC_CORESIDENT_SMEM : TC_SMEM_LIMIT;

@@ -16,6 +16,9 @@ flow_embed_kernel(const float* __restrict__ prev, const int* __restrict__ slot_i
                   float* __restrict__ h, int d, int ldim) {
   pdl_launch_dependents();
   const unsigned tl = tl_begin(5);
+  // input_linear's weight (128 KB, cold every step) -> L2 while the previous kernel is still running
+  for (int off = (blockIdx.x * blockDim.x + threadIdx.x) * 128; off < d * ldim * 4; off += gridDim.x * blockDim.x * 128)
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(w_in) + off));
   pdl_wait();
   tl_mark(tl, 2);
   __shared__ float seq[64];
