@@ -115,6 +115,8 @@ int Engine::init() {
   if (const char* f = getenv("PTTS_LOOP")) loop_fork = f[0] == 'f';
   PTTS_CUDA_CHECK(cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, c.device));
   n_sms_flow = n_sms_mimi = n_sms;
+  // PTTS_MIMI_GRID_SMS=k: size the grids of the Mimi branch for k SMs (no partition: it only leaves SMs idle for the FlowLM chain)
+  if (const char* f = getenv("PTTS_MIMI_GRID_SMS")) { const int k = atoi(f); if (k >= 8 && k <= n_sms) n_sms_mimi = k; }
   {  // PTTS_FLOW_SMS=k: FlowLM chain on k SMs, Mimi branch on the others (green contexts); 0 / unset: shared SMs
     const char* e = getenv("PTTS_FLOW_SMS");
     const int want = e ? atoi(e) : 0;

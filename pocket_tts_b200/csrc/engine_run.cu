@@ -148,6 +148,8 @@ int Engine::flow_layer_decode_folded(int l, int n) {
   }
   {
     GemmEpilogue ep; ep.out = mid; ep.out_map = plain(ffn); ep.act_pre = ACT_GELU;
+    static const bool no_gelu = getenv("PTTS_DEBUG_NOGELU") != nullptr;   // timing probe only (wrong results)
+    if (no_gelu) ep.act_pre = ACT_NONE;
     ep.ln_part_in = ln_part; ep.ln_nparts = np; ep.ln_c1 = L.ffn_c1; ep.ln_c2 = L.ffn_c2;
     if ((rc = gemm("flow.ffn1", h16, true, plain(d), L.lin1_ln, n, ep, true)) != PTTS_OK) return rc;
   }
