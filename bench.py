@@ -137,6 +137,14 @@ def run_ours(args, rank, world, local_rank):
             td.barrier()
         torch.cuda.synchronize()
 
+    # one-off set-up outside every timed region: a throw-away batch runs 12 frames so that every kernel module is
+    # loaded and every graph variant of the loop (group sizes 1, 1, 2, 4, 4) is captured before anything is timed
+    # (on a fresh box the first 4-frame Mimi pass otherwise pays lazy module loading inside the timed region)
+    slots, noise = fresh_streams(99)
+    eng.run_frames(slots, noise[:min(12, Wm + K)].cuda().contiguous())
+    eng.synchronize()
+    close(slots)
+
     # ---------------- device-resident timed region (value) ----------------
     slots, noise = fresh_streams(0)
     noise_dev = noise.cuda()
@@ -197,11 +205,11 @@ def run_ours(args, rank, world, local_rank):
                 tokens, voice, noise = synth_inputs(dims, nb, 1, 50 + trial)
                 sl = [eng.open_stream() for _ in range(nb)]
                 eng.prefill(sl, [torch.cat([bos, voice[i]]) for i in range(nb)])
-                text = [emb[tokens[i]] for i in range(nb)]
+                text = [tokens[i].tolist() for i in range(nb)]
                 nz = noise[0].pin_memory()
                 eng.synchronize()
                 t0 = time.perf_counter()
-                eng.prefill(sl, text)
+                eng.prefill_tokens(sl, text)                       # token ids in, embedding gather on the device
                 eng.step(sl, nz)                                   # returns latents, EOS logits and PCM on the host
                 times.append((time.perf_counter() - t0) * 1e3)
                 close(sl)

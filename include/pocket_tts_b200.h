@@ -108,6 +108,14 @@ int ptts_stream_set_prev_latent(ptts_engine* e, int32_t slot, const float* laten
 int ptts_prefill(ptts_engine* e, int32_t n, const int32_t* slots, const int32_t* lens,
                  const float* embeds_any);
 
+/* Text prefill from token ids: the LUT conditioner's embedding gather (conditioners/text.py:74-76,
+ * called from tts_model.py:718-725) runs on the device from the table loaded as
+ * "flow_lm.conditioner.embed.weight", so a text chunk crosses the bus as 4 bytes per token instead
+ * of 4 KB.  tokens [sum(lens)] are sentencepiece ids in [0, table rows); PTTS_EINVAL otherwise or
+ * when the table was not loaded. */
+int ptts_prefill_tokens(ptts_engine* e, int32_t n, const int32_t* slots, const int32_t* lens,
+                        const int32_t* tokens);
+
 /* One frame for n streams: FlowLM step + flow head (+ optional Mimi decode).
  * _autoregressive_generation body (tts_model.py:756-768) + _decode_audio_worker body
  * (tts_model.py:449-455).  noise_any [n, ldim] is the injected N(0, temp) draw

@@ -61,6 +61,7 @@ def load_library() -> C.CDLL:
         "ptts_stream_get_offset": (C.c_int, [p, i32, i32p]),
         "ptts_stream_set_prev_latent": (C.c_int, [p, i32, f32p]),
         "ptts_prefill": (C.c_int, [p, i32, i32p, i32p, f32p]),
+        "ptts_prefill_tokens": (C.c_int, [p, i32, i32p, i32p, i32p]),
         "ptts_step": (C.c_int, [p, i32, i32p, f32p, i32, i32, f32p, f32p, f32p]),
         "ptts_mimi_decode": (C.c_int, [p, i32, i32p, f32p, f32p]),
         "ptts_run_frames": (C.c_int, [p, i32, i32p, i32, f32p, i32, f32p, f32p]),

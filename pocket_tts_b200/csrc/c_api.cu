@@ -109,6 +109,9 @@ int ptts_stream_set_prev_latent(ptts_engine* e, int32_t slot, const float* laten
 int ptts_prefill(ptts_engine* e, int32_t n, const int32_t* slots, const int32_t* lens, const float* embeds_any) {
   API_BEGIN NEED(e) return e->impl->prefill(n, slots, lens, embeds_any); API_END
 }
+int ptts_prefill_tokens(ptts_engine* e, int32_t n, const int32_t* slots, const int32_t* lens, const int32_t* tokens) {
+  API_BEGIN NEED(e) return e->impl->prefill(n, slots, lens, nullptr, tokens); API_END
+}
 int ptts_step(ptts_engine* e, int32_t n, const int32_t* slots, const float* noise_any, int32_t lsd_steps,
               int32_t decode_audio, float* out_latents_any, float* out_eos_logit_any, float* out_pcm_any) {
   API_BEGIN NEED(e)

@@ -178,6 +178,7 @@ int Engine::init() {
   const int D = c.d_model, F = c.flow_dim, Md = c.mimi_d;
   d_slot_ids = dmalloc<int>(allocs, S, stream);
   d_row_start = dmalloc<int>(allocs, S, stream);
+  d_tokens = dmalloc<int>(allocs, max_rows, stream);
   d_lens = dmalloc<int>(allocs, S, stream);
   d_mimi_row_start = dmalloc<int>(allocs, S, stream);
   d_mimi_lens = dmalloc<int>(allocs, S, stream);

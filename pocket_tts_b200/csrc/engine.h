@@ -100,7 +100,7 @@ class Engine {
   int get_offset(int slot, int* off);
   int set_prev_latent(int slot, const float* latent_any);
 
-  int prefill(int n, const int* slots, const int* lens, const float* embeds_any);
+  int prefill(int n, const int* slots, const int* lens, const float* embeds_any, const int* tokens = nullptr);
   int step(int n, const int* slots, const float* noise_any, int lsd, int audio, float* out_lat,
            float* out_eos, float* out_pcm);
   int mimi_decode(int n, const int* slots, const float* latents_any, float* out_pcm);
@@ -178,6 +178,9 @@ class Engine {
   // weights
   float *bos_emb, *w_in, *out_norm_w, *out_norm_b, *eos_w, *eos_b, *emb_std, *emb_mean;
   float *rope_freqs, *tcomb;
+  float* text_embed = nullptr;               // optional LUT conditioner table [text_embed_rows, d_model] (ptts_prefill_tokens)
+  int text_embed_rows = 0;
+  int* d_tokens = nullptr;                   // [max_rows]
   int tcomb_rows = 0;
   std::vector<LayerW> flow_layers, mimi_layers;
   Mat cond_embed, input_proj, mod_all, final_lin;

@@ -155,11 +155,12 @@ int Engine::upload_slots(int n, const int* slots) {
   return PTTS_OK;
 }
 
-int Engine::prefill(int n, const int* slots, const int* lens, const float* embeds_any) {
+int Engine::prefill(int n, const int* slots, const int* lens, const float* embeds_any, const int* tokens) {
   NEED_READY();
   int rc;
   if ((rc = check_slots(n, slots, false)) != PTTS_OK) return rc;
-  if (!lens || !embeds_any) PTTS_FAIL(PTTS_EINVAL, "prefill: null argument");
+  if (!lens || (!embeds_any && !tokens)) PTTS_FAIL(PTTS_EINVAL, "prefill: null argument");
+  if (tokens && !text_embed) PTTS_FAIL(PTTS_EINVAL, "prefill_tokens: flow_lm.conditioner.embed.weight was not loaded");
   int rows = 0;
   std::vector<int> rs(n);
   for (int i = 0; i < n; ++i) {
@@ -176,7 +177,16 @@ int Engine::prefill(int n, const int* slots, const int* lens, const float* embed
   if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
   PTTS_CUDA_CHECK(cudaMemcpyAsync(d_row_start, rs.data(), n * sizeof(int), cudaMemcpyHostToDevice, stream));
   PTTS_CUDA_CHECK(cudaMemcpyAsync(d_lens, lens, n * sizeof(int), cudaMemcpyHostToDevice, stream));
-  PTTS_CUDA_CHECK(cudaMemcpyAsync(h, embeds_any, (size_t)rows * cfg.d_model * sizeof(float), cudaMemcpyDefault, stream));
+  if (tokens) {
+    for (int r = 0; r < rows; ++r)
+      if (tokens[r] < 0 || tokens[r] >= text_embed_rows)
+        PTTS_FAIL(PTTS_EINVAL, "prefill_tokens: token %d at row %d outside the table of %d rows", tokens[r], r, text_embed_rows);
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(d_tokens, tokens, (size_t)rows * sizeof(int), cudaMemcpyHostToDevice, stream));
+    PTTS_CUDA_CHECK(launch_embed_gather(d_tokens, text_embed, h, rows, cfg.d_model, stream));
+    ++launches;
+  } else {
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(h, embeds_any, (size_t)rows * cfg.d_model * sizeof(float), cudaMemcpyDefault, stream));
+  }
   for (int l = 0; l < cfg.n_layers; ++l) {
     // rows == n would select the decode kernel, which is equivalent for len == 1
     if ((rc = transformer_layer_common(flow_layers[l], h, rows, cfg.d_model, cfg.ffn, a_ln, qkv, attn_o, mid,

@@ -103,6 +103,16 @@ int Engine::finalize() {
     tcomb = upload(it->second.data);
     if (!tcomb) PTTS_FAIL(PTTS_ECUDA, "upload failed");
   }
+  {  // optional: the text conditioner's embedding table, for prefill from token ids
+    auto it = host_w.find("flow_lm.conditioner.embed.weight");
+    if (it != host_w.end()) {
+      if (it->second.shape.size() != 2 || it->second.shape[1] != D)
+        PTTS_FAIL(PTTS_EINVAL, "flow_lm.conditioner.embed.weight must be [rows, d_model]");
+      text_embed_rows = (int)it->second.shape[0];
+      text_embed = upload(it->second.data);
+      if (!text_embed) PTTS_FAIL(PTTS_ECUDA, "upload failed");
+    }
+  }
   flow_layers.resize(c.n_layers);
   for (int i = 0; i < c.n_layers; ++i) {
     const std::string p = "flow_lm.transformer.layers." + std::to_string(i) + ".";

@@ -49,6 +49,21 @@ cudaError_t launch_flow_embed(const float* prev_latent, const int* slot_ids, con
   return cudaGetLastError();
 }
 
+__global__ void embed_gather_kernel(const int* __restrict__ tokens, const float* __restrict__ table,
+                                    float* __restrict__ h, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const float* src = table + (long long)tokens[blockIdx.x] * d;
+  float* dst = h + (long long)blockIdx.x * d;
+  for (int c = threadIdx.x * 4; c < d; c += blockDim.x * 4) store4(dst + c, load4(src + c));
+}
+
+cudaError_t launch_embed_gather(const int* tokens, const float* table, float* h, int rows, int d, cudaStream_t st) {
+  if (d % 4) return cudaErrorInvalidValue;
+  launch_k(embed_gather_kernel, rows, 256, 0, st, tokens, table, h, d);
+  return cudaGetLastError();
+}
+
 // =====================================================================================
 // LayerNorm over rows (nn.LayerNorm, biased variance)      mimi_transformer.py:26-27,47,41
 // one warp-group of 128 threads per row, d <= 1024: each thread owns 2 float4

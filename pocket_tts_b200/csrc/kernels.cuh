@@ -22,6 +22,9 @@ cudaError_t launch_flow_embed(const float* prev_latent, const int* slot_ids, con
                               const float* w_in /*[d,ldim]*/, float* h, int n, int d, int ldim,
                               cudaStream_t st);
 
+// h[r,:] = table[tokens[r],:]   LUT conditioner embedding (conditioners/text.py:74-76); d % 4 == 0
+cudaError_t launch_embed_gather(const int* tokens, const float* table, float* h, int rows, int d, cudaStream_t st);
+
 // y = LayerNorm(x; w, b, eps) rows of width d (<= 1024), x fp32 -> y (act type)
 cudaError_t launch_ln_rows(const float* x, const float* w, const float* b, float eps, void* y,
                            int y_type, int rows, int d, cudaStream_t st);

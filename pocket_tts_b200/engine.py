@@ -116,8 +116,9 @@ class GenerationEngine:
     def _load(self, sd: dict) -> None:
         skip = ("flow_lm.conditioner.", "flow_lm.bos_before_voice", "flow_lm.speaker_proj_weight",
                 "flow_lm.flow_net.time_embed.")  # host-side only / folded into flow.tcomb
+        keep = ("flow_lm.conditioner.embed.weight",)  # device-side embedding gather of prefill_tokens
         for name, t in sd.items():
-            if name.startswith(skip):
+            if name.startswith(skip) and name not in keep:
                 continue
             self._load_one(name, t)
         self._load_one("rope.freqs", rope_freqs(self.cfg.d_model // self.cfg.n_heads, self.cfg.max_period))
@@ -189,6 +190,13 @@ class GenerationEngine:
         lens = [int(e.shape[0]) for e in embeds]
         flat = torch.cat([e.detach().to(torch.float32).reshape(-1, self.cfg.d_model) for e in embeds]).contiguous()
         N.check(self.lib.ptts_prefill(self._h, len(slots), _i32(slots), _i32(lens), _ptr(flat)))
+
+    def prefill_tokens(self, slots, tokens: list) -> None:
+        """tokens[i]: 1-D integer ids of the text chunk of stream slots[i]; the embedding gather
+        (conditioners/text.py:74-76) runs on the device."""
+        lens = [int(len(t)) for t in tokens]
+        flat = [int(v) for t in tokens for v in (t.tolist() if hasattr(t, "tolist") else t)]
+        N.check(self.lib.ptts_prefill_tokens(self._h, len(slots), _i32(slots), _i32(lens), _i32(flat)))
 
     def step(self, slots, noise: torch.Tensor, *, lsd_steps: int | None = None, decode_audio: bool = True,
              out_device: str = "cpu"):

@@ -330,7 +330,7 @@ class TTSModel:
                 job.slot = work
                 start = eng.offset(work)
                 self._check_capacity(start, job)
-                eng.prefill([work], [self._text_rows(job.tokens)])
+                eng.prefill_tokens([work], [list(job.tokens)])     # embedding gather on the device
                 self._draw_noise(1)              # sample of the prefill call, discarded (tts_model.py:723-725)
                 yield from self._run_single(job)
                 if not copy_state:
@@ -442,7 +442,7 @@ class TTSModel:
                     eng.reset_decoder(job.slot)
                     admitted.append(job)
                 if admitted:
-                    eng.prefill([j.slot for j in admitted], [self._text_rows(j.tokens) for j in admitted])
+                    eng.prefill_tokens([j.slot for j in admitted], [list(j.tokens) for j in admitted])
                     active.extend(admitted)
                 F = max(1, min(block, min(j.max_gen_len - j.done for j in active)))
                 n = len(active)

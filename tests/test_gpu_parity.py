@@ -312,6 +312,33 @@ def test_layernorm_folded_decode_gemms(monkeypatch):
     assert float((outs["1"][1] - outs["0"][1]).abs().max()) <= 5e-2      # EOS logits
 
 
+def test_prefill_from_token_ids_equals_prefill_from_embeddings():
+    """ptts_prefill_tokens gathers the LUT conditioner rows on the device (conditioners/text.py:74-76): the KV
+    cache it leaves must be bit-identical to prefilling with the same rows gathered on the host; bad ids fail."""
+    from pocket_tts_b200 import _native as N
+
+    W = weights(2)
+    emb = W["flow_lm.conditioner.embed.weight"]
+    g = torch.Generator().manual_seed(5)
+    toks = [torch.randint(0, emb.shape[0], (n,), generator=g) for n in (3, 17, 40)]
+    states = []
+    for use_tokens in (True, False):
+        eng = make_engine(2, precision="fp32")
+        slots = [eng.open_stream() for _ in toks]
+        if use_tokens:
+            eng.prefill_tokens(slots, toks)
+        else:
+            eng.prefill(slots, [emb[t] for t in toks])
+        states.append([eng.export_state(s) for s in slots])
+        if use_tokens:
+            with pytest.raises(N.NativeError):
+                eng.prefill_tokens(slots[:1], [[emb.shape[0]]])
+        eng.close()
+    for a, b in zip(*states):
+        for k in a:
+            assert torch.equal(a[k]["offset"], b[k]["offset"]) and torch.equal(a[k]["cache"], b[k]["cache"]), k
+
+
 def test_error_conventions():
     from pocket_tts_b200 import _native as N
     from pocket_tts_b200.engine import GenerationEngine, ModelConfig
