@@ -54,6 +54,7 @@ struct TcParams {
   const bf16* w_base;  // SWAP: weight matrix [N, w_ld] for the L2 prefetch of this CTA's slice (nullptr: none)
   int w_ld;
   KvPrefetchJob pf;    // SWAP: K/V rows of the following decode attention -> L2 (base == nullptr: none)
+  int dry_epilogue;    // SWAP: epilogue warps run one storeless pass of the slab epilogue while the mainloop runs (opt-in probe, PTTS_DRY_EPI=1)
   int slab1;           // SWAP, cluster == 1: still go through the slab epilogue (transpose in this CTA's shared memory,
                        // row-contiguous 16-byte stores) instead of the column epilogue (one 4-byte store per stream row)
   long long* trace;    // debug: per-event SM clock stamps of CTA (0,0,0) (PTTS_TC_TRACE=1)
@@ -257,7 +258,8 @@ __device__ __forceinline__ SlabVecs slab_vecs_load(const GemmEpilogue& ep, const
 
 template <int BN, typename TO>
 __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcParams& P, const float* slab, int S,
-                                               int rank, int row0, int et, const float2* ln_stat, const SlabVecs& sv) {
+                                               int rank, int row0, int et, const float2* ln_stat, const SlabVecs& sv, unsigned tl_s = ~0u,
+                                               bool dry = false) {
   const int F = BM_TC / S, FV = F >> 2;
   const int fv = et % FV, mstep = 256 / FV;
   const int n = row0 + rank * F + fv * 4;
@@ -286,9 +288,9 @@ __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcP
       const float4 r4 = load4(reinterpret_cast<const TO*>(ep.res) + (long long)m * ep.res_map.ld + n);
       v[0] += r4.x; v[1] += r4.y; v[2] += r4.z; v[3] += r4.w;
     }
-    if (ep.out2) store4(reinterpret_cast<TO*>(ep.out2) + (long long)m * ep.out2_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
+    if (ep.out2 && !dry) store4(reinterpret_cast<TO*>(ep.out2) + (long long)m * ep.out2_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
     if (ep.ln_part_out) {   // producer side of a folded LayerNorm: bf16 copy + (sum, M2) over this 16-feature block
-      store4(ep.ln_raw + (long long)m * P.N + n, make_float4(v[0], v[1], v[2], v[3]));
+      if (!dry) store4(ep.ln_raw + (long long)m * P.N + n, make_float4(v[0], v[1], v[2], v[3]));
       float sum = (v[0] + v[1]) + (v[2] + v[3]);
       sum += __shfl_xor_sync(grp_mask, sum, 1);
       sum += __shfl_xor_sync(grp_mask, sum, 2);
@@ -297,10 +299,15 @@ __device__ __forceinline__ void epilogue_slabs(const GemmEpilogue& ep, const TcP
       float m2 = fmaf(d0, d0, fmaf(d1, d1, fmaf(d2, d2, d3 * d3)));
       m2 += __shfl_xor_sync(grp_mask, m2, 1);
       m2 += __shfl_xor_sync(grp_mask, m2, 2);
-      if ((fv & 3) == 0) ep.ln_part_out[(long long)(n >> 4) * P.M + m] = make_float2(sum, m2);   // [block][row]: full-sector runs
+      if ((fv & 3) == 0 && !dry) ep.ln_part_out[(long long)(n >> 4) * P.M + m] = make_float2(sum, m2);   // [block][row]: full-sector runs
     }
     act_inplace<4>(v, ep.act_post);
+    // dry pass (before the accumulator exists): same instructions and the same residual / gate loads on garbage
+    // slab contents, nothing stored - it pulls the epilogue's code into the instruction cache and its operands into
+    // L1 while the mainloop runs (the first real pass cost 1.6 us in every GEMM of the chain, timeline)
+    if (dry) break;
     store4(reinterpret_cast<TO*>(ep.out) + (long long)m * ep.out_map.ld + n, make_float4(v[0], v[1], v[2], v[3]));
+    if (tl_s != ~0u) { tl_mark(tl_s, 5); tl_s = ~0u; }   // timeline: first row pass of the slab epilogue stored
   }
 }
 
@@ -482,7 +489,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     const int q = warp & 3, half = (warp - 2) >> 2;
     if (warp == 2) TC_TRACE(1);
     if (SWAP && ep.ln_part_in) ln_combine(ep, P.M, ln_stat, (int)threadIdx.x - 64);
-    if (clustered) sv = slab_vecs_load(ep, P, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64);
+    if (clustered) {
+      sv = slab_vecs_load(ep, P, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64);
+      if (P.dry_epilogue)
+        epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64, ln_stat, sv, ~0u, true);
+    }
     const bool tl_me = warp == 2 && lane == 0 && blockIdx.x + blockIdx.y + blockIdx.z == 0;
     if (tl_me) tl_mark(tl_slot, 5);                  // epilogue warps ready (LayerNorm statistics combined)
     mbar_wait(&tmem_full_bar, 0);
@@ -509,7 +520,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
     cluster_wait_acquire();                   // ... and so are everybody else's into this CTA
     if (warp == 2 && lane == 0 && blockIdx.x + blockIdx.y + blockIdx.z == 0) tl_mark(tl_slot, 7);   // partial slabs exchanged
     if (warp == 2) TC_TRACE(5);
-    if (warp >= 2) epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64, ln_stat, sv);
+    if (warp >= 2)
+      epilogue_slabs<BN, TO>(ep, P, slab, P.cluster, (int)blockIdx.z, row0, (int)threadIdx.x - 64, ln_stat, sv,
+                             (threadIdx.x == 64 && !ep.ln_part_in && blockIdx.x + blockIdx.y + blockIdx.z == 0) ? tl_slot : ~0u);
     if (warp == 2) TC_TRACE(6);
   }
   __syncthreads();
@@ -806,6 +819,8 @@ cudaError_t gemm_tc_launch(const GemmProblem& p, int out_type, long long a_rows_
     P.w_base = w_prefetch ? reinterpret_cast<const bf16*>(p.W) : nullptr;
     P.w_ld = p.K;
     P.pf = p.kv_prefetch;
+    static const bool dry_epi = [] { const char* e = getenv("PTTS_DRY_EPI"); return e && e[0] == '1'; }();   // measured: no gain (the 1.6 us first pass is not instruction fetch)
+    P.dry_epilogue = dry_epi ? 1 : 0;
     const int tiles = (p.N + BM_TC - 1) / BM_TC;
     // split K over a cluster of S CTAs (S in 1,2,4,8) so that many SMs stream the weight matrix
     int splits = 1;
