@@ -90,6 +90,7 @@ template <typename TK> struct KvVec;
 template <> struct KvVec<bf16> {
   static constexpr int EPL = 8;   // elements per lane
   typedef uint4 Raw;
+  __device__ static Raw load_raw(const bf16* p) { return *reinterpret_cast<const uint4*>(p); }
   __device__ static Raw zero() { return make_uint4(0u, 0u, 0u, 0u); }
   __device__ static void unpack(const Raw& r, float* f) {
     const uint32_t w[4] = {r.x, r.y, r.z, r.w};
@@ -121,6 +122,7 @@ template <> struct KvVec<bf16> {
 template <> struct KvVec<float> {
   static constexpr int EPL = 4;
   typedef float4 Raw;
+  __device__ static Raw load_raw(const float* p) { return *reinterpret_cast<const float4*>(p); }
   __device__ static Raw zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
   __device__ static void unpack(const Raw& r, float* f) { f[0] = r.x; f[1] = r.y; f[2] = r.z; f[3] = r.w; }
   __device__ static void load(const float* p, float* f) {
@@ -130,8 +132,8 @@ template <> struct KvVec<float> {
   __device__ static void store(float* p, const float* f) { *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]); }
 };
 
-template <typename TK, typename TO>
-__global__ void __launch_bounds__(128)   // 72 registers: 7 CTAs per SM (64 registers spills and is slower, measured)
+template <typename TK, typename TO, int U>   // U: 16-byte loads of K and of V in flight per lane (rows stay packed in registers)
+__global__ void __launch_bounds__(128)   // bf16: U = 6 -> 72 registers, 7 CTAs per SM; U = 4 -> 56; U = 8 -> 80
 attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs,
                    const int* __restrict__ offsets, const int* __restrict__ slot_ids, KvGeom g,
                    int layer, TO* __restrict__ out) {
@@ -140,7 +142,6 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   constexpr int EPL = KvVec<TK>::EPL;      // dims per lane
   constexpr int LPR = 64 / EPL;            // lanes per row: 8 / 16
   constexpr int RPL = 32 / LPR;            // rows per warp load: 4 / 2
-  constexpr int U = 4;                     // loads in flight per warp (of K and of V)
   __shared__ float sm_m[NW][32], sm_l[NW][32];
   __shared__ float sm_acc[NW][32][EPL];
   const int h = blockIdx.x, i = blockIdx.y;
@@ -196,24 +197,25 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   for (int e = 0; e < EPL; ++e) acc[e] = 0.0f;
   constexpr int STEP = NW * U * RPL;   // positions per block iteration
   for (int p0 = w * U * RPL; p0 < L; p0 += STEP) {
-    float kf[U][EPL], vf[U][EPL];
+    typename KvVec<TK>::Raw kr[U], vr[U];   // rows stay packed until they are used: U loads of K and of V in flight
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int p = p0 + u * RPL + sub;
       if (p < L) {
-        KvVec<TK>::load(kbase + (long long)p * 64, kf[u]);
-        KvVec<TK>::load(vbase + (long long)p * 64, vf[u]);
+        kr[u] = KvVec<TK>::load_raw(kbase + (long long)p * 64);
+        vr[u] = KvVec<TK>::load_raw(vbase + (long long)p * 64);
       } else {
-#pragma unroll
-        for (int e = 0; e < EPL; ++e) { kf[u][e] = 0.0f; vf[u][e] = 0.0f; }
+        kr[u] = KvVec<TK>::zero(); vr[u] = KvVec<TK>::zero();
       }
     }
     float sc[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
+      float kf[EPL];
+      KvVec<TK>::unpack(kr[u], kf);
       float a = 0.0f;
 #pragma unroll
-      for (int e = 0; e < EPL; ++e) a = fmaf(q[e], kf[u][e], a);
+      for (int e = 0; e < EPL; ++e) a = fmaf(q[e], kf[e], a);
       sc[u] = a;
     }
 #pragma unroll
@@ -236,8 +238,10 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
       for (int u = 0; u < U; ++u) {
         const float pr = expf(sc[u] - mx);
         l += pr;
+        float vf[EPL];
+        KvVec<TK>::unpack(vr[u], vf);
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) acc[e] = fmaf(pr, vf[u][e], acc[e]);
+        for (int e = 0; e < EPL; ++e) acc[e] = fmaf(pr, vf[e], acc[e]);
       }
       m = mx;
     }
@@ -495,14 +499,18 @@ cudaError_t launch_attn_decode(const float* qkv, const float* rope_freqs, const 
     return cudaErrorInvalidValue;
   }
   dim3 grid(kv.H, n);
-  if (kv.type == 0 && out_type == 0)
-    launch_k(attn_decode_kernel<float, float>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out);
-  else if (kv.type == 1 && out_type == 1)
-    launch_k(attn_decode_kernel<bf16, bf16>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
-  else if (kv.type == 0 && out_type == 1)
-    launch_k(attn_decode_kernel<float, bf16>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
-  else
+  static const int u_sel = [] { const char* e = getenv("PTTS_ATTN_U"); return e ? atoi(e) : 6; }();
+#define ATTN_CASE(UV)                                                                                                              \
+  if (kv.type == 0 && out_type == 0)                                                                                               \
+    launch_k(attn_decode_kernel<float, float, UV>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out);  \
+  else if (kv.type == 1 && out_type == 1)                                                                                          \
+    launch_k(attn_decode_kernel<bf16, bf16, UV>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);     \
+  else if (kv.type == 0 && out_type == 1)                                                                                          \
+    launch_k(attn_decode_kernel<float, bf16, UV>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);    \
+  else                                                                                                                             \
     return cudaErrorInvalidValue;
+  if (u_sel == 4) { ATTN_CASE(4) } else if (u_sel == 8) { ATTN_CASE(8) } else { ATTN_CASE(6) }
+#undef ATTN_CASE
   return cudaGetLastError();
 }
 
