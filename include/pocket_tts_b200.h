@@ -148,6 +148,11 @@ int ptts_generate_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_
                          const float* noise_any, int32_t lsd_steps, float* out_pcm_any,
                          float* out_latents_any, float* out_eos_logit_any);
 
+/* PCM egress: fp32 -> 16-bit samples exactly as the reference's WAV writer does on the host
+ * (data/audio.py:77-78: clamp(-1, 1) * 32767, truncated), on the device; n samples; both
+ * pointers may be host or device memory.  Halves the bytes of the device-to-host PCM copy. */
+int ptts_pcm_to_int16(ptts_engine* e, const float* pcm_any, int16_t* out_any, int64_t n);
+
 int ptts_synchronize(ptts_engine* e);
 /* Number of engine kernels launched (or replayed through a graph) since creation. */
 int64_t ptts_launch_count(ptts_engine* e);

@@ -67,6 +67,7 @@ Engine::~Engine() {
   for (auto& kv : graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (void* p : allocs) cudaFree(p);
+  if (egress_buf) cudaFree(egress_buf);
   if (h_pinned) cudaFreeHost(h_pinned);
   if (h_mega_diag) cudaFreeHost(h_mega_diag);
   if (ev_fork) cudaEventDestroy(ev_fork);

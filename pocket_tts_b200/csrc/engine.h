@@ -109,6 +109,7 @@ class Engine {
   int debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out);
   int debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_batch, int valid_rows,
                  const float* a_host, long long a_elems, const float* w_host, float* out_host);
+  int pcm_to_int16(const float* pcm_any, short* out_any, long long n);
   int profile_begin();
   int profile_end(char* json_out, int64_t cap);
 
@@ -231,6 +232,7 @@ class Engine {
 
   std::map<GraphKey, GraphEntry> graphs;
   std::vector<int> cur_slots;
+  void* egress_buf = nullptr; size_t egress_cap = 0;   // staging of ptts_pcm_to_int16 for host pointers
   int prefill_max_len = 0;                   // longest chunk of the current prefill batch (selects the two-pass attention)
   float* h_pinned = nullptr;
   float* lat_ring[2] = {nullptr, nullptr};   // latents [mimi_gmax][S][ldim] handed from the FlowLM branch to the Mimi branch

@@ -200,6 +200,40 @@ int Engine::prefill(int n, const int* slots, const int* lens, const float* embed
   return PTTS_OK;
 }
 
+static bool is_device_ptr(const void* p) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// data/audio.py:77-78 on the device; host pointers are staged through one growing device buffer
+int Engine::pcm_to_int16(const float* pcm_any, short* out_any, long long n) {
+  NEED_READY();
+  if (n < 0 || (n > 0 && (!pcm_any || !out_any))) PTTS_FAIL(PTTS_EINVAL, "pcm_to_int16: bad arguments");
+  if (n == 0) return PTTS_OK;
+  const bool din = is_device_ptr(pcm_any), dout = is_device_ptr(out_any);
+  const size_t need = (din ? 0 : (size_t)n * 4) + (dout ? 0 : (size_t)n * 2 + 16);
+  if (need > egress_cap) {
+    if (egress_buf) cudaFree(egress_buf);
+    egress_buf = nullptr; egress_cap = 0;
+    PTTS_CUDA_CHECK(cudaMalloc(&egress_buf, need));
+    egress_cap = need;
+  }
+  const float* src = pcm_any;
+  char* scratch = reinterpret_cast<char*>(egress_buf);
+  if (!din) {
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(scratch, pcm_any, (size_t)n * 4, cudaMemcpyHostToDevice, stream));
+    src = reinterpret_cast<const float*>(scratch);
+    scratch += ((size_t)n * 4 + 15) / 16 * 16;
+  }
+  short* dst = dout ? out_any : reinterpret_cast<short*>(scratch);
+  PTTS_CUDA_CHECK(launch_pcm_to_int16(src, dst, n, stream));
+  ++launches;
+  if (!dout) PTTS_CUDA_CHECK(cudaMemcpyAsync(out_any, dst, (size_t)n * 2, cudaMemcpyDeviceToHost, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  return PTTS_OK;
+}
+
 // one frame for the streams in d_slot_ids with noise in noise_buf; graph-replayed when enabled
 int Engine::frame(int n, int lsd, int audio) {
   int rc;

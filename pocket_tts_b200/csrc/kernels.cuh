@@ -140,6 +140,9 @@ cudaError_t launch_hist_scatter(const HistTable& t, const int* slot_ids, int typ
 cudaError_t launch_last_conv(const void* buf, int buf_type, const float* w, const float* b,
                              float* pcm, int n, int T, int C, int K, cudaStream_t st);
 
+// data/audio.py:77-78: (clamp(x, -1, 1) * 32767) truncated to int16
+cudaError_t launch_pcm_to_int16(const float* pcm, short* out, long long n, cudaStream_t st);
+
 // fp32 -> bf16 conversion (weights at load time), strided fill helpers
 cudaError_t launch_f32_to_bf16(const float* src, bf16* dst, long long n, cudaStream_t st);
 cudaError_t launch_fill_f32(float* dst, float v, long long n, cudaStream_t st);

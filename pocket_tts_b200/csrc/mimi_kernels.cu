@@ -198,4 +198,15 @@ cudaError_t launch_bf16_to_f32(const bf16* src, float* dst, long long n, cudaStr
   launch_k(bf16_to_f32_kernel, (int)min(4096LL, (n + 255) / 256), 256, 0, st, src, dst, n);
   return cudaGetLastError();
 }
+__global__ void pcm_to_int16_kernel(const float* __restrict__ pcm, short* __restrict__ out, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (short)(fminf(fmaxf(pcm[i], -1.0f), 1.0f) * 32767.0f);   // C cast truncates, as Tensor.short()
+}
+
+cudaError_t launch_pcm_to_int16(const float* pcm, short* out, long long n, cudaStream_t st) {
+  if (n <= 0) return cudaSuccess;
+  pcm_to_int16_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(pcm, out, n);
+  return cudaGetLastError();
+}
+
 }  // namespace ptts

@@ -252,6 +252,14 @@ class GenerationEngine:
                                               _ptr(pcm), _ptr(lat), _ptr(eos)))
         return pcm, lat, eos
 
+    def pcm_to_int16(self, pcm: torch.Tensor) -> torch.Tensor:
+        """16-bit samples as the reference's WAV writer makes them (data/audio.py:77-78), converted on the device;
+        the result lives where the input lives."""
+        pcm = pcm.detach().to(torch.float32).contiguous()
+        out = torch.empty(pcm.shape, dtype=torch.int16, device=pcm.device)
+        N.check(self.lib.ptts_pcm_to_int16(self._h, _ptr(pcm), _ptr(out), pcm.numel()))
+        return out
+
     def synchronize(self) -> None:
         N.check(self.lib.ptts_synchronize(self._h))
 

@@ -115,3 +115,19 @@ def test_api_error_conventions():
             m.generate_audio(state, torch.zeros(400, dtype=torch.long))
     finally:
         m.close()
+
+
+@pytest.mark.gpu
+def test_pcm_to_int16_matches_reference_wav_writer():
+    """data/audio.py:77-78: (chunk.clamp(-1, 1) * 32767).short(), bit-exact, host and device buffers."""
+    import torch
+    from tests.helpers import make_engine
+
+    eng = make_engine(1)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(3, 1920, generator=g) * 0.8
+    x[0, :4] = torch.tensor([1.0, -1.0, 1.5, -2.0])
+    want = (x.clamp(-1, 1) * 32767).short()
+    assert torch.equal(eng.pcm_to_int16(x), want)
+    assert torch.equal(eng.pcm_to_int16(x.cuda()).cpu(), want)
+    eng.close()
