@@ -339,6 +339,31 @@ def test_prefill_from_token_ids_equals_prefill_from_embeddings():
             assert torch.equal(a[k]["offset"], b[k]["offset"]) and torch.equal(a[k]["cache"], b[k]["cache"]), k
 
 
+def test_large_batch_matches_small_batch_bf16():
+    """130 streams take the large-batch forms (three flow-head clusters, separate LayerNorm launches above 128 rows);
+    the first 6 streams must agree with the same streams run as a batch of 6 (folded LayerNorm, one cluster) inside
+    the bf16 gate: the result of a stream does not depend on who shares its batch."""
+    B, b, G = 130, 6, 3
+    g = torch.Generator().manual_seed(21)
+    orc = oracle_for(2)
+    conds = [torch.randn(4 + i % 5, 1024, generator=g) * 0.3 for i in range(B)]
+    noise = torch.randn(G, B, 32, generator=g) * 0.7 ** 0.5
+    outs = []
+    for n in (B, b):
+        eng = make_engine(2, precision="bf16", max_streams=n, max_prefill_rows=1024)
+        slots = [eng.open_stream() for _ in range(n)]
+        eng.prefill(slots, [orc.voice_conditioning(c[None])[0] for c in conds[:n]])
+        lat = []
+        for f in range(G):
+            l, _, _ = eng.step(slots, noise[f, :n], decode_audio=False)
+            lat.append(l[:b])
+        outs.append(torch.stack(lat))
+        eng.close()
+    for i in range(b):
+        assert po.rel_l2(outs[0][0, i], outs[1][0, i]) <= TOL_BF16, i     # first frame: identical inputs
+    assert torch.isfinite(outs[0]).all()
+
+
 def test_error_conventions():
     from pocket_tts_b200 import _native as N
     from pocket_tts_b200.engine import GenerationEngine, ModelConfig
