@@ -179,6 +179,9 @@ int ptts_debug_gemm(ptts_engine* e, int32_t backend, int32_t M, int32_t N, int32
  * JSON object {"<kernel tag>": {"count": n, "total_ms": t}, ...} into json_out. */
 int ptts_profile_begin(ptts_engine* e);
 int ptts_profile_end(ptts_engine* e, char* json_out, int64_t capacity);
+/* Developer: in-graph device timeline (engine created with PTTS_TIMELINE=1 in the environment): the last
+ * max_records kernel records as a JSON array of [name, entry_us, pdl_wait_returned_us, exit_us]. */
+int ptts_debug_timeline(ptts_engine* e, char* json_out, int64_t capacity, int32_t max_records);
 
 #ifdef __cplusplus
 }

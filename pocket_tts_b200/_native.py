@@ -75,6 +75,7 @@ def load_library() -> C.CDLL:
         "ptts_debug_gemm": (C.c_int, [p, i32, i32, i32, i32, i32, i32, i32, f32p, i64, f32p, f32p]),
         "ptts_profile_begin": (C.c_int, [p]),
         "ptts_profile_end": (C.c_int, [p, C.c_char_p, i64]),
+        "ptts_debug_timeline": (C.c_int, [p, C.c_char_p, i64, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

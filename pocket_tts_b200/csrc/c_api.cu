@@ -162,6 +162,12 @@ int ptts_debug_gemm(ptts_engine* e, int32_t backend, int32_t M, int32_t N, int32
   API_END
 }
 int ptts_profile_begin(ptts_engine* e) { API_BEGIN NEED(e) return e->impl->profile_begin(); API_END }
+int ptts_debug_timeline(ptts_engine* e, char* json_out, int64_t capacity, int32_t max_records) {
+  API_BEGIN NEED(e)
+  if (!json_out || capacity < 2) { ptts::set_error("null buffer"); return PTTS_EINVAL; }
+  return e->impl->timeline_json(json_out, capacity, max_records);
+  API_END
+}
 int ptts_profile_end(ptts_engine* e, char* json_out, int64_t capacity) {
   API_BEGIN NEED(e) return e->impl->profile_end(json_out, capacity); API_END
 }

@@ -62,6 +62,32 @@ static void tl_dump(unsigned long long* dev) {
   if (last_attn_exit) fprintf(stderr, "[timeline] latest exit of any decode-attention CTA: %9.2f\n", (double)(last_attn_exit - t0) / 1e3);
 }
 
+// last <= max_records timeline records as a JSON array of [name, entry_us, wait_us, exit_us] (times relative to the first)
+int Engine::timeline_json(char* out, int64_t cap, int max_records) {
+  if (!tl_buf) PTTS_FAIL(PTTS_ESTATE, "timeline not enabled (PTTS_TIMELINE=1 before engine creation)");
+  std::vector<unsigned long long> b(2 + TL_W * TL_MAX);
+  PTTS_CUDA_CHECK(cudaDeviceSynchronize());
+  PTTS_CUDA_CHECK(cudaMemcpy(b.data(), tl_buf, b.size() * 8, cudaMemcpyDeviceToHost));
+  const unsigned long long total = b[0];
+  const unsigned n = (unsigned)std::min<unsigned long long>(std::min<unsigned long long>(total, TL_MAX), (unsigned long long)max_records);
+  std::string js = "[";
+  unsigned long long t0 = 0;
+  for (unsigned k = 0; k < n; ++k) {
+    const unsigned long long* r = &b[2 + TL_W * (unsigned)((total - n + k) % TL_MAX)];
+    if (k == 0) t0 = r[1];
+    char name[64], rec[192];
+    if (r[0] >> 28) snprintf(name, sizeof name, "gemm N=%llu kb=%llu", (r[0] >> 8) & 0xFFFFF, r[0] & 0xFF);
+    else snprintf(name, sizeof name, "%s", r[0] == 2 ? "attn_decode" : r[0] == 3 ? "ln_rows" : r[0] == 4 ? "final_norm_eos" : r[0] == 5 ? "flow_embed" : r[0] == 6 ? "head_cluster" : "?");
+    snprintf(rec, sizeof rec, "%s[\"%s\",%.3f,%.3f,%.3f]", k ? "," : "", name, (double)(r[1] - t0) / 1e3,
+             r[2] ? (double)(r[2] - t0) / 1e3 : -1.0, r[3] ? (double)(r[3] - t0) / 1e3 : -1.0);
+    js += rec;
+  }
+  js += "]";
+  if ((int64_t)js.size() + 1 > cap) PTTS_FAIL(PTTS_EINVAL, "timeline_json: buffer of %lld bytes too small", (long long)cap);
+  memcpy(out, js.c_str(), js.size() + 1);
+  return PTTS_OK;
+}
+
 Engine::~Engine() {
   if (tl_buf) { tl_dump(tl_buf); tl_enable_kernels(nullptr); tl_enable_gemm_tc(nullptr); tl_enable_attention(nullptr); tl_enable_head_tc(nullptr); }
   for (auto& kv : graphs)

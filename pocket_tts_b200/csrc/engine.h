@@ -110,6 +110,7 @@ class Engine {
   int debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_batch, int valid_rows,
                  const float* a_host, long long a_elems, const float* w_host, float* out_host);
   int pcm_to_int16(const float* pcm_any, short* out_any, long long n);
+  int timeline_json(char* out, int64_t cap, int max_records);
   int profile_begin();
   int profile_end(char* json_out, int64_t cap);
 

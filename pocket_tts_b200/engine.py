@@ -293,6 +293,14 @@ class GenerationEngine:
         N.check(self.lib.ptts_profile_end(self._h, buf, len(buf)))
         return json.loads(buf.value.decode())
 
+    def timeline(self, max_records: int = 2048) -> list:
+        """In-graph device timeline (engine created with PTTS_TIMELINE=1): [[name, entry_us, wait_us, exit_us], ...]."""
+        import json
+
+        buf = C.create_string_buffer(1 << 20)
+        N.check(self.lib.ptts_debug_timeline(self._h, buf, len(buf), max_records))
+        return json.loads(buf.value.decode())
+
     def debug_read(self, what: str, numel: int) -> torch.Tensor:
         out = torch.empty(numel, dtype=torch.float32)
         got = C.c_int64(0)
