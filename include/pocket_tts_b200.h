@@ -129,6 +129,13 @@ int ptts_step(ptts_engine* e, int32_t n, const int32_t* slots, const float* nois
 int ptts_mimi_decode(ptts_engine* e, int32_t n, const int32_t* slots, const float* latents_any,
                      float* out_pcm_any);
 
+/* The decoder thread's loop over a queue of latents (tts_model.py:434-474) for n streams at once: n_frames consecutive
+ * latents per stream, latents_any [n_frames, n, ldim] -> out_pcm_any [n, n_frames*1920], decoded in passes of up to 4
+ * frames x 16 tokens per stream (the pass form of ptts_generate_frames; arithmetically the same as n_frames calls of
+ * ptts_mimi_decode).  BASELINE config 4 (Mimi decoder-only sweep) runs through this call. */
+int ptts_mimi_decode_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames,
+                            const float* latents_any, float* out_pcm_any);
+
 /* Device-resident multi-frame loop for throughput runs: n_frames frames back to back with
  * noise [n_frames, n, ldim] already on the device, PCM written to a device buffer
  * [n, n_frames*1920] (or NULL), no host round trip in between (CUDA-graph replay). */
@@ -139,9 +146,10 @@ int ptts_run_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_f
 /* Streaming generation of n_frames frames for n streams with caller buffers that may live on the
  * host (pinned memory makes the copies asynchronous) or on the device: the body of
  * TTSModel._autoregressive_generation + the decoder thread (tts_model.py:651-658,745-779) as one
- * call.  Per frame: noise_any[f] is copied in, the FlowLM step + flow head of frame f run
- * concurrently with the Mimi decode of frame f-1 (two branches of one CUDA graph), and
- * latents / EOS logits of frame f and the PCM of frame f-1 are copied out.  Layouts:
+ * call.  Frames are issued in groups of 1, 1, 2, 4, 4, ...: each frame's FlowLM step + flow head is one
+ * CUDA graph on the high-priority stream, the Mimi pass over a group's latents is one graph on a second
+ * stream that runs beside the next group's FlowLM frames, and noise / latents / EOS logits / PCM copies
+ * ride a third stream ordered by events.  Layouts:
  * noise [n_frames, n, ldim], out_pcm [n, n_frames*1920], out_latents [n_frames, n, ldim],
  * out_eos_logit [n_frames, n]; outputs may be NULL.  Returns after everything has landed. */
 int ptts_generate_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames,

@@ -64,6 +64,7 @@ def load_library() -> C.CDLL:
         "ptts_prefill_tokens": (C.c_int, [p, i32, i32p, i32p, i32p]),
         "ptts_step": (C.c_int, [p, i32, i32p, f32p, i32, i32, f32p, f32p, f32p]),
         "ptts_mimi_decode": (C.c_int, [p, i32, i32p, f32p, f32p]),
+        "ptts_mimi_decode_frames": (C.c_int, [p, i32, i32p, i32, f32p, f32p]),
         "ptts_run_frames": (C.c_int, [p, i32, i32p, i32, f32p, i32, f32p, f32p]),
         "ptts_generate_frames": (C.c_int, [p, i32, i32p, i32, f32p, i32, f32p, f32p, f32p]),
         "ptts_pcm_to_int16": (C.c_int, [p, f32p, p, i64]),

@@ -469,11 +469,10 @@ static cudaError_t launch_attn_decode_bulk_w(const float* qkv, const float* rope
   const int tasks = n * kv.H;
   const size_t smem = (size_t)W * AD_SLOTS * 2 * AD_CHUNK;
   auto kern = attn_decode_bulk_kernel<TK, TO, W>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_done;
+  if (attr_done.first()) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_done = true;
   }
   launch_k(kern, dim3((tasks + W - 1) / W), dim3(W * 32), smem, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, out, tasks);
   return cudaGetLastError();
@@ -772,12 +771,11 @@ cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const 
   const bool use_mma = !env_mma || atoi(env_mma) != 0;
   const int NQ = frames * T;
   if (use_mma && kv.type == 1 && out_type == 1 && T == 16 && NQ <= 64 && context - 1 + NQ <= WM_MAXW) {
-    static bool attr = false;
-    if (!attr) {
+    static DeviceOnce attr;
+    if (attr.first()) {
       cudaError_t e = cudaFuncSetAttribute(attn_window_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)attn_window_mma_smem());
       if (e != cudaSuccess) return e;
-      attr = true;
     }
     launch_k(attn_window_mma_kernel, dim3(kv.H, n), WM_THREADS, attn_window_mma_smem(), st, qkv, rope_freqs, offsets,
              slot_ids, kv, layer, context, NQ, (bf16*)out);
@@ -788,11 +786,11 @@ cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const 
   const size_t smem = ((size_t)2 * maxw * ld + (size_t)16 * maxw + 16 * 64) * 4;
 #define WIN_CASE(TKT, TOT)                                                                                        \
   do {                                                                                                            \
-    static bool attr = false;                                                                                     \
-    if (!attr) {                                                                                                  \
+    static DeviceOnce attr;                                                                                     \
+    if (attr.first()) {                                                                                                  \
       cudaError_t e = cudaFuncSetAttribute(attn_window_kernel<TKT, TOT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
       if (e != cudaSuccess) return e;                                                                             \
-      attr = true;                                                                                                \
+                                                                                                                        \
     }                                                                                                             \
     launch_k(attn_window_kernel<TKT, TOT>, grid, 256, smem, st, qkv, rope_freqs, offsets, slot_ids, kv, layer,    \
              context, T, maxw, (TOT*)out);                                                                        \

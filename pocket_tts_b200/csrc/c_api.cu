@@ -24,11 +24,22 @@ struct ptts_engine {
     ptts::set_error("unknown exception");                    \
     return PTTS_EINVAL;                                      \
   }
+// Every entry point runs with the engine's CUDA device current and restores the caller's device on the way out
+// (an engine on device 1 called from a fresh thread, or after torch switched devices, must not land on device 0).
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; cudaGetLastError(); }
+    if (prev != dev) cudaSetDevice(dev); else prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
 #define NEED(e)                                 \
   if (!(e) || !(e)->impl) {                     \
     ptts::set_error("null engine handle");      \
     return PTTS_EINVAL;                         \
-  }
+  }                                             \
+  DeviceGuard _device_guard((e)->impl->cfg.device);
 
 extern "C" {
 
@@ -39,6 +50,7 @@ int ptts_engine_create(const ptts_config* cfg, ptts_engine** out) {
   API_BEGIN
   if (!cfg || !out) { ptts::set_error("null argument"); return PTTS_EINVAL; }
   *out = nullptr;
+  DeviceGuard guard(cfg->device);
   Engine* e = new Engine(*cfg);
   const int rc = e->init();
   if (rc != PTTS_OK) { delete e; return rc; }
@@ -50,7 +62,10 @@ int ptts_engine_create(const ptts_config* cfg, ptts_engine** out) {
 int ptts_engine_destroy(ptts_engine* e) {
   API_BEGIN
   if (!e) return PTTS_OK;
-  delete e->impl;
+  {
+    DeviceGuard guard(e->impl ? e->impl->cfg.device : 0);
+    delete e->impl;
+  }
   delete e;
   return PTTS_OK;
   API_END
@@ -120,6 +135,10 @@ int ptts_step(ptts_engine* e, int32_t n, const int32_t* slots, const float* nois
 }
 int ptts_mimi_decode(ptts_engine* e, int32_t n, const int32_t* slots, const float* latents_any, float* out_pcm_any) {
   API_BEGIN NEED(e) return e->impl->mimi_decode(n, slots, latents_any, out_pcm_any); API_END
+}
+int ptts_mimi_decode_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames, const float* latents_any,
+                            float* out_pcm_any) {
+  API_BEGIN NEED(e) return e->impl->mimi_decode_frames(n, slots, n_frames, latents_any, out_pcm_any); API_END
 }
 int ptts_run_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames, const float* noise_dev,
                     int32_t lsd_steps, float* out_pcm_dev, float* out_latents_dev) {

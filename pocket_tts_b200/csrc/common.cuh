@@ -132,6 +132,19 @@ struct RowMap {
 // stream serialization attribute (PTTS_PDL=0 disables) so that its prologue overlaps the tail of
 // the previous kernel; kernels call pdl_wait() before their first dependent access.
 bool pdl_enabled();
+
+// Per-process caches of per-device settings (cudaFuncSetAttribute opt-ins): first() is true once per CUDA device.
+struct DeviceOnce {
+  unsigned long long mask = 0;
+  bool first() {
+    int d = 0;
+    cudaGetDevice(&d);
+    const unsigned long long bit = 1ull << (d & 63);
+    if (mask & bit) return false;
+    mask |= bit;
+    return true;
+  }
+};
 // Every kernel asks for the same (maximum) shared-memory carveout: alternating carveouts between
 // consecutive kernels makes the SMs drain and repartition L1/shared memory at every boundary.
 void prefer_max_smem_carveout(const void* kern);

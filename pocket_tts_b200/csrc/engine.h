@@ -104,6 +104,7 @@ class Engine {
   int step(int n, const int* slots, const float* noise_any, int lsd, int audio, float* out_lat,
            float* out_eos, float* out_pcm);
   int mimi_decode(int n, const int* slots, const float* latents_any, float* out_pcm);
+  int mimi_decode_frames(int n, const int* slots, int n_frames, const float* latents_any, float* out_pcm_any);
   int run_frames(int n, const int* slots, int n_frames, const float* noise_any, int lsd,
                  float* out_pcm_any, float* out_lat_any, float* out_eos_any = nullptr, bool sync = false);
   int debug_read(const char* what, float* out_any, int64_t max_elems, int64_t* n_out);

@@ -406,6 +406,31 @@ int Engine::mimi_decode(int n, const int* slots, const float* latents_any, float
   return PTTS_OK;
 }
 
+// Mimi decode of n_frames consecutive latents per stream (latents [n_frames][n][ldim] -> PCM [n][n_frames*1920]) in
+// passes of up to mimi_gmax frames, the pass form the pipelined loop uses (BASELINE config 4: decoder-only sweep).
+int Engine::mimi_decode_frames(int n, const int* slots, int n_frames, const float* latents_any, float* out_pcm_any) {
+  NEED_READY();
+  int rc;
+  if ((rc = check_slots(n, slots, false)) != PTTS_OK) return rc;
+  if (!latents_any || n_frames < 1) PTTS_FAIL(PTTS_EINVAL, "mimi_decode_frames: bad arguments");
+  if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
+  const size_t fl = (size_t)n * cfg.ldim;
+  const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
+  for (int f0 = 0; f0 < n_frames;) {
+    const int g = std::min(mimi_gmax, n_frames - f0);
+    PTTS_CUDA_CHECK(cudaMemcpyAsync(lat_ring[0], latents_any + (size_t)f0 * fl, g * fl * sizeof(float), cudaMemcpyDefault, stream));
+    rc = launch_captured(GraphKey{n, 0, 1, 4000 + g}, stream, [&]() -> int { return mimi_sequence(n, lat_ring[0], g, pcm_ring[0]); });
+    if (rc != PTTS_OK) return rc;
+    if (out_pcm_any)
+      PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_any + (size_t)f0 * fs, (size_t)n_frames * fs * sizeof(float), pcm_ring[0],
+                                        g * fs * sizeof(float), g * fs * sizeof(float), n, cudaMemcpyDefault, stream));
+    f0 += g;
+  }
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
+  for (int i = 0; i < n; ++i) host_mimi_offsets[slots[i]] += n_frames * cfg.upsample_stride;
+  return PTTS_OK;
+}
+
 // The frame loop (tts_model.py:745-779 + the decoder thread :434-474) for n streams and n_frames frames.
 // Pipelined form: group k of the schedule 1, 1, 2, 4, ... (<= mimi_gmax frames) runs its FlowLM frames while the
 // Mimi pass decodes group k-1; the result copies of a group ride `copy_stream` beside the next group's graph.

@@ -350,12 +350,11 @@ bool flow_head_cluster_supported(int flow_dim, int ldim, int depth) {
 }
 
 cudaError_t launch_flow_head_cluster(const FlowHeadParams& p, cudaStream_t st) {
-  static bool attr_done = false;
+  static DeviceOnce attr_done;
   const size_t smem = sizeof(HeadSmem);
-  if (!attr_done) {
+  if (attr_done.first()) {
     cudaError_t e = cudaFuncSetAttribute(flow_head_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(HC_CL * ((p.n + HC_ROWS - 1) / HC_ROWS), 1, 1);

@@ -431,11 +431,10 @@ bool flow_head_tc_prepare(FlowHeadTcParams* p) {
 }
 
 cudaError_t launch_flow_head_tc(const FlowHeadTcParams& p, cudaStream_t st) {
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_done;
+  if (attr_done.first()) {
     cudaError_t e = cudaFuncSetAttribute(flow_head_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HT_SMEM);
     if (e != cudaSuccess) return e;
-    attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(HT_CL * ((p.h.n + HT_ROWS - 1) / HT_ROWS), 1, 1);

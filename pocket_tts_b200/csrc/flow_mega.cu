@@ -830,7 +830,10 @@ size_t flow_mega_smem_bytes(int stages, int a_bytes) {
 cudaError_t flow_mega_launch(const MegaParams& P, cudaStream_t st) {
   if (P.stages < 2 || P.stages > MEGA_MAX_STAGES || P.n_phases > MEGA_MAX_PHASES) return cudaErrorInvalidValue;
   const size_t smem = flow_mega_smem_bytes(P.stages, P.a_bytes);
-  static size_t attr_smem = 0;
+  static size_t attr_smem_dev[64] = {};
+  int cur_dev = 0;
+  cudaGetDevice(&cur_dev);
+  size_t& attr_smem = attr_smem_dev[cur_dev & 63];
   if (smem > attr_smem) {   // static shared memory (barriers) counts against the 227 KB limit too
     cudaError_t e = cudaFuncSetAttribute(flow_mega_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

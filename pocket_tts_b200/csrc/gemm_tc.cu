@@ -706,13 +706,12 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
   size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + (clustered ? (size_t)BN * BM_TC * sizeof(float) : 0);
   if (!SWAP) smem = std::max(smem, EPI_SMEM_BYTES);   // the epilogue staging reuses the (drained) pipeline buffers
   smem += 1024;
-  static bool attr_done = false;
+  static DeviceOnce attr_done;
   auto kern = gemm_tc_kernel<BN, SWAP, TO>;
-  if (!attr_done) {
+  if (attr_done.first()) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_LIMIT + 1024);
     if (e != cudaSuccess) return e;
     prefer_max_smem_carveout(reinterpret_cast<const void*>(kern));
-    attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = grid;
@@ -765,12 +764,11 @@ template <int BN, typename TO>
 static cudaError_t launch_rows(const CUtensorMap& ta, const CUtensorMap& tw, const TcRowsParams& P, const GemmEpilogue& ep,
                                int grid, bool pdl, cudaStream_t st) {
   const size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + EPI_SMEM_BYTES + 1024;
-  static bool attr_done = false;
+  static DeviceOnce attr_done;
   auto kern = gemm_tc_rows_kernel<BN, TO>;
-  if (!attr_done) {
+  if (attr_done.first()) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_LIMIT + 1024);
     if (e != cudaSuccess) return e;
-    attr_done = true;
   }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid, 1, 1);

@@ -219,6 +219,16 @@ class GenerationEngine:
         N.check(self.lib.ptts_mimi_decode(self._h, n, _i32(slots), _ptr(latents), _ptr(pcm)))
         return pcm
 
+    def mimi_decode_frames(self, slots, latents: torch.Tensor) -> torch.Tensor:
+        """latents [F, n, ldim] (host or device) -> PCM [n, F*1920] where the latents live, decoded in grouped
+        passes of up to 4 frames per stream."""
+        F, n, _ = latents.shape
+        assert n == len(slots)
+        latents = latents.detach().to(torch.float32).contiguous()
+        pcm = torch.empty(n, F * self.cfg.frame_samples, dtype=torch.float32, device=latents.device)
+        N.check(self.lib.ptts_mimi_decode_frames(self._h, n, _i32(slots), F, _ptr(latents), _ptr(pcm)))
+        return pcm
+
     def run_frames(self, slots, noise_dev: torch.Tensor, *, lsd_steps: int | None = None,
                    out_pcm: torch.Tensor | None = None, out_latents: torch.Tensor | None = None) -> None:
         """Device-resident loop: noise_dev [F, n, ldim] on the GPU; asynchronous."""

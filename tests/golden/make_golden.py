@@ -10,6 +10,7 @@ are what travels.
     python tests/golden/make_golden.py            # regenerates every fixture
 """
 
+import hashlib
 import sys
 from functools import partial
 from pathlib import Path
@@ -107,7 +108,10 @@ def run_reference_mimi(m, latents):
     return torch.cat(out)
 
 
-def case_generate(name, preset, n_layers, streams, G, lsd_steps, seed, keep_kv_layers=()):
+def case_generate(name, preset, n_layers, streams, G, lsd_steps, seed, keep_kv_layers=(), pcm_f16_after=None, cond_from_seed=False):
+    """pcm_f16_after: keep the long fixtures small — PCM is stored in full for the first N frames only; later
+    frames are stored as per-frame checksums (sum, sum of squares) plus a float16 copy used for an SNR gate
+    (float16 rounding is ~ 66 dB below the signal, far above the 40 dB gate)."""
     dims = po.ModelDims(n_layers=n_layers)
     W = po.make_weights(dims, seed=0)
     ref = build_reference(preset, n_layers, W, lsd_steps)
@@ -121,12 +125,25 @@ def case_generate(name, preset, n_layers, streams, G, lsd_steps, seed, keep_kv_l
         full_cond = torch.cat([ref.flow_lm.bos_before_voice, cond], dim=1)
         lat, logit, pcm, vkv = run_reference_stream(ref, full_cond, tokens, noise,
                                                     keep_kv_layers if si == 0 else ())
-        out[f"cond_{si}"] = cond[0].numpy()
+        if cond_from_seed:
+            # long voice prefixes are not stored: the loader redraws them from (seed, P) — the first draw of the
+            # generator — and checks the digest (tests/helpers.py::load_case)
+            assert si == 0
+            out["cond_seed"] = seed
+            out["cond_P"] = P
+            out["cond_sha256"] = hashlib.sha256(cond[0].numpy().tobytes()).hexdigest()
+        else:
+            out[f"cond_{si}"] = cond[0].numpy()
         out[f"tokens_{si}"] = tokens[0].numpy()
         out[f"noise_{si}"] = noise[:, 0].numpy()
         out[f"latents_{si}"] = lat.numpy()
         out[f"eos_logits_{si}"] = logit.numpy()
-        out[f"pcm_{si}"] = pcm.numpy()
+        if pcm_f16_after is None:
+            out[f"pcm_{si}"] = pcm.numpy()
+        else:
+            n_full = pcm_f16_after * 1920
+            out[f"pcm_{si}"] = pcm[:n_full].numpy()
+            out[f"pcm_tail_f16_{si}"] = pcm[n_full:].numpy().astype(np.float16)
         out.update(vkv)
         print(name, "stream", si, "P", P, "T", T, "pcm rms", float(pcm.pow(2).mean().sqrt()),
               "lat rms", float(lat.pow(2).mean().sqrt()))
@@ -145,7 +162,29 @@ def case_mimi(name, G, seed):
                         pcm=pcm.numpy(), G=G, torch_version=str(torch.__version__), weights_seed=0)
 
 
+def make_long_cases():
+    """Round-2 fixtures at the shapes bench.py runs (VERDICT r01 'parity gaps'):
+    * gen_english_6l_long: voice P = 125 (+ bos = 126), T = 40, G = 52 frames -> FlowLM context 166..218 (three
+      96-position block iterations of the bf16 decode kernel), Mimi 832 tokens = the 512-position KV ring wraps and
+      the 250-token window slides across the wrap, with 4-frame grouped passes over it;
+    * gen_english_6l_ctx640: P = 589 (+ bos = 590), T = 50, 4 frames -> context 640..644 (seven block iterations,
+      the kv_capacity edge of a 30 s voice prompt plus text);
+    * gen_italian_24l_long: 24 layers at context 166+.
+    """
+    case_generate("gen_english_6l_long", "english", 6, [(125, 40)], G=52, lsd_steps=1, seed=21, pcm_f16_after=8,
+                  cond_from_seed=True)
+    # a 30 s voice prompt is 375 frames; two 50-token chunks of text in front of the frames reach context ~ 640
+    case_generate("gen_english_6l_ctx640", "english", 6, [(589, 50)], G=4, lsd_steps=1, seed=22,
+                  cond_from_seed=True)
+    case_generate("gen_italian_24l_long", "italian_24l", 24, [(125, 40)], G=4, lsd_steps=1, seed=23,
+                  cond_from_seed=True)
+
+
 if __name__ == "__main__":
+    if "--long-only" in sys.argv:
+        torch.set_num_threads(8)
+        make_long_cases()
+        sys.exit(0)
     torch.set_num_threads(8)
     # (voice length P without the bos row, text tokens T)
     case_generate("gen_2l", "english", 2, [(20, 12), (33, 9), (7, 5)], G=6, lsd_steps=1, seed=11,
@@ -154,3 +193,4 @@ if __name__ == "__main__":
     case_generate("gen_english_6l", "english", 6, [(40, 16), (25, 10)], G=6, lsd_steps=1, seed=13)
     case_generate("gen_italian_24l", "italian_24l", 24, [(18, 8)], G=3, lsd_steps=1, seed=14)
     case_mimi("mimi_20f", G=20, seed=15)
+    make_long_cases()

@@ -32,8 +32,21 @@ def load_case(name: str):
     g = np.load(GOLD / f"{name}.npz")
     ns = int(g["n_streams"])
     case = dict(n_layers=int(g["n_layers"]), lsd=int(g["lsd_steps"]), G=int(g["G"]), ns=ns)
-    for k in ("cond", "tokens", "noise", "latents", "eos_logits", "pcm"):
+    for k in ("tokens", "noise", "latents", "eos_logits", "pcm"):
         case[k] = [torch.from_numpy(g[f"{k}_{i}"]) for i in range(ns)]
+    if "cond_seed" in g:   # long voice prefix redrawn from its seed (make_golden.py: first draw of the generator)
+        import hashlib
+
+        gen = torch.Generator().manual_seed(int(g["cond_seed"]))
+        cond = torch.randn(1, int(g["cond_P"]), 1024, generator=gen) * 0.3
+        digest = hashlib.sha256(cond[0].numpy().tobytes()).hexdigest()
+        assert digest == str(g["cond_sha256"]), "voice conditioning redrawn from the seed differs from the fixture's"
+        case["cond"] = [cond[0]]
+    else:
+        case["cond"] = [torch.from_numpy(g[f"cond_{i}"]) for i in range(ns)]
+    # long fixtures: PCM after the first frames is stored as float16 (SNR gate only)
+    case["pcm_tail"] = [torch.from_numpy(g[f"pcm_tail_f16_{i}"].astype(np.float32)) if f"pcm_tail_f16_{i}" in g else None
+                        for i in range(ns)]
     case["raw"] = g
     return case
 
