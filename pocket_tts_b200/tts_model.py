@@ -332,7 +332,7 @@ class TTSModel:
                 self._check_capacity(start, job)
                 eng.prefill_tokens([work], [list(job.tokens)])     # embedding gather on the device
                 self._draw_noise(1)              # sample of the prefill call, discarded (tts_model.py:723-725)
-                yield from self._run_single(job)
+                yield from self._run_single(job, keep_state=not copy_state)
                 if not copy_state:
                     steps = job.done if job.limit is None or job.limit >= job.max_gen_len else job.limit + 1
                     self._set_offset(work, start + len(job.tokens) + min(steps, job.max_gen_len))
@@ -369,7 +369,7 @@ class TTSModel:
                 job.eos_step = first_frame + int(hit[0])
                 job.limit = min(job.max_gen_len, job.eos_step + job.frames_after_eos)
 
-    def _run_single(self, job: _Job) -> Iterator[torch.Tensor]:
+    def _run_single(self, job: _Job, keep_state: bool = False) -> Iterator[torch.Tensor]:
         eng, fs = self.engine, self.cfg.frame_samples
         block_i = 0
         while job.done < job.target():
@@ -390,7 +390,12 @@ class TTSModel:
                 # the reference ran frame `limit` (one more draw) and then broke out of its loop
                 torch.set_rng_state(rng[job.limit - job.done])
             elif job.limit is not None and job.limit < job.max_gen_len and job.limit == job.done + F:
-                self._draw_noise(1)
+                # the block ended exactly at the limit: the reference still runs FlowLM for frame `limit` (one more
+                # draw, K/V of that position appended, tts_model.py:756-765) before it breaks.  With
+                # copy_state=False that position is part of the state handed back, so it is really computed.
+                extra = self._draw_noise(1)
+                if keep_state:
+                    eng.step([job.slot], extra, lsd_steps=self.lsd_decode_steps, decode_audio=False)
             job.done += F
         if job.limit is None or job.limit >= job.max_gen_len:
             logger.warning("Maximum generation length reached without EOS, this very often indicates an error.")
@@ -422,6 +427,7 @@ class TTSModel:
             waiting.extend(jobs)
         voices: dict = {}
         active: list = []
+        admitted: list = []
         try:
             for st in model_states:          # one resident slot per distinct voice state
                 if id(st) not in voices:
@@ -432,18 +438,18 @@ class TTSModel:
             if capacity < 1:
                 raise ValueError("no stream slot left for generation: raise max_streams")
             while waiting or active:
-                admitted = []
                 while waiting and len(active) + len(admitted) < capacity:
-                    job = waiting.pop(0)
-                    job.slot = eng.open_stream()
+                    job = waiting[0]
                     src = voices[id(model_states[job.request])]
                     self._check_capacity(eng.offset(src), job)
+                    job.slot = eng.open_stream()
+                    admitted.append(waiting.pop(0))      # from here on `finally` closes the slot
                     eng.fork(src, job.slot)
                     eng.reset_decoder(job.slot)
-                    admitted.append(job)
                 if admitted:
                     eng.prefill_tokens([j.slot for j in admitted], [list(j.tokens) for j in admitted])
                     active.extend(admitted)
+                    admitted = []
                 F = max(1, min(block, min(j.max_gen_len - j.done for j in active)))
                 n = len(active)
                 nz = torch.empty(F, n, self.cfg.ldim)
@@ -465,7 +471,7 @@ class TTSModel:
                         still.append(j)
                 active = still
         finally:
-            for j in active:
+            for j in active + admitted:
                 if j.slot >= 0:
                     eng.close_stream(j.slot)
             for v in voices.values():

@@ -62,16 +62,34 @@ def voice_state(ref, cond):
     return st
 
 
-def run(ref, cond, thr, frames_after_eos):
+def run(ref, cond, thr, frames_after_eos, text=TEXT, copy_state=True):
     ref.eos_threshold = thr
     logits = []
     h = ref.flow_lm.out_eos.register_forward_hook(lambda m, i, o: logits.append(float(o.view(-1)[0])))
     torch.manual_seed(SEED)
     st = voice_state(ref, cond)
-    chunks = [c.clone() for c in ref.generate_audio_stream(st, TEXT, max_tokens=MAX_TOKENS,
-                                                           frames_after_eos=frames_after_eos)]
+    chunks = [c.clone() for c in ref.generate_audio_stream(st, text, max_tokens=MAX_TOKENS,
+                                                           frames_after_eos=frames_after_eos, copy_state=copy_state)]
     h.remove()
     return torch.cat(chunks), logits, st
+
+
+def in_place_fixture(ref, cond):
+    """copy_state=False with the EOS limit exactly at an engine block boundary (blocks of 1, 1, 2, 4 frames: EOS
+    fires at frame 0, frames_after_eos = 4 -> 4 frames emitted, the reference still runs FlowLM for frame 4 and
+    appends its K/V before breaking, tts_model.py:756-765): the state handed back holds voice + text + 5 positions."""
+    text, fae = "hi there.", 4
+    audio, logits, st = run(ref, cond, -1e9, fae, text=text, copy_state=False)
+    off = int(st["transformer.layers.0.self_attn"]["offset"].view(-1)[0])
+    tail = np.stack([st[f"transformer.layers.{i}.self_attn"]["cache"][:, 0, off - 3:off].numpy() for i in range(2)])
+    after = np.stack([st[f"transformer.layers.{i}.self_attn"]["cache"][:, 0, off:off + 1].numpy() for i in range(2)]) \
+        if st["transformer.layers.0.self_attn"]["cache"].shape[2] > off else np.zeros(0)
+    print("in-place fixture: frames", audio.numel() // 1920, "offset", off, "flow calls", len(logits),
+          "cache len", st["transformer.layers.0.self_attn"]["cache"].shape[2])
+    np.savez_compressed(Path(__file__).parent / "api_inplace_2l.npz", cond=cond[0].numpy(), text=np.array(text),
+                        frames_after_eos=fae, eos_threshold=-1e9, seed=SEED, audio=audio.numpy(), offset=off,
+                        cache_tail=tail, next_draw=torch.randn(4).numpy(), torch_version=str(torch.__version__),
+                        weights_seed=0)
 
 
 TEXTS = [
@@ -114,6 +132,9 @@ if __name__ == "__main__":
     ref = build_reference("english", 2, W, 1)
     g = torch.Generator().manual_seed(77)
     cond = torch.randn(1, P, dims.d_model, generator=g) * 0.3
+    if "--inplace-only" in sys.argv:
+        in_place_fixture(ref, cond)
+        sys.exit(0)
     # probe: EOS never fires; logits[0] is the voice prefill, then per chunk: text prefill + frames
     _, logits, _ = run(ref, cond, 1e9, 2)
     first = np.array(logits[2:2 + 14])        # frames 0..13 of the first chunk
@@ -128,3 +149,4 @@ if __name__ == "__main__":
                         max_tokens=MAX_TOKENS, frames_after_eos=2, eos_threshold=thr, seed=SEED,
                         audio=audio.numpy(), n_flow_calls=len(logits2), next_draw=torch.randn(4).numpy(),
                         torch_version=str(torch.__version__), weights_seed=0)
+    in_place_fixture(ref, cond)

@@ -59,6 +59,32 @@ def test_stream_chunks_and_in_place_state():
         m.close()
 
 
+def test_in_place_state_with_eos_at_block_boundary_matches_reference():
+    """copy_state=False when the EOS limit falls exactly on an engine block boundary (blocks of 1, 1, 2 frames, limit
+    4): the reference runs FlowLM once more for frame 4 before breaking (tts_model.py:756-765), so the state handed
+    back has voice + text + 5 positions, all of them written.  Fixture recorded from the reference itself."""
+    g = np.load(GOLD / "api_inplace_2l.npz")
+    m = make_model(eos_threshold=float(g["eos_threshold"]))
+    try:
+        torch.manual_seed(int(g["seed"]))
+        state = m.get_state_for_audio_prompt(torch.from_numpy(g["cond"]))
+        audio = m.generate_audio(state, str(g["text"]), frames_after_eos=int(g["frames_after_eos"]), copy_state=False)
+        nxt = torch.randn(4)
+    finally:
+        m.close()
+    ref = torch.from_numpy(g["audio"])
+    off = int(g["offset"])
+    assert audio.shape == ref.shape and po.snr_db(ref, audio) >= 40.0
+    assert torch.equal(nxt, torch.from_numpy(g["next_draw"]))
+    tail = torch.from_numpy(g["cache_tail"])                          # [layer, 2, 3, 16, 64]: the last three positions
+    for i in range(2):
+        st = state[f"transformer.layers.{i}.self_attn"]
+        assert int(st["offset"].view(-1)[0]) == off
+        got = st["cache"][:, 0, off - 3:off]
+        assert po.rel_l2(got, tail[i]) <= 1e-4, (i, po.rel_l2(got, tail[i]))
+        assert po.rel_l2(got[:, -1], tail[i][:, -1]) <= 1e-4         # the position of the extra FlowLM call
+
+
 def test_generate_audio_batch_ragged_vs_oracle():
     dims = po.ModelDims(n_layers=2)
     orc = oracle_for(2)
