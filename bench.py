@@ -88,11 +88,12 @@ def synth_inputs(dims, B, G, seed_base=0):
     return tokens, voice, noise
 
 
-def algorithmic_bytes_per_step(dims, B, ctx_len, e):
-    """weights once + FlowLM KV read + Mimi KV window + conv state + I/O."""
+def algorithmic_bytes_per_step(dims, B, ctx_len, e, mimi_tokens):
+    """weights once + FlowLM KV read + Mimi KV window + conv state + I/O.  `mimi_tokens` is the
+    Mimi decoder's own offset (16 tokens per generated frame), not the FlowLM context."""
     w_elems = 95_582_018 if dims.n_layers == 6 else 322_074_434
     kv_flow = B * dims.n_layers * 2 * dims.d_model * e * (ctx_len + 1)
-    kv_mimi = B * dims.mimi_layers * 2 * dims.mimi_d * e * (min(ctx_len * 16, 265) + 16)
+    kv_mimi = B * dims.mimi_layers * 2 * dims.mimi_d * e * (min(mimi_tokens, 265) + 16)
     state = B * 2 * 14_720 * e
     io = B * (dims.ldim * 4 + dims.frame_samples * 4)
     return w_elems * e + kv_flow + kv_mimi + state + io
@@ -129,8 +130,7 @@ def run_ours(args, rank, world, local_rank):
     dist = world > 1
     if dist:
         import torch.distributed as td
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # NCCL's version banner / debug lines must not land on stdout
-        td.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        td.init_process_group("gloo")   # control plane only (barrier + two scalar reductions): no NCCL on any path
 
     def barrier():
         if dist:
@@ -287,10 +287,9 @@ def run_ours(args, rank, world, local_rank):
         peaks = json.loads(pk.read_text())
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     total_prof = sum(v["total_ms"] for v in prof.values()) or 1.0
-    # dominant kernel: FlowLM decode attention — largest algorithmic byte term of the step (KV stream)
-    # and the largest per-tag time in the event profile; fall back to the top tag by time
-    top = ("flow.attn_decode", prof["flow.attn_decode"]) if "flow.attn_decode" in prof else \
-        (max(prof.items(), key=lambda kv: kv[1]["total_ms"]) if prof else (None, None))
+    # dominant kernel = the tag with the largest summed event time among those with a byte model (kernel_ms_share)
+    ranked = sorted(prof.items(), key=lambda kv: -kv[1]["total_ms"])
+    top = next(((k, v) for k, v in ranked if kernel_algorithmic_bytes(k, dims, B, 200, e_bytes) > 0), (None, None))
     roofline = None
     if top[0]:
         ctx_mid = VOICE_P + TEXT_T + Wm + min(K, 32) // 2
@@ -298,14 +297,14 @@ def run_ours(args, rank, world, local_rank):
         avg_ms = top[1]["total_ms"] / top[1]["count"]
         ach = per_launch / (avg_ms / 1e3) / 1e9
         roofline = {"kernel": top[0], "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak,
-                    "unit": "GB/s", "frac": round(ach / hbm_peak, 4), "traffic": ncu_traffic_bytes(top[0]),
+                    "unit": "GB/s", "frac": round(ach / hbm_peak, 4), "traffic": ncu_traffic_bytes(top[0], args.workload),
                     "algorithmic_bytes_per_launch": int(per_launch),
                     "avg_launch_us": round(avg_ms * 1e3, 2), "share_of_step": round(top[1]["total_ms"] / total_prof, 3),
                     "peak_source": "measured (MEASURED_PEAKS.json)" if peaks else "fallback"}
     if in_graph and "achieved_GBps" in in_graph:
         in_graph["frac"] = round(in_graph["achieved_GBps"] / hbm_peak, 4)
     ctx_avg = VOICE_P + TEXT_T + Wm + K / 2
-    step_bytes = algorithmic_bytes_per_step(dims, B, ctx_avg, e_bytes)
+    step_bytes = algorithmic_bytes_per_step(dims, B, ctx_avg, e_bytes, 16 * (Wm + K / 2))
     step_frac = step_bytes / (ms / K / 1e3) / 1e9 / hbm_peak
 
     cpu = cpu_baseline(dims, W, sample_streams=8, frames=4)
@@ -332,11 +331,11 @@ def run_ours(args, rank, world, local_rank):
         td.destroy_process_group()
 
 
-def ncu_traffic_bytes(tag):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` summary
-    (profiles/), taken at the start of the generation (context 166-172); None when no capture exists."""
+def ncu_traffic_bytes(tag, workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` summary of THIS
+    workload and kernel (profiles/), taken at the start of the generation; None when no such capture exists."""
     import csv
-    f = {"flow.attn_decode": ROOT / "profiles" / "r01_attn_head_ncu_full_summary.csv"}.get(tag)
+    f = {("cfg2", "flow.attn_decode"): ROOT / "profiles" / "r01_attn_head_ncu_full_summary.csv"}.get((workload, tag))
     if not f or not f.exists():
         return None
     rows = list(csv.reader(open(f)))
@@ -352,6 +351,12 @@ def kernel_algorithmic_bytes(tag, dims, B, ctx, e):
     d, ffn = dims.d_model, dims.ffn
     if tag == "flow.attn_decode":
         return B * 2 * d * e * (ctx + 1) + B * 3 * d * 4 + B * d * e
+    if tag == "head.cluster":     # 12 matrices of 512 x 512 + final 32 x 512 (bf16), input_proj fp32, modulation rows in, latents out
+        F = dims.flow_dim
+        return (2 * dims.flow_depth * F * F + dims.ldim * F) * e + F * dims.ldim * 4 + B * (3 * dims.flow_depth + 2) * F * 4 + 3 * B * dims.ldim * 4
+    if tag == "head.adaln_mod":
+        F = dims.flow_dim
+        return (3 * dims.flow_depth + 2) * F * F * e + B * F * e + B * (3 * dims.flow_depth + 2) * F * 4
     gemm = {"flow.qkv": (3 * d, d), "flow.out_proj": (d, d), "flow.ffn1": (ffn, d), "flow.ffn2": (d, ffn),
             "mimi.qkv": (1536, 512), "mimi.out_proj": (512, 512), "mimi.ffn1": (2048, 512), "mimi.ffn2": (512, 2048)}
     if tag in gemm:
@@ -373,8 +378,38 @@ def kernel_algorithmic_bytes(tag, dims, B, ctx, e):
 
 
 # --------------------------------------------------------------------------- CPU arm
+def reference_cpu_arm(frames, warmup, n_procs=None):
+    """The reference's OWN code (oracle/_ref, vendored by oracle/make_ref.py) on this box's host cores, as shipped:
+    batch 1, torch.set_num_threads(1), generation thread + Mimi thread = 2 cores per utterance (tts_model.py:49,
+    651-658,741-742), through TTSModel.generate_audio_stream; (i) one utterance alone, (ii) floor(cores / 2)
+    utterances in as many processes pinned to disjoint core pairs.  Returns None when the copy is absent."""
+    from oracle import ref_runner as rr
+    if not rr.reference_available():
+        return None
+    cores = os.cpu_count() or 2
+    P = n_procs or max(1, cores // 2)
+    frames = max(4, min(frames, 180 - warmup))      # one utterance of 40 tokens is 192 frames long
+    one = rr.run_processes(1, PRESET, N_LAYERS, VOICE_P, TEXT_T, warmup, frames)
+    many = rr.run_processes(P, PRESET, N_LAYERS, VOICE_P, TEXT_T, warmup, frames) if P > 1 else one
+    return {"as_shipped": {"value": round(one["aggregate_audio_s_per_s"], 3), "cores": 2, "processes": 1},
+            "scaled": {"value": round(many["aggregate_audio_s_per_s"], 3), "cores": min(cores, 2 * P), "processes": P,
+                       "per_process": many["per_process_audio_s_per_s"]},
+            "frames": frames, "host_cores": cores}
+
+
 def cpu_baseline(dims, W, sample_streams=8, frames=4, threads=None):
-    """The CPU port of the reference path (oracle) on this box's host cores, bounded sample."""
+    """CPU baseline of the same workload on this box's host cores, bounded sample: the reference's own code when
+    oracle/_ref exists (kind "reference"), else the oracle port (kind "port")."""
+    try:
+        ref = reference_cpu_arm(frames=24, warmup=4)
+    except Exception as ex:   # the baseline must never break the bench line
+        log("reference CPU arm failed, falling back to the oracle port:", repr(ex)[:300])
+        ref = None
+    if ref is not None:
+        return {"value": ref["scaled"]["value"], "unit": "audio-s/s", "cores": ref["scaled"]["cores"], "kind": "reference",
+                "sample": f"kyutai-labs/pocket-tts own code (oracle/_ref) as shipped, B=1 per process, 1 torch thread per stage, "
+                          f"{ref['scaled']['processes']} processes x {ref['frames']} frames of one {TEXT_T}-token utterance at voice prefix {VOICE_P}",
+                "as_shipped_2_cores": ref["as_shipped"]["value"], "host_cores": ref["host_cores"]}
     import torch
     from oracle import pocket_oracle as po
     threads = threads or os.cpu_count() or 1
@@ -401,6 +436,30 @@ def cpu_baseline(dims, W, sample_streams=8, frames=4, threads=None):
 def run_reference(args, rank, world):
     if rank != 0:
         return
+    K, Wm = args.steps, args.warmup
+    try:
+        ref = reference_cpu_arm(frames=K, warmup=Wm)
+    except Exception as ex:
+        log("reference CPU arm failed, falling back to the oracle port:", repr(ex)[:300])
+        ref = None
+    if ref is not None:
+        value, P = ref["scaled"]["value"], ref["scaled"]["processes"]
+        sample = (f"kyutai-labs/pocket-tts own code (oracle/_ref) as shipped: B=1, torch.set_num_threads(1), generation thread + Mimi "
+                  f"thread per utterance; {P} concurrent utterances in {P} processes pinned to core pairs, {ref['frames']} timed frames "
+                  f"each after {Wm} warm-up frames (a step = one 80 ms frame of every utterance)")
+        line = {"impl": "reference", "metric": "audio-sec generated per sec (RTFx), batched", "value": value,
+                "unit": "audio-s/s", "n_gpus": world, "steps": ref["frames"], "warmup": Wm,
+                "ms_per_step": round(P * FRAME_S / value * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"{'default english' if PRESET == 'english' else PRESET} model ({N_LAYERS}L FlowLM), voice prefix {VOICE_P} + "
+                                       f"{TEXT_T} text tokens; CPU arm: {P} concurrent utterances (all host cores) instead of {STREAMS} streams per GPU"},
+                "cpu_baseline": {"value": value, "unit": "audio-s/s", "cores": ref["scaled"]["cores"], "kind": "reference", "sample": sample,
+                                 "as_shipped_2_cores": ref["as_shipped"]["value"], "host_cores": ref["host_cores"],
+                                 "per_process": ref["scaled"]["per_process"]},
+                "e2e": {"value": value, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0}
+        print(json.dumps(line), flush=True)
+        return
     import torch
     from oracle import pocket_oracle as po
     dims = po.PRESETS[PRESET]
@@ -408,7 +467,6 @@ def run_reference(args, rank, world):
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
     Bs = 16   # bounded sample of the 64-stream workload per step
-    K, Wm = args.steps, args.warmup
     orc = po.Oracle(dims, W)
     tokens, voice, noise = synth_inputs(dims, Bs, Wm + K)
     with torch.no_grad():

@@ -89,7 +89,7 @@ int Engine::timeline_json(char* out, int64_t cap, int max_records) {
 }
 
 Engine::~Engine() {
-  if (tl_buf) { tl_dump(tl_buf); tl_enable_kernels(nullptr); tl_enable_gemm_tc(nullptr); tl_enable_attention(nullptr); tl_enable_head_tc(nullptr); }
+  if (tl_buf) { tl_dump(tl_buf); tl_enable_kernels(nullptr); tl_enable_gemm_tc(nullptr); tl_enable_attention(nullptr); tl_enable_head_tc(nullptr); tl_enable_head_ss(nullptr); }
   for (auto& kv : graphs)
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (void* p : allocs) cudaFree(p);
@@ -166,12 +166,12 @@ int Engine::init() {
   if (const char* f = getenv("PTTS_TIMELINE")) {
     if (f[0] == '1') {
       tl_buf = dmalloc<unsigned long long>(allocs, 2 + TL_W * TL_MAX, stream);
-      if (tl_buf) { tl_enable_kernels(tl_buf); tl_enable_gemm_tc(tl_buf); tl_enable_attention(tl_buf); tl_enable_head_tc(tl_buf); }
+      if (tl_buf) { tl_enable_kernels(tl_buf); tl_enable_gemm_tc(tl_buf); tl_enable_attention(tl_buf); tl_enable_head_tc(tl_buf); tl_enable_head_ss(tl_buf); }
     }
   }
   if (const char* f = getenv("PTTS_KV_SIDE")) use_kv_side_prefetch = f[0] == '1';
   if (const char* f = getenv("PTTS_LNFOLD")) use_ln_fold = !(f[0] == '0');
-  if (const char* f = getenv("PTTS_HEAD")) head_mode = f[0] >= '0' && f[0] <= '2' ? f[0] - '0' : 2;
+  if (const char* f = getenv("PTTS_HEAD")) head_mode = f[0] >= '0' && f[0] <= '3' ? f[0] - '0' : 3;
   for (int k = 0; k < 2; ++k) {
     for (cudaEvent_t* e : {&ev_lat[k], &ev_mimi[k], &ev_copied_lat[k], &ev_copied_pcm[k]})
       PTTS_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));

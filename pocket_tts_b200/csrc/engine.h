@@ -64,6 +64,7 @@ void tl_enable_kernels(unsigned long long*);
 void tl_enable_gemm_tc(unsigned long long*);
 void tl_enable_attention(unsigned long long*);
 void tl_enable_head_tc(unsigned long long*);
+void tl_enable_head_ss(unsigned long long*);
 bool make_sm_partition(int device, int flow_sms, int prio_flow, int prio_mimi, cudaStream_t* s_flow, cudaStream_t* s_mimi,
                        int* n_flow, int* n_mimi);
 
@@ -247,7 +248,7 @@ class Engine {
   bool use_side_branch = true;               // PTTS_SIDE=0 disables
   bool use_kv_side_prefetch = false;         // PTTS_KV_SIDE=1: the QKV GEMM's idle epilogue warps prefetch the layer's K/V rows for the attention kernel (measured: attention 13.2 -> 12.8 us but the GEMM 8.5 -> 10.6 us on the chain, so off)
   bool use_ln_fold = true;                   // PTTS_LNFOLD=0: separate LayerNorm launches in the FlowLM decode layers
-  int head_mode = 2;                         // PTTS_HEAD: 0 flow head as separate launches, 1 cluster kernel on mma.sync (flow_head.cu), 2 on tcgen05 (flow_head_tc.cu)
+  int head_mode = 3;                         // PTTS_HEAD: 0 flow head as separate launches, 1 cluster kernel on mma.sync (flow_head.cu), 2 feature-split cluster kernel on tcgen05 (flow_head_tc.cu), 3 stream-split tcgen05 kernel without cross-CTA exchange (flow_head_ss.cu, default)
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph
   cudaEvent_t ev_lat[2] = {}, ev_mimi[2] = {}, ev_copied_lat[2] = {}, ev_copied_pcm[2] = {};
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)

@@ -224,7 +224,12 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
       const bool last = s == lsd - 1;
       hp.prev_latent = last ? prev_latent : nullptr;
       hp.commit_out = last ? commit_out : nullptr;
-      if (head_mode == 2) {
+      if (head_mode == 3 && flow_head_ss_supported(F, Ld, c.flow_depth)) {
+        FlowHeadTcParams tp;
+        tp.h = hp;
+        if (!flow_head_ss_prepare(&tp)) PTTS_FAIL(PTTS_ECUDA, "tensor map encode failed (flow head)");
+        LAUNCH("head.cluster", launch_flow_head_ss(tp, stream));
+      } else if (head_mode >= 2) {
         FlowHeadTcParams tp;
         tp.h = hp;
         tp.xchg = head_l2_exchange ? head_xchg : nullptr;

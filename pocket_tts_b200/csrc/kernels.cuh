@@ -104,6 +104,11 @@ struct FlowHeadTcParams {
 };
 bool flow_head_tc_prepare(FlowHeadTcParams* p);   // fills `maps` from h (cached driver encodes)
 cudaError_t launch_flow_head_tc(const FlowHeadTcParams& p, cudaStream_t st);
+// stream-split form (flow_head_ss.cu, default): 16 streams per CTA, features on the TMEM lanes, no cross-CTA exchange;
+// uses `maps` with 128-row weight boxes (its own prepare) and ignores xmap / xchg.
+bool flow_head_ss_supported(int flow_dim, int ldim, int depth);
+bool flow_head_ss_prepare(FlowHeadTcParams* p);
+cudaError_t launch_flow_head_ss(const FlowHeadTcParams& p, cudaStream_t st);
 
 // x[i,:] -> prev_latent[slot] and out (nullable)
 cudaError_t launch_commit_latent(const float* x, const int* slot_ids, float* prev_latent,

@@ -133,7 +133,7 @@ def test_mimi_52_frames_ring_wrap_grouped_passes(precision):
     lat = case["latents"][0]                                  # [52, 32]
     snrs = {}
     for mode in ("grouped", "single"):
-        eng = make_engine(1, precision=precision)
+        eng = make_engine(6, precision=precision)        # the Mimi weights of make_weights depend on n_layers (draw order)
         s = eng.open_stream()
         if mode == "grouped":
             pcm = eng.mimi_decode_frames([s], lat[:, None, :])[0]
