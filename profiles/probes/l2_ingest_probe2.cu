@@ -10,14 +10,16 @@
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 // NW issuing warps; warp w owns stages s with s % NW == w.  TENSOR: 2-D tiled loads of box 64 x ROWS bf16.
-template <int STAGES, int ROWS, int NW, bool TENSOR>
+template <int STAGES, int ROWS, int NW, bool TENSOR, bool LANES = false>
 __global__ void __launch_bounds__(NW * 32, 1) ingest2(const char* src, const __grid_constant__ CUtensorMap map, int n_tiles, int reps,
                                                       unsigned long long* out_ns) {
   extern __shared__ __align__(1024) char smraw[];
   char* sm = (char*)(((uintptr_t)smraw + 1023) & ~(uintptr_t)1023);
   __shared__ uint64_t full[STAGES];
   constexpr uint32_t CHUNK = ROWS * 128;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x;
+  const int warp = LANES ? (tid < NW ? tid : 0) : (tid >> 5);
+  const int lane = LANES ? (tid < NW ? 0 : 1) : (tid & 31);
   if (tid == 0)
     for (int s = 0; s < STAGES; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&full[s])), "r"(1));
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -61,7 +63,7 @@ __global__ void __launch_bounds__(NW * 32, 1) ingest2(const char* src, const __g
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
                              const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-template <int STAGES, int ROWS, int NW, bool TENSOR>
+template <int STAGES, int ROWS, int NW, bool TENSOR, bool LANES = false>
 void run(const char* d, EncodeFn enc, int ctas, int reps, unsigned long long* d_ns) {
   const size_t bytes = 512 * 1024;
   const int n_tiles = (int)(bytes / (ROWS * 128));
@@ -71,7 +73,7 @@ void run(const char* d, EncodeFn enc, int ctas, int reps, unsigned long long* d_
   CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)d, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { printf("encode failed %d\n", (int)r); return; }
-  auto k = ingest2<STAGES, ROWS, NW, TENSOR>;
+  auto k = ingest2<STAGES, ROWS, NW, TENSOR, LANES>;
   const size_t smem = (size_t)STAGES * ROWS * 128 + 1024;
   cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   for (int it = 0; it < 3; ++it) {
@@ -84,7 +86,7 @@ void run(const char* d, EncodeFn enc, int ctas, int reps, unsigned long long* d_
   unsigned long long mx = 0;
   for (auto v : ns) mx = v > mx ? v : mx;
   const double gb = (double)bytes * reps / 1e9;
-  printf("%s stages %2d box 64x%3d (%2d KB) warps %d ctas %3d: %.1f GB/s per CTA (%.1f us for %d x 512 KB), %.1f B/clk\n", TENSOR ? "tensor2d" : "bulk1d  ",
+  printf("%s%s stages %2d box 64x%3d (%2d KB) warps %d ctas %3d: %.1f GB/s per CTA (%.1f us for %d x 512 KB), %.1f B/clk\n", TENSOR ? "tensor2d" : "bulk1d  ", LANES ? " lanes-of-one-warp" : "",
          STAGES, ROWS, ROWS / 8, NW, ctas, gb / (mx * 1e-9), mx / 1e3, reps, gb / (mx * 1e-9) / 1.965);
 }
 
@@ -97,7 +99,7 @@ int main() {
   cudaMalloc(&d, 4 << 20); cudaMemset(d, 1, 4 << 20);
   cudaMalloc(&d_ns, 1024 * 8);
   const int reps = 12;
-  for (int ctas : {1, 4, 16}) {
+  for (int ctas : {1, 148}) {
     run<12, 128, 1, false>(d, enc, ctas, reps, d_ns);
     run<12, 128, 2, false>(d, enc, ctas, reps, d_ns);
     run<12, 128, 4, false>(d, enc, ctas, reps, d_ns);
@@ -108,6 +110,10 @@ int main() {
     run<6, 256, 2, true>(d, enc, ctas, reps, d_ns);
     run<24, 64, 4, true>(d, enc, ctas, reps, d_ns);
     run<24, 64, 1, true>(d, enc, ctas, reps, d_ns);
+    run<12, 128, 2, true, true>(d, enc, ctas, reps, d_ns);
+    run<12, 128, 4, true, true>(d, enc, ctas, reps, d_ns);
+    run<12, 128, 8, true>(d, enc, ctas, reps, d_ns);
+    run<6, 256, 4, true>(d, enc, ctas, reps, d_ns);
   }
   return 0;
 }
