@@ -161,6 +161,23 @@ int ptts_generate_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_
  * pointers may be host or device memory.  Halves the bytes of the device-to-host PCM copy. */
 int ptts_pcm_to_int16(ptts_engine* e, const float* pcm_any, int16_t* out_any, int64_t n);
 
+/* The same conversion for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * ptts_pcm_to_int16 stages host buffers through a device buffer it grows with cudaMalloc; this entry point stages them
+ * through a fixed file-scope device array instead (csrc/static_scratch.cu) and calls no cudaMalloc / cudaFree / other
+ * allocating routine.  Limits and rules:
+ *   - n <= PTTS_PCM_STATIC_MAX_SAMPLES (262144 samples = 10.9 s of 24 kHz audio); larger n returns PTTS_EINVAL.  Every
+ *     GPU that loads the library holds the array (6 bytes per sample = 1.5 MiB) until the process exits.
+ *   - The first call on a device resolves the array's device address (cudaGetSymbolAddress, once per device): make
+ *     one call before entering graph capture.
+ *   - All calls on a GPU share the array, which keeps the previous call's contents; a call only reads what it has
+ *     just written, so nothing needs clearing.  The call returns after the engine stream has drained, so calls on
+ *     one engine never overlap; calls that overlap on the same GPU (several engines / host threads) race on the
+ *     array and must be serialised by the caller.
+ * Results are bit-identical to ptts_pcm_to_int16. */
+#define PTTS_PCM_STATIC_MAX_SAMPLES 262144
+int ptts_pcm_to_int16_static(ptts_engine* e, const float* pcm_any, int16_t* out_any, int64_t n);
+
 int ptts_synchronize(ptts_engine* e);
 /* Number of engine kernels launched (or replayed through a graph) since creation. */
 int64_t ptts_launch_count(ptts_engine* e);

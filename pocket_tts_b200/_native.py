@@ -68,6 +68,7 @@ def load_library() -> C.CDLL:
         "ptts_run_frames": (C.c_int, [p, i32, i32p, i32, f32p, i32, f32p, f32p]),
         "ptts_generate_frames": (C.c_int, [p, i32, i32p, i32, f32p, i32, f32p, f32p, f32p]),
         "ptts_pcm_to_int16": (C.c_int, [p, f32p, p, i64]),
+        "ptts_pcm_to_int16_static": (C.c_int, [p, f32p, p, i64]),
         "ptts_synchronize": (C.c_int, [p]),
         "ptts_launch_count": (i64, [p]),
         "ptts_stream_handle": (p, [p]),

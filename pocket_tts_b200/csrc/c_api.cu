@@ -157,6 +157,11 @@ int ptts_generate_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_
 int ptts_pcm_to_int16(ptts_engine* e, const float* pcm_any, int16_t* out_any, int64_t n) {
   API_BEGIN NEED(e) return e->impl->pcm_to_int16(pcm_any, reinterpret_cast<short*>(out_any), (long long)n); API_END
 }
+int ptts_pcm_to_int16_static(ptts_engine* e, const float* pcm_any, int16_t* out_any, int64_t n) {
+  API_BEGIN NEED(e)
+  return ptts::pcm_to_int16_static(e->impl->stream, pcm_any, reinterpret_cast<short*>(out_any), (long long)n, &e->impl->launches);
+  API_END
+}
 int ptts_synchronize(ptts_engine* e) {
   API_BEGIN NEED(e)
   cudaError_t ce = cudaStreamSynchronize(e->impl->stream);

@@ -65,6 +65,8 @@ void tl_enable_gemm_tc(unsigned long long*);
 void tl_enable_attention(unsigned long long*);
 void tl_enable_head_tc(unsigned long long*);
 void tl_enable_head_ss(unsigned long long*);
+// static_scratch.cu: PCM egress conversion staged through a file-scope device array (no allocation)
+int pcm_to_int16_static(cudaStream_t stream, const float* pcm_any, short* out_any, long long n, long long* launches);
 bool make_sm_partition(int device, int flow_sms, int prio_flow, int prio_mimi, cudaStream_t* s_flow, cudaStream_t* s_mimi,
                        int* n_flow, int* n_mimi);
 

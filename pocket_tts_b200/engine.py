@@ -270,6 +270,19 @@ class GenerationEngine:
         N.check(self.lib.ptts_pcm_to_int16(self._h, _ptr(pcm), _ptr(out), pcm.numel()))
         return out
 
+    PCM_STATIC_MAX_SAMPLES = 262144
+
+    def pcm_to_int16_static(self, pcm: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        """`pcm_to_int16` without any device allocation inside the library: host buffers are staged through a fixed
+        device array (at most PCM_STATIC_MAX_SAMPLES samples per call).  Pass `out` (int16, same shape and place
+        as `pcm`) to keep the call allocation-free on the Python side too."""
+        assert pcm.dtype == torch.float32 and pcm.is_contiguous()
+        if out is None:
+            out = torch.empty(pcm.shape, dtype=torch.int16, device=pcm.device)
+        assert out.dtype == torch.int16 and out.is_contiguous() and out.numel() == pcm.numel()
+        N.check(self.lib.ptts_pcm_to_int16_static(self._h, _ptr(pcm), _ptr(out), pcm.numel()))
+        return out
+
     def synchronize(self) -> None:
         N.check(self.lib.ptts_synchronize(self._h))
 
