@@ -28,9 +28,13 @@ def make_ref(force: bool = False) -> Path | None:
         if (DST / ".stamp").exists() and (DST / ".stamp").stat().st_mtime >= newest_src:
             return DST
     if DST.exists():
+        for q in [DST, *DST.rglob("*")]:     # the copy inherits the read-only modes of /root/reference
+            q.chmod(0o755 if q.is_dir() else 0o644)
         shutil.rmtree(DST)
     DST.parent.mkdir(parents=True, exist_ok=True)
     shutil.copytree(SRC, DST, ignore=shutil.ignore_patterns("__pycache__", "*.pyc", "static"))
+    for q in [DST, *DST.rglob("*")]:
+        q.chmod(0o755 if q.is_dir() else 0o644)
     (DST / ".stamp").write_text("copied unmodified from /root/reference/pocket_tts by oracle/make_ref.py\n")
     return DST
 
