@@ -71,8 +71,9 @@ int ptts_engine_destroy(ptts_engine* e);
 
 /* load_state_dict (tts_model.py:209-210): one call per state_dict entry, names exactly as in
  * TTSModel.state_dict() ("flow_lm.transformer.layers.0.self_attn.in_proj.weight", ...).
- * Encode-only / unknown names return PTTS_EINVAL unless they start with an ignorable prefix
- * (mimi.encoder*, mimi.downsample*), which return PTTS_OK and are skipped.  Two derived,
+ * The Mimi encoder side (mimi.encoder.*, mimi.encoder_transformer.*, mimi.downsample.*,
+ * flow_lm.speaker_proj_weight) is optional: loaded whole it enables ptts_encode_audio, absent (the
+ * "without voice cloning" checkpoints, tts_model.py:871-872) that call returns PTTS_ESTATE.  Two derived,
  * input-independent tables are loaded the same way: "rope.freqs" [head_dim/2]
  * (rope.py:28-29) and "flow.tcomb" [lsd_steps, flow_dim] (mlp.py:205-209 evaluated at
  * s=i/n, t=(i+1)/n, flow_lm.py:33-37). */
@@ -155,6 +156,18 @@ int ptts_run_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_f
 int ptts_generate_frames(ptts_engine* e, int32_t n, const int32_t* slots, int32_t n_frames,
                          const float* noise_any, int32_t lsd_steps, float* out_pcm_any,
                          float* out_latents_any, float* out_eos_logit_any);
+
+/* Voice-prompt encoding on the device: TTSModel._encode_audio (tts_model.py:379-388) = MimiModel.encode_to_latent
+ * (mimi.py:96-119: right padding to whole 1920-sample frames, SEANet encoder seanet.py:44-113, causal window-250
+ * encoder transformer, ConvDownsample1d resample.py:7-29) followed by F.linear(latents, speaker_proj_weight).
+ * audio_any: n_samples mono fp32 samples at 24 kHz (what convert_audio hands the reference, tts_model.py:885-887);
+ * out_cond_any [n_frames, d_model] are the conditioning rows the caller prefills after bos_before_voice
+ * (tts_model.py:893-899) with ptts_prefill.  n_frames = ceil(n_samples / 1920) is returned through n_frames_out;
+ * out_cond_any == NULL only queries it.  Runs in fp32 in either precision mode.  At most
+ * PTTS_ENCODE_MAX_SAMPLES samples (60 s; the reference's truncate=True keeps 30 s, tts_model.py:878-882). */
+#define PTTS_ENCODE_MAX_SAMPLES 1440000
+int ptts_encode_audio(ptts_engine* e, const float* audio_any, int64_t n_samples, float* out_cond_any,
+                      int32_t max_frames, int32_t* n_frames_out);
 
 /* PCM egress: fp32 -> 16-bit samples exactly as the reference's WAV writer does on the host
  * (data/audio.py:77-78: clamp(-1, 1) * 32767, truncated), on the device; n samples; both

@@ -67,6 +67,7 @@ def load_library() -> C.CDLL:
         "ptts_mimi_decode_frames": (C.c_int, [p, i32, i32p, i32, f32p, f32p]),
         "ptts_run_frames": (C.c_int, [p, i32, i32p, i32, f32p, i32, f32p, f32p]),
         "ptts_generate_frames": (C.c_int, [p, i32, i32p, i32, f32p, i32, f32p, f32p, f32p]),
+        "ptts_encode_audio": (C.c_int, [p, f32p, i64, f32p, i32, i32p]),
         "ptts_pcm_to_int16": (C.c_int, [p, f32p, p, i64]),
         "ptts_pcm_to_int16_static": (C.c_int, [p, f32p, p, i64]),
         "ptts_synchronize": (C.c_int, [p]),

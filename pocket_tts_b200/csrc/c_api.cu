@@ -162,6 +162,15 @@ int ptts_pcm_to_int16_static(ptts_engine* e, const float* pcm_any, int16_t* out_
   return ptts::pcm_to_int16_static(e->impl->stream, pcm_any, reinterpret_cast<short*>(out_any), (long long)n, &e->impl->launches);
   API_END
 }
+int ptts_encode_audio(ptts_engine* e, const float* audio_any, int64_t n_samples, float* out_cond_any, int32_t max_frames,
+                      int32_t* n_frames_out) {
+  API_BEGIN NEED(e)
+  int nf = 0;
+  const int rc = e->impl->encode_audio(audio_any, (long long)n_samples, out_cond_any, max_frames, &nf);
+  if (n_frames_out) *n_frames_out = nf;
+  return rc;
+  API_END
+}
 int ptts_synchronize(ptts_engine* e) {
   API_BEGIN NEED(e)
   cudaError_t ce = cudaStreamSynchronize(e->impl->stream);

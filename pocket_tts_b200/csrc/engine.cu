@@ -94,6 +94,7 @@ Engine::~Engine() {
     if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
   for (void* p : allocs) cudaFree(p);
   if (egress_buf) cudaFree(egress_buf);
+  if (enc_scratch) cudaFree(enc_scratch);
   if (h_pinned) cudaFreeHost(h_pinned);
   if (h_mega_diag) cudaFreeHost(h_mega_diag);
   if (ev_fork) cudaEventDestroy(ev_fork);
@@ -290,9 +291,6 @@ int Engine::load_tensor(const char* name, const float* data, const int64_t* shap
   if (ready) PTTS_FAIL(PTTS_ESTATE, "load_tensor after finalize");
   if (!name || !data || ndim < 0 || ndim > 4) PTTS_FAIL(PTTS_EINVAL, "bad load_tensor arguments");
   std::string nm(name);
-  static const char* skip[] = {"mimi.encoder.", "mimi.encoder_transformer.", "mimi.downsample."};
-  for (const char* s : skip)
-    if (nm.rfind(s, 0) == 0) return PTTS_OK;  // encode-only (voice prompt, host side)
   HostTensor t;
   t.shape.assign(shape, shape + ndim);
   const int64_t n = t.numel();

@@ -54,6 +54,23 @@ struct ConvStageW {
   Mat c1;  float* c1_b;      // [C2, h]
 };
 
+// Mimi encoder side (voice-prompt encoding, engine_encoder.cu); all fp32
+struct EncStageW {
+  Mat c3;   float* c3_b = nullptr;     // ResBlock conv K3 [C/2, 3C]
+  Mat c1;   float* c1_b = nullptr;     // ResBlock conv K1 [C, C/2]
+  Mat down; float* down_b = nullptr;   // strided conv K = 2r, S = r: [2C, 2r*C]
+  int ratio = 0;
+};
+struct EncoderW {
+  bool loaded = false;
+  float *w0 = nullptr, *b0 = nullptr;  // first conv [C0, 1, K] as stored
+  EncStageW st[3];
+  Mat last; float* last_b = nullptr;   // final conv K3 -> mimi_d
+  std::vector<LayerW> layers;          // encoder transformer
+  Mat down;                            // ConvDownsample1d [ldim, 2U*mimi_d]
+  Mat speaker;                         // flow_lm.speaker_proj_weight [d_model, ldim]
+};
+
 struct MegaPlan {            // phase program of the persistent FlowLM step kernel for one lsd_steps value
   CUtensorMap* d_maps = nullptr;
   MegaPhase* d_phases = nullptr;
@@ -114,6 +131,7 @@ class Engine {
   int debug_gemm(int backend, int M, int N, int K, int ld, int rows_per_batch, int valid_rows,
                  const float* a_host, long long a_elems, const float* w_host, float* out_host);
   int pcm_to_int16(const float* pcm_any, short* out_any, long long n);
+  int encode_audio(const float* audio_any, long long n_samples, float* out_cond_any, int max_frames, int* n_frames);
   int timeline_json(char* out, int64_t cap, int max_records);
   int profile_begin();
   int profile_end(char* json_out, int64_t cap);
@@ -144,6 +162,7 @@ class Engine {
   KvPrefetchJob flow_kv_prefetch_job(int layer, int n) const;
   void prof_begin(const char* tag);
   void prof_end();
+  int load_encoder();
   int make_ln_folded(const std::string& wname, const std::string& gname, const std::string& bname, int N, int K, Mat* m,
                      float** c1, float** c2);
   int flow_layer_decode_folded(int l, int n);
@@ -175,6 +194,9 @@ class Engine {
   unsigned long long* d_mega_trace = nullptr;
   std::map<int, MegaPlan> mega_plans;
 
+  EncoderW enc;
+  float* enc_scratch = nullptr;              // encode_audio working set, grown on demand
+  long long enc_scratch_elems = 0;
   bool ready = false;
   int act_type = 0;  // 0 fp32, 1 bf16
   size_t act_size = 4;

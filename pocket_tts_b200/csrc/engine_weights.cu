@@ -255,6 +255,7 @@ int Engine::finalize() {
     last_w = upload(conv_to_gemm(*w));
     GETV(last_b, pl + "bias", 1);
   }
+  if ((rc = load_encoder()) != PTTS_OK) return rc;   // optional: mimi.encoder* / mimi.downsample* / speaker_proj_weight
   PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
   host_w.clear();
   ready = true;

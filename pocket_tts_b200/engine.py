@@ -114,9 +114,12 @@ class GenerationEngine:
         N.check(self.lib.ptts_load_tensor(self._h, name.encode(), _ptr(t), shape, t.dim()))
 
     def _load(self, sd: dict) -> None:
-        skip = ("flow_lm.conditioner.", "flow_lm.bos_before_voice", "flow_lm.speaker_proj_weight",
+        skip = ("flow_lm.conditioner.", "flow_lm.bos_before_voice",
                 "flow_lm.flow_net.time_embed.")  # host-side only / folded into flow.tcomb
         keep = ("flow_lm.conditioner.embed.weight",)  # device-side embedding gather of prefill_tokens
+        # the Mimi encoder side (mimi.encoder*, mimi.downsample*, speaker_proj_weight) is loaded when the state_dict
+        # carries it: it enables encode_audio (voice-prompt encoding on the device)
+        self.has_encoder = "mimi.encoder.model.0.conv.weight" in sd
         for name, t in sd.items():
             if name.startswith(skip) and name not in keep:
                 continue
@@ -268,6 +271,19 @@ class GenerationEngine:
         pcm = pcm.detach().to(torch.float32).contiguous()
         out = torch.empty(pcm.shape, dtype=torch.int16, device=pcm.device)
         N.check(self.lib.ptts_pcm_to_int16(self._h, _ptr(pcm), _ptr(out), pcm.numel()))
+        return out
+
+    ENCODE_MAX_SAMPLES = 1440000
+
+    def encode_audio(self, audio: torch.Tensor) -> torch.Tensor:
+        """TTSModel._encode_audio (tts_model.py:379-388) on the device: mono 24 kHz waveform [samples] or [1, samples]
+        -> conditioning rows [ceil(samples / 1920), d_model] (fp32, on the host), to be prefilled after
+        bos_before_voice.  Needs the Mimi encoder weights in the state_dict (models with voice cloning)."""
+        a = audio.detach().to(torch.float32).reshape(-1).contiguous()
+        nf = C.c_int32(0)
+        N.check(self.lib.ptts_encode_audio(self._h, _ptr(a), a.numel(), None, 0, C.byref(nf)))
+        out = torch.empty(nf.value, self.cfg.d_model, dtype=torch.float32)
+        N.check(self.lib.ptts_encode_audio(self._h, _ptr(a), a.numel(), _ptr(out), nf.value, C.byref(nf)))
         return out
 
     PCM_STATIC_MAX_SAMPLES = 262144

@@ -28,8 +28,8 @@ from .text import (MAX_TOKEN_PER_CHUNK, ReferenceTokenizerAdapter, SentencePiece
 logger = logging.getLogger(__name__)
 
 VOICE_CLONING_UNSUPPORTED = (
-    "Voice cloning from raw audio needs the Mimi encoder, which stays on the host: pass "
-    "`audio_encoder=` (e.g. the reference model's `_encode_audio`), a .safetensors model state, or a "
+    "Voice cloning from raw audio needs the Mimi encoder weights (mimi.encoder*, mimi.downsample*), which this "
+    "state_dict does not carry (a model without voice cloning): pass a .safetensors model state or a "
     "pre-encoded conditioning tensor [P, d_model]."
 )
 _BLOCK_SCHEDULE = (1, 1, 2, 4)  # frames per engine call at the start of a chunk (first PCM after one frame)
@@ -105,14 +105,15 @@ class TTSModel:
         self.pad_with_spaces_for_short_inputs = pad_with_spaces_for_short_inputs
         self.remove_semicolons = remove_semicolons
         self.model_recommended_frames_after_eos = model_recommended_frames_after_eos
-        self.audio_encoder = audio_encoder
-        self.has_voice_cloning = audio_encoder is not None
+        self.audio_encoder = audio_encoder          # optional host override; default is the engine's own encoder
         self._embed = state_dict["flow_lm.conditioner.embed.weight"].detach().float().cpu()
         bos = state_dict.get("flow_lm.bos_before_voice")
         self._bos_before_voice = None if bos is None else bos.detach().float().cpu().reshape(1, cfg.d_model)
         self.engine = GenerationEngine(cfg, state_dict, max_streams=max_streams, kv_capacity=kv_capacity,
                                        precision=precision, device=device, lsd_steps=lsd_decode_steps,
                                        max_prefill_rows=max_prefill_rows)
+        # voice cloning = the Mimi encoder side is in the state_dict (tts_model.py:871-872) -> ptts_encode_audio
+        self.has_voice_cloning = self.engine.has_encoder or audio_encoder is not None
         self._outs: dict = {}
 
     # ------------------------------------------------------------------ construction
@@ -159,8 +160,11 @@ class TTSModel:
                           last_kernel=sn.last_kernel_size,
                           upsample_stride=int(ref.mimi.encoder_frame_rate / ref.mimi.frame_rate),
                           frame_rate=float(c.mimi.frame_rate), sample_rate=int(c.mimi.sample_rate))
-        enc = (lambda audio: ref._encode_audio(audio)) if getattr(ref, "has_voice_cloning", False) else None
-        return cls(cfg, ref.state_dict(), ReferenceTokenizerAdapter(ref.flow_lm.conditioner.tokenizer),
+        sd = ref.state_dict()
+        if not getattr(ref, "has_voice_cloning", False):   # encoder weights of such a checkpoint are uninitialised
+            sd = {k: v for k, v in sd.items() if not k.startswith(("mimi.encoder", "mimi.downsample"))}
+        enc = None
+        return cls(cfg, sd, ReferenceTokenizerAdapter(ref.flow_lm.conditioner.tokenizer),
                    temp=ref.temp, lsd_decode_steps=ref.lsd_decode_steps, noise_clamp=ref.noise_clamp,
                    eos_threshold=ref.eos_threshold,
                    pad_with_spaces_for_short_inputs=getattr(ref, "pad_with_spaces_for_short_inputs", False),
@@ -246,8 +250,9 @@ class TTSModel:
     @torch.no_grad()
     def get_state_for_audio_prompt(self, audio_conditioning, truncate: bool = False) -> dict:
         """tts_model.py:788-905.  Accepts a .safetensors model state, a waveform tensor
-        [channels, samples] / audio file (needs `audio_encoder`, the Mimi encoder stays on the host), or -
-        extension - an already encoded conditioning tensor [P, d_model] / [1, P, d_model]."""
+        [channels, samples] / audio file (encoded on the device by the engine's Mimi encoder, ptts_encode_audio =
+        _encode_audio tts_model.py:379-388), or - extension - an already encoded conditioning tensor
+        [P, d_model] / [1, P, d_model]."""
         if isinstance(audio_conditioning, (str, Path)) and str(audio_conditioning).endswith(".safetensors"):
             return import_model_state(audio_conditioning)
         if isinstance(audio_conditioning, (str, Path)):
@@ -267,7 +272,12 @@ class TTSModel:
         else:
             if not self.has_voice_cloning:
                 raise ValueError(VOICE_CLONING_UNSUPPORTED)
-            prompt = self.audio_encoder(t.unsqueeze(0)).reshape(-1, self.cfg.d_model).float().cpu()
+            if self.audio_encoder is not None:
+                prompt = self.audio_encoder(t.unsqueeze(0)).reshape(-1, self.cfg.d_model).float().cpu()
+            else:
+                if t.dim() == 2 and t.shape[0] != 1:
+                    raise ValueError("audio conditioning must be mono [1, samples] (convert_audio, tts_model.py:885-887)")
+                prompt = self.engine.encode_audio(t)
         if self.cfg.insert_bos_before_voice and self._bos_before_voice is not None:
             prompt = torch.cat([self._bos_before_voice, prompt], dim=0)
         slot = self.engine.open_stream()

@@ -51,6 +51,32 @@ def load_case(name: str):
     return case
 
 
+def synth_audio(seed: int, samples: int) -> torch.Tensor:
+    """[1, samples] synthetic voice prompt (noise + two tones, amplitude ~0.1) of the encoder fixtures."""
+    g = torch.Generator().manual_seed(seed)
+    t = torch.arange(samples, dtype=torch.float32) / 24000.0
+    x = 0.05 * torch.randn(samples, generator=g)
+    x = x + 0.08 * torch.sin(2 * torch.pi * 220.0 * t) + 0.04 * torch.sin(2 * torch.pi * 1333.0 * t + 0.5)
+    return x[None].contiguous()
+
+
+def load_encoder_case(name: str):
+    """tests/golden/encode_*.npz (make_golden_encoder.py): the waveform is redrawn from its seed and checked."""
+    import hashlib
+
+    g = np.load(GOLD / f"{name}.npz")
+    audio = synth_audio(int(g["seed"]), int(g["samples"]))
+    assert hashlib.sha256(audio.numpy().tobytes()).hexdigest() == str(g["audio_sha256"]), "synthetic waveform differs from the fixture's"
+    rows = torch.from_numpy(g["rows"]).long() if "rows" in g else torch.arange(int(g["frames"]))
+    return dict(audio=audio, frames=int(g["frames"]), rows=rows, cond=torch.from_numpy(g["cond"]))
+
+
+def encoder_weights():
+    if "enc" not in _WEIGHTS:
+        _WEIGHTS["enc"] = po.make_encoder_weights(po.ModelDims(n_layers=2), seed=0)
+    return _WEIGHTS["enc"]
+
+
 def oracle_for(n_layers: int, lsd=1):
     return po.Oracle(po.ModelDims(n_layers=n_layers), weights(n_layers), lsd_steps=lsd)
 
