@@ -1,6 +1,7 @@
 // Engine implementation, part 3: the kernel sequences of prefill / frame step / Mimi decode.
 #include "engine.h"
 
+#include <algorithm>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
@@ -302,6 +303,16 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
   }
   for (int i = 0; i < 3; ++i) {
     const int r = c.ratios[i], T2 = T * r, C2 = C / 2, hc = hid_width(C2 / 2), rk = c.res_kernel - 1;
+    if (i == 2 && use_fused_stage2 && act_type == 1 && use_tc &&
+        seanet_stage2_fused_supported(C, C2, r, C2 / 2, hc, c.res_kernel, c.last_kernel)) {
+      // the whole last stage + final conv in one persistent kernel (seanet_fused.cu): reads b_tr[2], writes PCM
+      LAUNCH("seanet.stage2_fused",
+             launch_seanet_stage2_fused((const bf16*)b_tr[2], stages[2].tr.b16, stages[2].c3.b16, stages[2].c1.b16, fused2_consts,
+                                        (bf16*)b_res[2], (bf16*)b_last, pcm_out, n, T,
+                                        fused_sms > 0 ? std::min(fused_sms, n_sms) : (fused_sms < 0 ? n_sms : 1 << 30), pdl_enabled(), stream));
+      LAUNCH("seanet.hist_scatter", launch_hist_scatter(tab, d_slot_ids, act_type, n, stream));
+      return PTTS_OK;
+    }
     {  // ConvTranspose1d K=2r (seanet.py:147-152): raw -> b_raw (residual), ELU(raw) -> b_res
       const int rpb = 1 + T;
       GemmEpilogue ep; ep.bias = stages[i].tr_b; ep.act_post = ACT_ELU;

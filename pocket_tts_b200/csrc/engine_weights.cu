@@ -254,6 +254,25 @@ int Engine::finalize() {
     if (w->shape != std::vector<int64_t>{1, C, c.last_kernel}) PTTS_FAIL(PTTS_EINVAL, "bad last conv shape");
     last_w = upload(conv_to_gemm(*w));
     GETV(last_b, pl + "bias", 1);
+    // host copies of the last stage's per-channel vectors for the fused stage kernel (seanet_fused.cu)
+    if (C == 64 && c.last_kernel == 3 && c.ratios[2] == 4) {
+      const std::vector<float> lw = conv_to_gemm(*w);
+      const std::string pt2 = "mimi.decoder.model." + std::to_string(idx - 2) + ".convtr.bias";
+      const std::string pr2 = "mimi.decoder.model." + std::to_string(idx - 1) + ".block.";
+      const HostTensor *bt = need(pt2), *b3 = need(pr2 + "1.conv.bias"), *b1 = need(pr2 + "3.conv.bias"), *bl = need(pl + "bias");
+      if (!bt || !b3 || !b1 || !bl) return PTTS_EINVAL;
+      if (bt->numel() == 64 && b3->numel() == 32 && b1->numel() == 64 && lw.size() == 192) {
+        for (int j = 0; j < 256; ++j) fused2_consts.b_tr[j] = bt->data[j & 63];
+        for (int j = 0; j < 64; ++j) fused2_consts.b_c1[j] = b1->data[j];
+        for (int j = 0; j < 32; ++j) fused2_consts.b_c3[j] = b3->data[j];
+        for (int j = 0; j < 192; ++j) fused2_consts.w_last[j] = lw[j];
+        fused2_consts.b_last = bl->data[0];
+      } else {
+        use_fused_stage2 = false;
+      }
+    } else {
+      use_fused_stage2 = false;
+    }
   }
   if ((rc = load_encoder()) != PTTS_OK) return rc;   // optional: mimi.encoder* / mimi.downsample* / speaker_proj_weight
   PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));

@@ -145,6 +145,18 @@ cudaError_t launch_hist_scatter(const HistTable& t, const int* slot_ids, int typ
 cudaError_t launch_last_conv(const void* buf, int buf_type, const float* w, const float* b,
                              float* pcm, int n, int T, int C, int K, cudaStream_t st);
 
+// Last SEANet decoder stage + final conv as one persistent tcgen05 kernel (seanet_fused.cu; bf16 mode, english / 24L shapes):
+// x_buf [n][1 + T][128] -> pcm [n][4T]; conv histories in / out through the history rows of res_buf / last_buf.
+bool seanet_stage2_fused_supported(int c_in, int c_out, int ratio, int hid, int hid_padded, int res_kernel, int last_kernel);
+struct FusedStage2Consts {       // host copies of the stage's per-channel vectors (they travel as kernel parameters)
+  float b_tr[256], b_c1[64], b_c3[32], w_last[192], b_last;
+};
+// grid_cap: at most that many CTAs (>= number of tiles: one tile per CTA, short CTAs that high-priority kernels of the
+// other branch can slip between; number of SMs: persistent form)
+cudaError_t launch_seanet_stage2_fused(const bf16* x_buf, const bf16* w_tr, const bf16* w3, const bf16* w1, const FusedStage2Consts& cst,
+                                       bf16* res_buf, bf16* last_buf, float* pcm, int n, int T, int grid_cap, bool pdl, cudaStream_t st,
+                                       unsigned long long* trace = nullptr);
+
 // data/audio.py:77-78: (clamp(x, -1, 1) * 32767) truncated to int16
 cudaError_t launch_pcm_to_int16(const float* pcm, short* out, long long n, cudaStream_t st);
 

@@ -163,22 +163,26 @@ template <int CH> __device__ __forceinline__ void row_store(bf16* p, const float
 // short forms below (absolute error <= 2e-7) are exact to the storage precision while keeping the
 // unrolled epilogue small (the libm erff / expm1f bodies made each kernel ~10k SASS instructions and
 // cold instruction fetch dominated the short decode GEMMs).  The fp32 parity mode never comes here.
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float gelu_call(float x) {
-  // erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7)
+  // erf by Abramowitz-Stegun 7.1.26 (|err| < 1.5e-7); one MUFU.RCP + one MUFU.EX2, flush-to-zero forms (the plain
+  // __expf / __frcp_rn bodies carry denormal and rounding fix-ups that tripled the instruction count of the epilogue)
   const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __frcp_rn(fmaf(0.3275911f, z, 1.0f));
+  const float t = rcp_ftz(fmaf(0.3275911f, z, 1.0f));
   float p = fmaf(1.061405429f, t, -1.453152027f);
   p = fmaf(p, t, 1.421413741f);
   p = fmaf(p, t, -0.284496736f);
   p = fmaf(p, t, 0.254829592f);
-  const float e = 1.0f - p * t * __expf(-z * z);
+  const float e = 1.0f - p * t * ex2_ftz(-1.4426950408889634f * z * z);
   return 0.5f * x * (1.0f + copysignf(e, x));
 }
-__device__ __forceinline__ float silu_call(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float silu_call(float x) { return x * rcp_ftz(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
+// exp(x) - 1 through ex2.approx: absolute error ~1e-7, i.e. below half a bf16 ulp of the result for |x| > 1e-4 and
+// negligible against the signal below that
 __device__ __forceinline__ float elu_call(float x) {
-  const float small = x * fmaf(x, fmaf(x, fmaf(x, fmaf(x, 0.0083333333f, 0.041666667f), 0.16666667f), 0.5f), 1.0f);
-  const float big = __expf(x) - 1.0f;
-  return x > 0.0f ? x : (x > -0.125f ? small : big);
+  const float e = ex2_ftz(1.4426950408889634f * x);
+  return x > 0.0f ? x : e - 1.0f;
 }
 template <int CH> __device__ __forceinline__ void act_inplace(float* v, int act) {
   if (act == ACT_NONE) return;
