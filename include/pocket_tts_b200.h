@@ -91,6 +91,14 @@ int ptts_stream_close(ptts_engine* e, int32_t slot);
 int ptts_stream_reset_decoder(ptts_engine* e, int32_t slot);
 /* copy.deepcopy(model_state) (tts_model.py:637-638): dst gets src's FlowLM KV prefix+offset. */
 int ptts_stream_fork(ptts_engine* e, int32_t src_slot, int32_t dst_slot);
+/* The same copy.deepcopy(model_state) (tts_model.py:637-638) for many streams of ONE voice, without the copy: dst
+ * reads positions [0, offset(src)) from the slot that owns them (one resident voice prefix per GPU, read by every
+ * stream forked from it) and appends its own text / frame positions behind them.  The owner must stay open until every
+ * dependent is closed (ptts_stream_close on it returns PTTS_ESTATE before that) and may itself keep appending.
+ * A dependent that has not appended yet can be shared onward (the owner is shared instead); after it has,
+ * ptts_stream_fork makes a deep copy.  Export / fork of a dependent read through the sharing; ptts_stream_import_kv
+ * into a dependent returns PTTS_ESTATE.  (prefix sharing, zero-copy stream_fork.) */
+int ptts_stream_fork_shared(ptts_engine* e, int32_t src_slot, int32_t dst_slot);
 /* model_state import/export in the reference layout cache[2, 1, P, H, D] per layer
  * (transformer.py:46-57, tts_model.py:1047-1072). */
 int ptts_stream_import_kv(ptts_engine* e, int32_t slot, int32_t layer, const float* cache_any,

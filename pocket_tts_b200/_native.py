@@ -55,6 +55,7 @@ def load_library() -> C.CDLL:
         "ptts_stream_close": (C.c_int, [p, i32]),
         "ptts_stream_reset_decoder": (C.c_int, [p, i32]),
         "ptts_stream_fork": (C.c_int, [p, i32, i32]),
+        "ptts_stream_fork_shared": (C.c_int, [p, i32, i32]),
         "ptts_stream_import_kv": (C.c_int, [p, i32, i32, f32p, i32]),
         "ptts_stream_export_kv": (C.c_int, [p, i32, i32, f32p, i32]),
         "ptts_stream_set_offset": (C.c_int, [p, i32, i32]),

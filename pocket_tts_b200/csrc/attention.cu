@@ -21,6 +21,16 @@ __device__ __forceinline__ TK* kv_row(const KvGeom& g, int layer, int slot, int 
   return reinterpret_cast<TK*>(g.base) + idx * g.D;
 }
 
+// shared voice prefix of `slot`: rows [0, plen) live `delta` elements away (in the prefix owner's cache, same layout)
+__device__ __forceinline__ long long pfx_delta(const KvGeom& g, int slot, int& plen) {
+  plen = 0;
+  if (!g.pfx_slot) return 0;
+  const int ps = g.pfx_slot[slot];
+  if (ps < 0) return 0;
+  plen = g.pfx_len[slot];
+  return (long long)(ps - slot) * 2 * g.H * g.cap * g.D;
+}
+
 __device__ __forceinline__ float2 rope_pair(float2 x, float pos, float freq) {
   // rope.py:42-50: angle = freq * position in fp32; (r, i) -> (r cos - i sin, r sin + i cos)
   float s, c;
@@ -38,13 +48,14 @@ struct OnlineSm {
 template <typename TK>
 __device__ __forceinline__ void attend4(OnlineSm& s, const TK* __restrict__ kbase,
                                         const TK* __restrict__ vbase, int idx0, int count,
-                                        float2 q, float scale, int lane) {
+                                        float2 q, float scale, int lane, int plen = 0, long long dsh = 0) {
   float2 kk[4], vv[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     if (j < count) {
-      kk[j] = load2(kbase + (long long)(idx0 + j) * 64 + 2 * lane);
-      vv[j] = load2(vbase + (long long)(idx0 + j) * 64 + 2 * lane);
+      const long long o = (long long)(idx0 + j) * 64 + 2 * lane + (idx0 + j < plen ? dsh : 0);
+      kk[j] = load2(kbase + o);
+      vv[j] = load2(vbase + o);
     } else {
       kk[j] = make_float2(0.f, 0.f);
       vv[j] = make_float2(0.f, 0.f);
@@ -132,7 +143,7 @@ template <> struct KvVec<float> {
   __device__ static void store(float* p, const float* f) { *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]); }
 };
 
-template <typename TK, typename TO, int U>   // U: 16-byte loads of K and of V in flight per lane (rows stay packed in registers)
+template <typename TK, typename TO, int U, bool SH = false>   // U: 16-byte loads of K and of V in flight per lane (rows stay packed in registers); SH: some stream reads a shared voice prefix
 __global__ void __launch_bounds__(128)   // bf16: U = 6 -> 72 registers, 7 CTAs per SM; U = 4 -> 56; U = 8 -> 80
 attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs,
                    const int* __restrict__ offsets, const int* __restrict__ slot_ids, KvGeom g,
@@ -150,15 +161,18 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int sub = lane / LPR, ch = lane % LPR;   // row within a load, 16-byte chunk of the row
   const int d_model = g.H * 64;
+  int plen = 0;
+  const long long dsh = SH ? pfx_delta(g, slot, plen) : 0;
   if (g.prefetch) {
     // The cached positions [0, pos) were written by earlier steps, not by the kernel this one waits for: pull
     // them into L2 now, while the QKV projection (latency-bound, HBM nearly idle) is still running.
     const char* kb = reinterpret_cast<const char*>(kv_row<TK>(g, layer, slot, 0, h, 0));
     const char* vb = reinterpret_cast<const char*>(kv_row<TK>(g, layer, slot, 1, h, 0));
-    const int bytes = pos * 64 * (int)sizeof(TK);
+    const int bytes = pos * 64 * (int)sizeof(TK), pbytes = plen * 64 * (int)sizeof(TK);
     for (int off = threadIdx.x * 128; off < bytes; off += 128 * 128) {
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(kb + off));
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(vb + off));
+      const long long sh = (SH && off < pbytes) ? dsh * (long long)sizeof(TK) : 0;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(kb + off + sh));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(vb + off + sh));
     }
   }
   const unsigned tl = tl_begin(2);
@@ -202,8 +216,9 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
     for (int u = 0; u < U; ++u) {
       const int p = p0 + u * RPL + sub;
       if (p < L) {
-        kr[u] = KvVec<TK>::load_raw(kbase + (long long)p * 64);
-        vr[u] = KvVec<TK>::load_raw(vbase + (long long)p * 64);
+        const long long o = (long long)p * 64 + ((SH && p < plen) ? dsh : 0);
+        kr[u] = KvVec<TK>::load_raw(kbase + o);
+        vr[u] = KvVec<TK>::load_raw(vbase + o);
       } else {
         kr[u] = KvVec<TK>::zero(); vr[u] = KvVec<TK>::zero();
       }
@@ -491,6 +506,18 @@ cudaError_t launch_attn_decode(const float* qkv, const float* rope_freqs, const 
                                const int* slot_ids, KvGeom kv, int layer, void* out, int out_type,
                                int n, cudaStream_t st) {
   if (kv.D != 64) return cudaErrorInvalidValue;
+  if (kv.pfx_slot) {   // some stream of the batch reads a shared voice prefix: per-lane form with the row select
+    dim3 grid(kv.H, n);
+    if (kv.type == 0 && out_type == 0)
+      launch_k(attn_decode_kernel<float, float, 6, true>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out);
+    else if (kv.type == 1 && out_type == 1)
+      launch_k(attn_decode_kernel<bf16, bf16, 6, true>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+    else if (kv.type == 0 && out_type == 1)
+      launch_k(attn_decode_kernel<float, bf16, 6, true>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+    else
+      return cudaErrorInvalidValue;
+    return cudaGetLastError();
+  }
   if (kv.prefetch == 2 && !kv.ring) {
     if (kv.type == 0 && out_type == 0) return launch_attn_decode_bulk<float, float>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (float*)out, n, st);
     if (kv.type == 1 && out_type == 1) return launch_attn_decode_bulk<bf16, bf16>(qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out, n, st);
@@ -553,6 +580,8 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
 
   const TK* kbase = kv_row<TK>(g, layer, slot, 0, h, 0);
   const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0);
+  int plen = 0;
+  const long long dsh = pfx_delta(g, slot, plen);   // shared voice prefix (never with ring storage)
   const int t_first = mode == 2 ? (int)blockIdx.z * NW + w : w;
   const int t_step = mode == 2 ? T : NW;        // mode 2: exactly one query per warp
   for (int t = t_first; t < T; t += t_step) {
@@ -573,7 +602,7 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
           attend4<TK>(s, kbase, vbase, i0, cnt, q, 0.125f, lane);
         }
       } else {
-        attend4<TK>(s, kbase, vbase, p0, cnt, q, 0.125f, lane);
+        attend4<TK>(s, kbase, vbase, p0, cnt, q, 0.125f, lane, plen, dsh);
       }
     }
     const float inv = 1.0f / s.l;
@@ -822,6 +851,23 @@ __global__ void kv_import_kernel(const float* __restrict__ ref, KvGeom g, int la
     kv_row<TK>(g, layer, slot, kv, h, p)[d] = from_f<TK>(ref[idx]);
   }
 }
+// positions [p0, p1) of `slot` -> rows [p0, p1) of ref [2, P, H, D]
+template <typename TK>
+__global__ void kv_export_range_kernel(float* __restrict__ ref, KvGeom g, int layer, int slot, int P, int p0, int p1) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int np = p1 - p0;
+  const long long total = 2LL * np * g.H * g.D;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int d = (int)(idx % g.D);
+    long long r = idx / g.D;
+    const int h = (int)(r % g.H); r /= g.H;
+    const int p = p0 + (int)(r % np);
+    const int kv = (int)(r / np);
+    ref[(((long long)kv * P + p) * g.H + h) * g.D + d] = to_f(kv_row<TK>(g, layer, slot, kv, h, p)[d]);
+  }
+}
 template <typename TK>
 __global__ void kv_export_kernel(float* __restrict__ ref, KvGeom g, int layer, int slot, int P) {
   pdl_launch_dependents();
@@ -838,15 +884,15 @@ __global__ void kv_export_kernel(float* __restrict__ ref, KvGeom g, int layer, i
   }
 }
 template <typename TK>
-__global__ void kv_fork_kernel(KvGeom g, int n_layers, int src, int dst, int P) {
+__global__ void kv_fork_kernel(KvGeom g, int n_layers, int src, int dst, int p0, int P) {
   pdl_launch_dependents();
   pdl_wait();
-  // copy positions [0,P) of every (layer, kv, head): P*D contiguous elements each
+  // copy positions [p0,P) of every (layer, kv, head): (P - p0)*D contiguous elements each
   const int seg = blockIdx.x;  // layer*2*H + kv*H + h
   const int h = seg % g.H, kv = (seg / g.H) % 2, layer = seg / (2 * g.H);
-  const TK* s = kv_row<TK>(g, layer, src, kv, h, 0);
-  TK* d = kv_row<TK>(g, layer, dst, kv, h, 0);
-  const int total = P * g.D;
+  const TK* s = kv_row<TK>(g, layer, src, kv, h, p0);
+  TK* d = kv_row<TK>(g, layer, dst, kv, h, p0);
+  const int total = (P - p0) * g.D;
   for (int idx = threadIdx.x * 4; idx < total; idx += blockDim.x * 4) store4(d + idx, load4(s + idx));
 }
 
@@ -864,11 +910,27 @@ cudaError_t launch_kv_export(float* ref, KvGeom kv, int layer, int slot, int P, 
   else launch_k(kv_export_kernel<bf16>, blocks, 256, 0, st, ref, kv, layer, slot, P);
   return cudaGetLastError();
 }
+cudaError_t launch_kv_export_range(float* ref, KvGeom kv, int layer, int slot, int P, int p0, int p1, cudaStream_t st) {
+  if (p1 <= p0) return cudaSuccess;
+  const int blocks = (int)min(1024LL, (2LL * (p1 - p0) * kv.H * kv.D + 255) / 256);
+  if (kv.type == 0) launch_k(kv_export_range_kernel<float>, blocks, 256, 0, st, ref, kv, layer, slot, P, p0, p1);
+  else launch_k(kv_export_range_kernel<bf16>, blocks, 256, 0, st, ref, kv, layer, slot, P, p0, p1);
+  return cudaGetLastError();
+}
+// positions [p0, p1) of every (layer, k|v, head) of src -> dst
+cudaError_t launch_kv_fork_range(KvGeom kv, int n_layers, int src, int dst, int p0, int p1, cudaStream_t st);
 cudaError_t launch_kv_fork(KvGeom kv, int n_layers, int src, int dst, int P, cudaStream_t st) {
   if (P <= 0) return cudaSuccess;
   const int blocks = n_layers * 2 * kv.H;
-  if (kv.type == 0) launch_k(kv_fork_kernel<float>, blocks, 256, 0, st, kv, n_layers, src, dst, P);
-  else launch_k(kv_fork_kernel<bf16>, blocks, 256, 0, st, kv, n_layers, src, dst, P);
+  if (kv.type == 0) launch_k(kv_fork_kernel<float>, blocks, 256, 0, st, kv, n_layers, src, dst, 0, P);
+  else launch_k(kv_fork_kernel<bf16>, blocks, 256, 0, st, kv, n_layers, src, dst, 0, P);
+  return cudaGetLastError();
+}
+cudaError_t launch_kv_fork_range(KvGeom kv, int n_layers, int src, int dst, int p0, int p1, cudaStream_t st) {
+  if (p1 <= p0) return cudaSuccess;
+  const int blocks = n_layers * 2 * kv.H;
+  if (kv.type == 0) launch_k(kv_fork_kernel<float>, blocks, 256, 0, st, kv, n_layers, src, dst, p0, p1);
+  else launch_k(kv_fork_kernel<bf16>, blocks, 256, 0, st, kv, n_layers, src, dst, p0, p1);
   return cudaGetLastError();
 }
 

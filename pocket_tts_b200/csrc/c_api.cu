@@ -91,6 +91,9 @@ int ptts_stream_reset_decoder(ptts_engine* e, int32_t slot) {
 int ptts_stream_fork(ptts_engine* e, int32_t src, int32_t dst) {
   API_BEGIN NEED(e) return e->impl->stream_fork(src, dst); API_END
 }
+int ptts_stream_fork_shared(ptts_engine* e, int32_t src_slot, int32_t dst_slot) {
+  API_BEGIN NEED(e) return e->impl->stream_fork_shared(src_slot, dst_slot); API_END
+}
 int ptts_stream_import_kv(ptts_engine* e, int32_t slot, int32_t layer, const float* cache_any, int32_t n_positions) {
   API_BEGIN NEED(e)
   if (!cache_any && n_positions > 0) { ptts::set_error("null cache"); return PTTS_EINVAL; }

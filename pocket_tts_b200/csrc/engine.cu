@@ -201,6 +201,13 @@ int Engine::init() {
     PTTS_FAIL(PTTS_ECUDA, "out of device memory for stream state");
   host_offsets.assign(S, 0);
   host_mimi_offsets.assign(S, 0);
+  host_pfx_slot.assign(S, -1);
+  host_pfx_len.assign(S, 0);
+  pfx_refs.assign(S, 0);
+  d_pfx_slot = dmalloc<int>(allocs, S, stream);
+  d_pfx_len = dmalloc<int>(allocs, S, stream);
+  if (!d_pfx_slot || !d_pfx_len) PTTS_FAIL(PTTS_ECUDA, "out of device memory for stream state");
+  PTTS_CUDA_CHECK(cudaMemsetAsync(d_pfx_slot, 0xff, S * sizeof(int), stream));
   slot_used.assign(S, 0);
 
   // ---- per-batch buffers

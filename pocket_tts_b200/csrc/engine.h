@@ -90,7 +90,9 @@ bool make_sm_partition(int device, int flow_sms, int prio_flow, int prio_mimi, c
 struct GraphKey {
   int n, lsd, audio;
   int mode = 0;   // 0: sequential frame; 8 + parity*4 + do_flow*2 + do_mimi: pipelined frame
+  int shared = 0; // 1: captured with the shared-prefix attention kernels (KvGeom pointers are baked into the nodes)
   bool operator<(const GraphKey& o) const {
+    if (shared != o.shared) return shared < o.shared;
     if (n != o.n) return n < o.n;
     if (lsd != o.lsd) return lsd < o.lsd;
     if (audio != o.audio) return audio < o.audio;
@@ -114,6 +116,7 @@ class Engine {
   int stream_close(int slot);
   int stream_reset_decoder(int slot);
   int stream_fork(int src, int dst);
+  int stream_fork_shared(int src, int dst);
   int import_kv(int slot, int layer, const float* cache_any, int P);
   int export_kv(int slot, int layer, float* cache_any, int P);
   int set_offset(int slot, int off);
@@ -227,6 +230,13 @@ class Engine {
   float* e_prev = nullptr;                           // device [slots, mimi_d]
   void* hist_state[PTTS_MAX_HIST] = {};
   std::vector<int> host_offsets, host_mimi_offsets;
+  // shared voice prefixes (stream_fork_shared): per slot the owner of positions [0, pfx_len) or -1, and how many live
+  // slots read a slot's prefix; mirrored on the device for the attention kernels
+  std::vector<int> host_pfx_slot, host_pfx_len, pfx_refs;
+  int *d_pfx_slot = nullptr, *d_pfx_len = nullptr;
+  bool batch_shared = false;                 // some slot of the current batch (cur_slots) reads a shared prefix
+  KvGeom flow_kv() const { KvGeom g = kv_flow; if (batch_shared) { g.pfx_slot = d_pfx_slot; g.pfx_len = d_pfx_len; } return g; }
+  int unshare(int slot);
   std::vector<char> slot_used;
 
   // per-batch buffers

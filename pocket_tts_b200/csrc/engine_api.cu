@@ -23,7 +23,7 @@ int Engine::stream_open(int* slot) {
       *slot = s;
       host_offsets[s] = 0;
       PTTS_CUDA_CHECK(cudaMemsetAsync(offsets + s, 0, sizeof(int), stream));
-      return stream_reset_decoder(s);
+      return stream_reset_decoder(s);   // host_pfx_slot[s] is -1 here (stream_close / init)
     }
   PTTS_FAIL(PTTS_ENOSLOT, "all %d stream slots in use", cfg.max_streams);
 }
@@ -31,7 +31,55 @@ int Engine::stream_open(int* slot) {
 int Engine::stream_close(int slot) {
   NEED_READY();
   CHECK_SLOT(slot);
+  if (pfx_refs[slot] > 0)
+    PTTS_FAIL(PTTS_ESTATE, "slot %d holds the shared voice prefix of %d live stream(s): close them first", slot, pfx_refs[slot]);
+  int rc;
+  if ((rc = unshare(slot)) != PTTS_OK) return rc;
   slot_used[slot] = 0;
+  return PTTS_OK;
+}
+
+// drop the slot's reference to a shared prefix (its own rows [0, pfx_len) are NOT filled in: callers that keep the
+// slot alive copy them first)
+int Engine::unshare(int slot) {
+  if (host_pfx_slot[slot] < 0) return PTTS_OK;
+  --pfx_refs[host_pfx_slot[slot]];
+  host_pfx_slot[slot] = -1;
+  host_pfx_len[slot] = 0;
+  PTTS_CUDA_CHECK(cudaMemsetAsync(d_pfx_slot + slot, 0xff, sizeof(int), stream));
+  cur_slots.clear();   // batch_shared is recomputed by the next upload_slots
+  return PTTS_OK;
+}
+
+// copy.deepcopy(model_state) without the copy (tts_model.py:637-638 for many streams of one voice): dst reads the
+// positions [0, offset(src)) from the slot that owns them and appends its own positions behind; the owner must stay
+// open (and may keep appending: dependents never read past their pfx_len) until every dependent is closed.
+int Engine::stream_fork_shared(int src, int dst) {
+  NEED_READY();
+  CHECK_SLOT(src);
+  CHECK_SLOT(dst);
+  if (src == dst) PTTS_FAIL(PTTS_EINVAL, "fork_shared: source and destination are the same slot");
+  if (pfx_refs[dst] > 0) PTTS_FAIL(PTTS_ESTATE, "fork_shared: slot %d is itself a shared prefix", dst);
+  int owner = src;
+  const int P = host_offsets[src];
+  if (host_pfx_slot[src] >= 0) {
+    // a dependent can be shared onward only while it has appended nothing of its own
+    if (P != host_pfx_len[src]) PTTS_FAIL(PTTS_ESTATE, "fork_shared: slot %d already appended to its shared prefix; use ptts_stream_fork", src);
+    owner = host_pfx_slot[src];
+  }
+  int rc;
+  if ((rc = unshare(dst)) != PTTS_OK) return rc;
+  host_pfx_slot[dst] = owner;
+  host_pfx_len[dst] = P;
+  ++pfx_refs[owner];
+  host_offsets[dst] = P;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(offsets + dst, offsets + src, sizeof(int), cudaMemcpyDeviceToDevice, stream));
+  int* hp = reinterpret_cast<int*>(h_pinned) + 3 * cfg.max_streams;
+  hp[0] = owner; hp[1] = P;
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(d_pfx_slot + dst, hp, sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaMemcpyAsync(d_pfx_len + dst, hp + 1, sizeof(int), cudaMemcpyHostToDevice, stream));
+  PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));   // h_pinned is reused
+  cur_slots.clear();
   return PTTS_OK;
 }
 
@@ -55,8 +103,18 @@ int Engine::stream_fork(int src, int dst) {
   CHECK_SLOT(src);
   CHECK_SLOT(dst);
   if (src == dst) return PTTS_OK;
+  if (pfx_refs[dst] > 0) PTTS_FAIL(PTTS_ESTATE, "fork: slot %d holds a shared prefix in use", dst);
   const int P = host_offsets[src];
-  PTTS_CUDA_CHECK(launch_kv_fork(kv_flow, cfg.n_layers, src, dst, P, stream));
+  int rc;
+  if ((rc = unshare(dst)) != PTTS_OK) return rc;
+  if (host_pfx_slot[src] >= 0) {   // deep copy of a sharing slot: the prefix rows from their owner, the rest from src
+    const int pl = std::min(P, host_pfx_len[src]);
+    PTTS_CUDA_CHECK(launch_kv_fork_range(kv_flow, cfg.n_layers, host_pfx_slot[src], dst, 0, pl, stream));
+    PTTS_CUDA_CHECK(launch_kv_fork_range(kv_flow, cfg.n_layers, src, dst, pl, P, stream));
+    ++launches;
+  } else {
+    PTTS_CUDA_CHECK(launch_kv_fork(kv_flow, cfg.n_layers, src, dst, P, stream));
+  }
   ++launches;
   host_offsets[dst] = P;
   PTTS_CUDA_CHECK(cudaMemcpyAsync(offsets + dst, offsets + src, sizeof(int), cudaMemcpyDeviceToDevice, stream));
@@ -69,6 +127,7 @@ int Engine::import_kv(int slot, int layer, const float* cache_any, int P) {
   if (layer < 0 || layer >= cfg.n_layers || P < 0 || P > cfg.kv_capacity)
     PTTS_FAIL(PTTS_EINVAL, "import_kv: layer %d / positions %d out of range", layer, P);
   if (P == 0) return PTTS_OK;
+  if (host_pfx_slot[slot] >= 0) PTTS_FAIL(PTTS_ESTATE, "import_kv: slot %d reads a shared prefix (fork it with ptts_stream_fork first)", slot);
   const size_t elems = 2ull * P * cfg.d_model;
   float* tmp = nullptr;
   PTTS_CUDA_CHECK(cudaMallocAsync((void**)&tmp, elems * sizeof(float), stream));
@@ -88,7 +147,13 @@ int Engine::export_kv(int slot, int layer, float* cache_any, int P) {
   const size_t elems = 2ull * P * cfg.d_model;
   float* tmp = nullptr;
   PTTS_CUDA_CHECK(cudaMallocAsync((void**)&tmp, elems * sizeof(float), stream));
-  PTTS_CUDA_CHECK(launch_kv_export(tmp, kv_flow, layer, slot, P, stream));
+  if (host_pfx_slot[slot] >= 0) {
+    const int pl = std::min(P, host_pfx_len[slot]);
+    PTTS_CUDA_CHECK(launch_kv_export_range(tmp, kv_flow, layer, host_pfx_slot[slot], P, 0, pl, stream));
+    PTTS_CUDA_CHECK(launch_kv_export_range(tmp, kv_flow, layer, slot, P, pl, P, stream));
+  } else {
+    PTTS_CUDA_CHECK(launch_kv_export(tmp, kv_flow, layer, slot, P, stream));
+  }
   PTTS_CUDA_CHECK(cudaMemcpyAsync(cache_any, tmp, elems * sizeof(float), cudaMemcpyDefault, stream));
   PTTS_CUDA_CHECK(cudaFreeAsync(tmp, stream));
   PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
@@ -99,6 +164,8 @@ int Engine::set_offset(int slot, int off) {
   NEED_READY();
   CHECK_SLOT(slot);
   if (off < 0 || off > cfg.kv_capacity) PTTS_FAIL(PTTS_EINVAL, "offset %d out of range", off);
+  if (host_pfx_slot[slot] >= 0 && off < host_pfx_len[slot])
+    PTTS_FAIL(PTTS_ESTATE, "offset %d lies inside the shared prefix of slot %d (%d positions)", off, slot, host_pfx_len[slot]);
   host_offsets[slot] = off;
   PTTS_CUDA_CHECK(cudaMemcpyAsync(offsets + slot, &host_offsets[slot], sizeof(int), cudaMemcpyHostToDevice, stream));
   PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));
@@ -152,6 +219,8 @@ int Engine::upload_slots(int n, const int* slots) {
   PTTS_CUDA_CHECK(cudaMemcpyAsync(d_mimi_lens, hp + 2 * S, S * sizeof(int), cudaMemcpyHostToDevice, stream));
   PTTS_CUDA_CHECK(cudaStreamSynchronize(stream));  // h_pinned is reused
   cur_slots.assign(slots, slots + n);
+  batch_shared = false;
+  for (int i = 0; i < n; ++i) batch_shared = batch_shared || host_pfx_slot[slots[i]] >= 0;
   return PTTS_OK;
 }
 
@@ -247,6 +316,7 @@ int Engine::frame(int n, int lsd, int audio) {
     return PTTS_OK;
   }
   GraphKey key{n, lsd, audio};
+  key.shared = batch_shared ? 1 : 0;
   auto it = graphs.find(key);
   if (it == graphs.end()) {
     const long long before = launches;
@@ -274,8 +344,10 @@ int Engine::frame(int n, int lsd, int audio) {
 // that is a DIFFERENT executable graph, and graphs of more than ~110 nodes lose that overlap.  So the loop launches
 // one ~70-node FlowLM graph per frame (executables alternate by frame slot and group parity) and one Mimi graph per
 // group of frames, ordered with events instead of intra-graph forks.
-int Engine::launch_captured(const GraphKey& key, cudaStream_t on, const std::function<int()>& body) {
+int Engine::launch_captured(const GraphKey& key_in, cudaStream_t on, const std::function<int()>& body) {
   if (!use_graphs) return body();
+  GraphKey key = key_in;
+  key.shared = batch_shared ? 1 : 0;
   auto it = graphs.find(key);
   if (it == graphs.end()) {
     const long long before = launches;

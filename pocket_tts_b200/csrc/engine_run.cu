@@ -99,9 +99,9 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
     LAUNCH("mimi.attn", launch_attn_window(qkvb, rope_freqs, mimi_offsets, d_slot_ids, kv_mimi, li, cfg.mimi_context,
                                            cfg.upsample_stride, ao, act_type, n, stream, rows / (n * cfg.upsample_stride)));
   } else if (rows == n) {
-    LAUNCH("flow.attn_decode", launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, kv_flow, li, ao, act_type, n, stream));
+    LAUNCH("flow.attn_decode", launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, flow_kv(), li, ao, act_type, n, stream));
   } else {
-    LAUNCH("flow.attn_prefill", launch_attn_chunk(qkvb, rope_freqs, offsets, d_slot_ids, d_row_start, d_lens, kv_flow, li,
+    LAUNCH("flow.attn_prefill", launch_attn_chunk(qkvb, rope_freqs, offsets, d_slot_ids, d_row_start, d_lens, flow_kv(), li,
                              INT_MAX / 2, ao, act_type, n, stream, prefill_max_len));
   }
   {
@@ -141,7 +141,7 @@ int Engine::flow_layer_decode_folded(int l, int n) {
     ep.ln_part_in = ln_part; ep.ln_nparts = np; ep.ln_c1 = L.qkv_c1; ep.ln_c2 = L.qkv_c2;
     if ((rc = gemm("flow.qkv", h16, true, plain(d), L.in_proj_ln, n, ep, false, &pf)) != PTTS_OK) return rc;
   }
-  LAUNCH("flow.attn_decode", launch_attn_decode(qkv, rope_freqs, offsets, d_slot_ids, kv_flow, l, attn_o, act_type, n, stream));
+  LAUNCH("flow.attn_decode", launch_attn_decode(qkv, rope_freqs, offsets, d_slot_ids, flow_kv(), l, attn_o, act_type, n, stream));
   {
     GemmEpilogue ep; ep.out = h; ep.out_map = plain(d); ep.res = h; ep.res_map = plain(d);
     ep.ln_raw = h16; ep.ln_part_out = ln_part;

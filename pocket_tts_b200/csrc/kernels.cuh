@@ -15,6 +15,11 @@ struct KvGeom {
   int type;        // 0 float, 1 bf16
   int ring;        // 1: pos stored at pos & (cap-1) (Mimi sliding window), 0: linear
   int prefetch;    // decode attention form (PTTS_ATTN): 0 per-lane loads, 1 + L2 prefetch before the producer wait, 2 bulk-copy kernel
+  // Shared voice prefix (ptts_stream_fork_shared): positions [0, pfx_len[slot]) of a slot with pfx_slot[slot] >= 0 are
+  // read from that slot's cache at the same position index (one resident copy of the voice K/V for every stream forked
+  // from it); nullptr: no stream of the launch shares a prefix.
+  const int* pfx_slot = nullptr;
+  const int* pfx_len = nullptr;
 };
 
 // h[i,:] = input_linear(where(isnan(prev), bos, prev))            flow_lm.py:121-122
@@ -170,5 +175,7 @@ cudaError_t launch_kv_import(const float* ref /*[2,P,H,D]*/, KvGeom kv, int laye
                              cudaStream_t st);
 cudaError_t launch_kv_export(float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st);
 cudaError_t launch_kv_fork(KvGeom kv, int n_layers, int src, int dst, int P, cudaStream_t st);
+cudaError_t launch_kv_export_range(float* ref, KvGeom kv, int layer, int slot, int P, int p0, int p1, cudaStream_t st);
+cudaError_t launch_kv_fork_range(KvGeom kv, int n_layers, int src, int dst, int p0, int p1, cudaStream_t st);
 
 }  // namespace ptts

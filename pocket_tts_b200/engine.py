@@ -154,6 +154,11 @@ class GenerationEngine:
     def fork(self, src: int, dst: int) -> None:
         N.check(self.lib.ptts_stream_fork(self._h, src, dst))
 
+    def fork_shared(self, src: int, dst: int) -> None:
+        """Zero-copy fork: `dst` reads `src`'s positions from their owner's cache (one resident voice prefix for every
+        stream of that voice) and appends behind them; `src` (or its owner) must outlive `dst`."""
+        N.check(self.lib.ptts_stream_fork_shared(self._h, src, dst))
+
     def offset(self, slot: int) -> int:
         o = C.c_int32(0)
         N.check(self.lib.ptts_stream_get_offset(self._h, slot, C.byref(o)))

@@ -60,6 +60,13 @@ def import_model_state(source, device="cpu") -> dict:
     return out
 
 
+class VoiceState(dict):
+    """A model_state dict in the reference format (what get_state_for_audio_prompt returns and generate_audio takes)
+    that also remembers the engine slot holding the same K/V on the device, so that every generation from this voice
+    forks that resident prefix (ptts_stream_fork_shared) instead of uploading the cache again."""
+    resident = None   # (engine token, slot) or None
+
+
 def _state_offset(model_state: dict) -> int:
     """tts_model.py:423-431."""
     for st in model_state.values():
@@ -115,6 +122,9 @@ class TTSModel:
         # voice cloning = the Mimi encoder side is in the state_dict (tts_model.py:871-872) -> ptts_encode_audio
         self.has_voice_cloning = self.engine.has_encoder or audio_encoder is not None
         self._outs: dict = {}
+        # voice prefixes kept resident on the device: slot -> True, oldest first
+        self._resident: dict = {}
+        self.max_resident_voices = max(1, min(8, max_streams // 8))
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -281,12 +291,39 @@ class TTSModel:
         if self.cfg.insert_bos_before_voice and self._bos_before_voice is not None:
             prompt = torch.cat([self._bos_before_voice, prompt], dim=0)
         slot = self.engine.open_stream()
+        keep = False
         try:
             self.engine.prefill([slot], [prompt])
             self._draw_noise(1)  # the reference evaluates (and discards) a flow-head sample here: same RNG use
-            return self.engine.export_state(slot)
+            state = VoiceState(self.engine.export_state(slot))
+            keep = self._make_room_for_voice()
+            if keep:
+                self._resident[slot] = True
+                state.resident = (id(self.engine), slot)
+            return state
         finally:
-            self.engine.close_stream(slot)
+            if not keep:
+                self.engine.close_stream(slot)
+
+    def _make_room_for_voice(self) -> bool:
+        """Evict the oldest resident voice prefixes that no live stream reads until one more fits."""
+        from . import _native as N
+
+        for slot in list(self._resident):
+            if len(self._resident) < self.max_resident_voices:
+                break
+            try:
+                self.engine.close_stream(slot)
+                del self._resident[slot]
+            except N.NativeError:      # still the prefix of live streams
+                continue
+        return len(self._resident) < self.max_resident_voices
+
+    def _resident_slot(self, model_state) -> int | None:
+        r = getattr(model_state, "resident", None)
+        if r is not None and r[0] == id(self.engine) and r[1] in self._resident:
+            return r[1]
+        return None
 
     def _read_audio(self, path: Path, truncate: bool) -> torch.Tensor:
         """data/audio.py:23-52 for PCM WAV + resampling to 24 kHz mono (host, scipy)."""
@@ -327,15 +364,21 @@ class TTSModel:
         included), so a seeded run reproduces the reference's noise."""
         jobs = self._jobs_for_text(0, text_to_generate, max_tokens, frames_after_eos)
         eng = self.engine
-        base = eng.open_stream()
+        resident = self._resident_slot(model_state) if copy_state else None
+        base = resident if resident is not None else eng.open_stream()
         work = base
         try:
-            eng.import_state(base, model_state)
+            if resident is None:
+                eng.import_state(base, model_state)
+            elif not copy_state and isinstance(model_state, VoiceState):
+                model_state.resident = None      # about to be mutated in place
             if copy_state:
                 work = eng.open_stream()
             for job in jobs:
                 if copy_state:
-                    eng.fork(base, work)         # copy.deepcopy(model_state), tts_model.py:637-638
+                    # copy.deepcopy(model_state), tts_model.py:637-638 - without the copy: the chunk's stream reads
+                    # the voice prefix from the slot that holds it and appends behind it
+                    eng.fork_shared(base, work)
                 eng.reset_decoder(work)          # fresh Mimi state + BOS, tts_model.py:444,748-753
                 job.slot = work
                 start = eng.offset(work)
@@ -348,10 +391,13 @@ class TTSModel:
                     self._set_offset(work, start + len(job.tokens) + min(steps, job.max_gen_len))
             if not copy_state:
                 self._write_back(model_state, eng.export_state(work))
+                if isinstance(model_state, VoiceState):
+                    model_state.resident = None
         finally:
             if work != base:
                 eng.close_stream(work)
-            eng.close_stream(base)
+            if resident is None:
+                eng.close_stream(base)
 
     def _set_offset(self, slot: int, offset: int) -> None:
         from . import _native as N
@@ -436,15 +482,21 @@ class TTSModel:
             per_request.append(jobs)
             waiting.extend(jobs)
         voices: dict = {}
+        temp_voices: list = []
         active: list = []
         admitted: list = []
         try:
             for st in model_states:          # one resident slot per distinct voice state
                 if id(st) not in voices:
-                    v = eng.open_stream()
-                    voices[id(st)] = v
-                    eng.import_state(v, st)
-            capacity = eng.max_streams - len(voices)
+                    v = self._resident_slot(st)
+                    if v is None:
+                        v = eng.open_stream()
+                        temp_voices.append(v)
+                        voices[id(st)] = v
+                        eng.import_state(v, st)
+                    else:
+                        voices[id(st)] = v
+            capacity = eng.max_streams - len(temp_voices) - len(self._resident)
             if capacity < 1:
                 raise ValueError("no stream slot left for generation: raise max_streams")
             while waiting or active:
@@ -454,7 +506,7 @@ class TTSModel:
                     self._check_capacity(eng.offset(src), job)
                     job.slot = eng.open_stream()
                     admitted.append(waiting.pop(0))      # from here on `finally` closes the slot
-                    eng.fork(src, job.slot)
+                    eng.fork_shared(src, job.slot)       # every chunk of a voice reads one resident prefix
                     eng.reset_decoder(job.slot)
                 if admitted:
                     eng.prefill_tokens([j.slot for j in admitted], [list(j.tokens) for j in admitted])
@@ -484,7 +536,7 @@ class TTSModel:
             for j in active + admitted:
                 if j.slot >= 0:
                     eng.close_stream(j.slot)
-            for v in voices.values():
+            for v in temp_voices:
                 eng.close_stream(v)
         return [torch.cat([p for j in jobs for p in j.pcm]) if any(j.pcm for j in jobs) else torch.zeros(0)
                 for jobs in per_request]

@@ -33,3 +33,16 @@ def test_empty_text_raises():
 def test_max_gen_len_values():
     # tts_model.py:907-910: T=40 -> 192 frames, T=50 -> 234
     assert estimate_max_gen_len(40) == 192 and estimate_max_gen_len(50) == 234
+
+
+def test_public_api_surface_matches_reference_pin():
+    """reference tests/test_python_api.py:8-26: __all__ and the public methods / properties of TTSModel."""
+    import pocket_tts_b200
+    from pocket_tts_b200.tts_model import TTSModel
+
+    assert pocket_tts_b200.__all__ == ["TTSModel", "export_model_state"]
+    assert pocket_tts_b200.TTSModel is TTSModel
+    for name in ("load_model", "generate_audio", "generate_audio_stream", "get_state_for_audio_prompt"):
+        assert callable(getattr(TTSModel, name))
+    for name in ("device", "sample_rate"):
+        assert isinstance(getattr(TTSModel, name), property)
