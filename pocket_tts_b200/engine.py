@@ -88,6 +88,7 @@ class GenerationEngine:
         self.lsd_steps = lsd_steps
         self.max_streams = max_streams
         self.kv_capacity = kv_capacity
+        self.max_prefill_rows = max_prefill_rows
         pc = N.PttsConfig()
         for k in ("n_layers", "d_model", "n_heads", "ffn", "ldim", "flow_dim", "flow_depth", "mimi_d",
                   "mimi_heads", "mimi_layers", "mimi_ffn", "mimi_context", "n_filters", "kernel",

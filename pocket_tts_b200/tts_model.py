@@ -88,6 +88,8 @@ class _Job:
     eos_step: int | None = None
     limit: int | None = None  # frames to emit once EOS is known
     pcm: list = field(default_factory=list)
+    t_admit: float | None = None   # generate_audio_batch: slot opened / first PCM block on the host
+    t_first: float | None = None
 
     def target(self) -> int:
         return self.max_gen_len if self.limit is None else self.limit
@@ -236,6 +238,13 @@ class TTSModel:
                 toks = self._tokens_of(chunk)
                 jobs.append(_Job(request, toks, self._frames_after_eos(chunk, frames_after_eos),
                                  estimate_max_gen_len(len(toks), self.cfg.frame_rate)))
+            return jobs
+        if isinstance(text, (list, tuple)) and text and isinstance(text[0], (list, tuple, torch.Tensor)):
+            # extension: a long text already split into chunks of token ids (one stream per chunk, as the reference
+            # generates sentence chunks one after the other from copies of the voice state, tts_model.py:618-631)
+            jobs = []
+            for chunk in text:
+                jobs.extend(self._jobs_for_text(request, chunk, max_tokens, frames_after_eos))
             return jobs
         toks = [int(t) for t in torch.as_tensor(text).view(-1).tolist()]  # extension: token ids of one chunk
         if not toks:
@@ -459,13 +468,18 @@ class TTSModel:
     @torch.no_grad()
     def generate_audio_batch(self, model_states: Sequence[dict], texts: Sequence, max_tokens: int = MAX_TOKEN_PER_CHUNK,
                              frames_after_eos: int | None = None, noise: Sequence[torch.Tensor] | None = None,
-                             block: int = _BLOCK_MAX) -> list:
+                             block: int = _BLOCK_MAX, frame_limits: Sequence[int] | None = None) -> list:
         """Extension: many independent utterances at once.  Every text chunk of every
         request is one stream; up to `max_streams` streams step together and a finished stream's slot is
         handed to the next waiting chunk after each block of frames (ragged completion).  The caller's
         states are never mutated.  Requests that share a model_state object share one imported voice
         slot.  `noise[i]` ([frames, ldim], single-chunk texts only) injects the draws of request i.
+        `frame_limits[i]` caps the frames of every chunk of request i (synthetic workloads: random-init weights never
+        raise the EOS logit, the cap stands in for it and makes completion ragged).  Per-chunk timings of the call
+        (admission -> first PCM block on the host) are left in `self.last_batch_stats`.
         Returns one 1-D PCM tensor per request."""
+        import time as _time
+
         if len(model_states) != len(texts):
             raise ValueError("model_states and texts differ in length")
         eng, fs = self.engine, self.cfg.frame_samples
@@ -479,12 +493,17 @@ class TTSModel:
                 if noise[r].shape[0] < jobs[0].max_gen_len:
                     raise ValueError(f"noise[{r}] holds {noise[r].shape[0]} frames, {jobs[0].max_gen_len} may be needed")
                 jobs[0].noise = noise[r].float()
+            if frame_limits is not None:
+                for j in jobs:
+                    j.max_gen_len = max(1, min(j.max_gen_len, int(frame_limits[r])))
             per_request.append(jobs)
             waiting.extend(jobs)
         voices: dict = {}
         temp_voices: list = []
         active: list = []
         admitted: list = []
+        t_engine = t_prefill = 0.0
+        t_call = _time.perf_counter()
         try:
             for st in model_states:          # one resident slot per distinct voice state
                 if id(st) not in voices:
@@ -505,26 +524,46 @@ class TTSModel:
                     src = voices[id(model_states[job.request])]
                     self._check_capacity(eng.offset(src), job)
                     job.slot = eng.open_stream()
+                    job.t_admit = _time.perf_counter()
                     admitted.append(waiting.pop(0))      # from here on `finally` closes the slot
                     eng.fork_shared(src, job.slot)       # every chunk of a voice reads one resident prefix
                     eng.reset_decoder(job.slot)
-                if admitted:
-                    eng.prefill_tokens([j.slot for j in admitted], [list(j.tokens) for j in admitted])
-                    active.extend(admitted)
-                    admitted = []
+                while admitted:      # text prefill of the newcomers, in groups that fit the engine's prefill buffers
+                    grp, rows = [], 0
+                    while admitted and (not grp or rows + len(admitted[0].tokens) <= eng.max_prefill_rows):
+                        rows += len(admitted[0].tokens)
+                        grp.append(admitted.pop(0))
+                    try:
+                        _t = _time.perf_counter()
+                        eng.prefill_tokens([j.slot for j in grp], [list(j.tokens) for j in grp])
+                        t_prefill += _time.perf_counter() - _t
+                    finally:
+                        active.extend(grp)   # `finally` of the call closes their slots on error
                 F = max(1, min(block, min(j.max_gen_len - j.done for j in active)))
                 n = len(active)
-                nz = torch.empty(F, n, self.cfg.ldim)
-                for i, j in enumerate(active):
-                    nz[:, i] = j.noise[j.done:j.done + F] if j.noise is not None else self._draw_noise(F)
+                if any(j.noise is not None for j in active):
+                    nz = torch.empty(F, n, self.cfg.ldim)
+                    for i, j in enumerate(active):
+                        nz[:, i] = j.noise[j.done:j.done + F] if j.noise is not None else self._draw_noise(F)
+                else:
+                    nz = self._draw_noise(F * n).view(F, n, self.cfg.ldim)   # one draw for the whole block
+                _t = _time.perf_counter()
                 pcm, _, eos = eng.generate_frames([j.slot for j in active], nz, out=self._buffers(n, F),
                                                   want_latents=False)
+                t_engine += _time.perf_counter() - _t
+                pcm = pcm.clone()                      # one copy out of the reusable pinned buffer; jobs keep views
+                hit = eos > self.eos_threshold         # [F, n]; EOS bookkeeping of tts_model.py:761-764 for the block
+                any_hit, first_hit = hit.any(dim=0).tolist(), hit.to(torch.int8).argmax(dim=0).tolist()
                 still = []
                 for i, j in enumerate(active):
-                    self._update_eos(j, eos[:, i], j.done)
+                    if j.eos_step is None and any_hit[i]:
+                        j.eos_step = j.done + first_hit[i]
+                        j.limit = min(j.max_gen_len, j.eos_step + j.frames_after_eos)
                     upto = min(j.done + F, j.target())
                     if upto > j.done:
-                        j.pcm.append(pcm[i, : (upto - j.done) * fs].clone())
+                        j.pcm.append(pcm[i, : (upto - j.done) * fs])
+                        if j.t_first is None:
+                            j.t_first = _time.perf_counter()
                     j.done += F
                     if j.done >= j.target():
                         eng.close_stream(j.slot)
@@ -538,6 +577,10 @@ class TTSModel:
                     eng.close_stream(j.slot)
             for v in temp_voices:
                 eng.close_stream(v)
+        lat = sorted((j.t_first - j.t_admit) * 1e3 for jobs in per_request for j in jobs if j.t_first is not None)
+        self.last_batch_stats = {"chunks": len(lat), "first_block_ms": lat, "engine_s": t_engine, "prefill_s": t_prefill,
+                                 "total_s": _time.perf_counter() - t_call,
+                                 "frames": sum(min(j.done, j.target()) for jobs in per_request for j in jobs)}
         return [torch.cat([p for j in jobs for p in j.pcm]) if any(j.pcm for j in jobs) else torch.zeros(0)
                 for jobs in per_request]
 
