@@ -88,11 +88,11 @@ def synth_inputs(dims, B, G, seed_base=0):
     return tokens, voice, noise
 
 
-def algorithmic_bytes_per_step(dims, B, ctx_len, e, mimi_tokens):
+def algorithmic_bytes_per_step(dims, B, ctx_len, e, mimi_tokens, kv_e=None):
     """weights once + FlowLM KV read + Mimi KV window + conv state + I/O.  `mimi_tokens` is the
     Mimi decoder's own offset (16 tokens per generated frame), not the FlowLM context."""
     w_elems = 95_582_018 if dims.n_layers == 6 else 322_074_434
-    kv_flow = B * dims.n_layers * 2 * dims.d_model * e * (ctx_len + 1)
+    kv_flow = B * dims.n_layers * 2 * dims.d_model * (kv_e if kv_e is not None else e) * (ctx_len + 1)
     kv_mimi = B * dims.mimi_layers * 2 * dims.mimi_d * e * (min(mimi_tokens, 265) + 16)
     state = B * 2 * 14_720 * e
     io = B * (dims.ldim * 4 + dims.frame_samples * 4)
@@ -110,9 +110,11 @@ def run_ours(args, rank, world, local_rank):
     prec = args.precision
     e_bytes = 2 if prec == "bf16" else 4
     W = po.make_weights(dims, seed=0)
+    kv_dtype = None if args.kv == "act" else args.kv
+    kv_e = (1 + 4 / 64) if kv_dtype == "fp8" else e_bytes      # e4m3 row + its fp32 scale
     eng = GenerationEngine(ModelConfig(n_layers=dims.n_layers), W, max_streams=B,
                            kv_capacity=VOICE_P + TEXT_T + Wm + K + 8, precision=prec, device=local_rank,
-                           max_prefill_rows=B * VOICE_P)
+                           max_prefill_rows=B * VOICE_P, kv_dtype=kv_dtype)
     emb = W["flow_lm.conditioner.embed.weight"]
     bos = W["flow_lm.bos_before_voice"][0]
 
@@ -241,7 +243,7 @@ def run_ours(args, rank, world, local_rank):
             os.environ["PTTS_TIMELINE"] = "1"
             eng2 = GenerationEngine(ModelConfig(n_layers=dims.n_layers), W, max_streams=B,
                                     kv_capacity=VOICE_P + TEXT_T + 40, precision=prec, device=local_rank,
-                                    max_prefill_rows=B * VOICE_P)
+                                    max_prefill_rows=B * VOICE_P, kv_dtype=kv_dtype)
             os.environ.pop("PTTS_TIMELINE", None)
             tokens, voice, noise2 = synth_inputs(dims, B, 24, 7)
             sl2 = [eng2.open_stream() for _ in range(B)]
@@ -259,7 +261,7 @@ def run_ours(args, rank, world, local_rank):
             if costs:
                 costs = costs[len(costs) // 2:]                      # frames 12..23: context 178-189
                 us = statistics.median(costs)
-                per_launch = kernel_algorithmic_bytes("flow.attn_decode", dims, B, VOICE_P + TEXT_T + 18, e_bytes)
+                per_launch = kernel_algorithmic_bytes("flow.attn_decode", dims, B, VOICE_P + TEXT_T + 18, e_bytes, kv_e)
                 in_graph = {"kernel": "flow.attn_decode", "median_us_wait_to_next_wait": round(us, 2), "launches": len(costs),
                             "achieved_GBps": round(per_launch / (us * 1e-6) / 1e9, 1),
                             "method": "globaltimer stamps inside the CUDA-graph loop (PTTS_TIMELINE), FlowLM || Mimi running"}
@@ -289,11 +291,11 @@ def run_ours(args, rank, world, local_rank):
     total_prof = sum(v["total_ms"] for v in prof.values()) or 1.0
     # dominant kernel = the tag with the largest summed event time among those with a byte model (kernel_ms_share)
     ranked = sorted(prof.items(), key=lambda kv: -kv[1]["total_ms"])
-    top = next(((k, v) for k, v in ranked if kernel_algorithmic_bytes(k, dims, B, 200, e_bytes) > 0), (None, None))
+    top = next(((k, v) for k, v in ranked if kernel_algorithmic_bytes(k, dims, B, 200, e_bytes, kv_e) > 0), (None, None))
     roofline = None
     if top[0]:
         ctx_mid = VOICE_P + TEXT_T + Wm + min(K, 32) // 2
-        per_launch = kernel_algorithmic_bytes(top[0], dims, B, ctx_mid, e_bytes)
+        per_launch = kernel_algorithmic_bytes(top[0], dims, B, ctx_mid, e_bytes, kv_e)
         avg_ms = top[1]["total_ms"] / top[1]["count"]
         ach = per_launch / (avg_ms / 1e3) / 1e9
         roofline = {"kernel": top[0], "bound": "hbm", "achieved": round(ach, 1), "peak": hbm_peak,
@@ -304,7 +306,7 @@ def run_ours(args, rank, world, local_rank):
     if in_graph and "achieved_GBps" in in_graph:
         in_graph["frac"] = round(in_graph["achieved_GBps"] / hbm_peak, 4)
     ctx_avg = VOICE_P + TEXT_T + Wm + K / 2
-    step_bytes = algorithmic_bytes_per_step(dims, B, ctx_avg, e_bytes, 16 * (Wm + K / 2))
+    step_bytes = algorithmic_bytes_per_step(dims, B, ctx_avg, e_bytes, 16 * (Wm + K / 2), kv_e)
     step_frac = step_bytes / (ms / K / 1e3) / 1e9 / hbm_peak
 
     cpu = cpu_baseline(dims, W, sample_streams=8, frames=4)
@@ -314,7 +316,7 @@ def run_ours(args, rank, world, local_rank):
         "scaling": "weak", "vs_baseline": None, "dtype": prec, "data": "synthetic",
         "config": {"workload": f"{'default english' if PRESET == 'english' else PRESET} model ({dims.n_layers}L FlowLM), {B} concurrent streams per GPU, "
                                f"voice prefix {VOICE_P} + {TEXT_T} text tokens, lsd_steps 1, frame step = FlowLM + flow head + Mimi decode",
-                   "streams_per_gpu": B, "precision": prec, "parallelism": f"streams sharded x{world}, no collective",
+                   "streams_per_gpu": B, "precision": prec, "kv_cache": kv_dtype or prec, "parallelism": f"streams sharded x{world}, no collective",
                    "l2_policy": "working set per step (weights + KV, >= 0.6 GB) exceeds the 126 MB L2; no flush"},
         "e2e": {"value": round(e2e_value, 1), "unit": "audio-s/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": round(e2e_ms / K, 4),
@@ -346,11 +348,11 @@ def ncu_traffic_bytes(tag, workload):
     return int(sum(vals) / len(vals)) if vals else None
 
 
-def kernel_algorithmic_bytes(tag, dims, B, ctx, e):
+def kernel_algorithmic_bytes(tag, dims, B, ctx, e, kv_e=None):
     """Algorithmic bytes one launch of `tag` must move (DESIGN.md kernel table)."""
     d, ffn = dims.d_model, dims.ffn
     if tag == "flow.attn_decode":
-        return B * 2 * d * e * (ctx + 1) + B * 3 * d * 4 + B * d * e
+        return B * 2 * d * (kv_e if kv_e is not None else e) * (ctx + 1) + B * 3 * d * 4 + B * d * e
     if tag == "head.cluster":     # 12 matrices of 512 x 512 + final 32 x 512 (bf16), input_proj fp32, modulation rows in, latents out
         F = dims.flow_dim
         return (2 * dims.flow_depth * F * F + dims.ldim * F) * e + F * dims.ldim * 4 + B * (3 * dims.flow_depth + 2) * F * 4 + 3 * B * dims.ldim * 4
@@ -613,6 +615,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--kv", default="act", choices=["act", "fp8"],
+                    help="FlowLM KV cache storage: the activation type (default) or FP8 e4m3 with per-row scales (bf16 mode)")
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg5"],
                     help="cfg2: english 6L, 64 streams per GPU (the headline line); cfg3: italian_24l, 256 streams per GPU; "
                          "cfg5: 256 streams per GPU, long texts in 50-token chunks from wav-prompt voices through generate_audio_batch")

@@ -58,6 +58,10 @@ typedef struct ptts_config {
   int32_t max_lsd_steps;  /* rows accepted for the "flow.tcomb" table              */
   int32_t precision;      /* PTTS_PRECISION_*                                      */
   int32_t device;         /* CUDA ordinal                                          */
+  int32_t kv_fp8;         /* 1: FlowLM KV cache stored as FP8 e4m3 with one fp32 scale per cached row (bf16 mode only):
+                           * the low-precision mode of this engine, the analogue of the reference's quantize=True
+                           * (quantization.py:60-88) on the term that bounds the step on a GPU - KV bytes - with its own
+                           * tolerance; 0: cache in the activation type                                    */
 } ptts_config;
 
 typedef struct ptts_engine ptts_engine;

@@ -22,7 +22,7 @@ class PttsConfig(C.Structure):
         [("ratios", C.c_int32 * 3)] + \
         [(n, C.c_int32) for n in (
             "kernel", "res_kernel", "last_kernel", "upsample_stride", "max_streams", "kv_capacity",
-            "max_prefill_rows", "max_lsd_steps", "precision", "device")]
+            "max_prefill_rows", "max_lsd_steps", "precision", "device", "kv_fp8")]
 
 
 class NativeError(RuntimeError):

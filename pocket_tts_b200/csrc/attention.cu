@@ -21,6 +21,15 @@ __device__ __forceinline__ TK* kv_row(const KvGeom& g, int layer, int slot, int 
   return reinterpret_cast<TK*>(g.base) + idx * g.D;
 }
 
+__device__ __forceinline__ float* kv_scale_row(const KvGeom& g, int layer, int slot, int kv, int h, int pos) {
+  const long long idx = ((((long long)layer * g.n_slots + slot) * 2 + kv) * g.H + h) * g.cap + pos;
+  return g.scale + idx;
+}
+template <typename TK> struct IsFp8 { static constexpr bool v = false; };
+template <> struct IsFp8<fp8e4> { static constexpr bool v = true; };
+// e4m3 row scale: amax / 448 (largest finite e4m3), 1 for an all-zero row
+__device__ __forceinline__ float fp8_scale(float amax) { return amax > 0.0f ? amax * (1.0f / 448.0f) : 1.0f; }
+
 // shared voice prefix of `slot`: rows [0, plen) live `delta` elements away (in the prefix owner's cache, same layout)
 __device__ __forceinline__ long long pfx_delta(const KvGeom& g, int slot, int& plen) {
   plen = 0;
@@ -48,7 +57,8 @@ struct OnlineSm {
 template <typename TK>
 __device__ __forceinline__ void attend4(OnlineSm& s, const TK* __restrict__ kbase,
                                         const TK* __restrict__ vbase, int idx0, int count,
-                                        float2 q, float scale, int lane, int plen = 0, long long dsh = 0) {
+                                        float2 q, float scale, int lane, int plen = 0, long long dsh = 0,
+                                        const float* __restrict__ ksbase = nullptr, const float* __restrict__ vsbase = nullptr) {
   float2 kk[4], vv[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -56,6 +66,11 @@ __device__ __forceinline__ void attend4(OnlineSm& s, const TK* __restrict__ kbas
       const long long o = (long long)(idx0 + j) * 64 + 2 * lane + (idx0 + j < plen ? dsh : 0);
       kk[j] = load2(kbase + o);
       vv[j] = load2(vbase + o);
+      if constexpr (IsFp8<TK>::v) {   // FP8 cache: rows carry their scale
+        const long long so = (long long)(idx0 + j) + (idx0 + j < plen ? dsh / 64 : 0);
+        const float ks = ksbase[so], vs = vsbase[so];
+        kk[j].x *= ks; kk[j].y *= ks; vv[j].x *= vs; vv[j].y *= vs;
+      }
     } else {
       kk[j] = make_float2(0.f, 0.f);
       vv[j] = make_float2(0.f, 0.f);
@@ -130,6 +145,31 @@ template <> struct KvVec<bf16> {
     *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
   }
 };
+template <> struct KvVec<fp8e4> {
+  static constexpr int EPL = 16;  // 16 bytes per lane: a 64-wide row is 4 lanes, a warp load covers 8 positions
+  typedef uint4 Raw;
+  __device__ static Raw load_raw(const fp8e4* p) { return *reinterpret_cast<const uint4*>(p); }
+  __device__ static Raw zero() { return make_uint4(0u, 0u, 0u, 0u); }
+  __device__ static void unpack(const Raw& r, float* f) {
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 lo = load2(reinterpret_cast<const fp8e4*>(&w[i]));
+      const float2 hi = load2(reinterpret_cast<const fp8e4*>(&w[i]) + 2);
+      f[4 * i] = lo.x; f[4 * i + 1] = lo.y; f[4 * i + 2] = hi.x; f[4 * i + 3] = hi.y;
+    }
+  }
+  __device__ static void store(fp8e4* p, const float* f) {   // values already divided by the row scale
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const uint32_t lo = __nv_cvt_float2_to_fp8x2(make_float2(f[4 * i], f[4 * i + 1]), __NV_SATFINITE, __NV_E4M3);
+      const uint32_t hi = __nv_cvt_float2_to_fp8x2(make_float2(f[4 * i + 2], f[4 * i + 3]), __NV_SATFINITE, __NV_E4M3);
+      w[i] = lo | (hi << 16);
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
 template <> struct KvVec<float> {
   static constexpr int EPL = 4;
   typedef float4 Raw;
@@ -185,6 +225,10 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   float q[EPL];
   {
     float kx[EPL], vx[EPL];
+    if constexpr (IsFp8<TK>::v) {
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) { kx[e] = 0.0f; vx[e] = 0.0f; }
+    }
 #pragma unroll
     for (int e = 0; e < EPL; e += 2) {
       const float fr = freqs[(ch * EPL + e) >> 1];
@@ -196,7 +240,28 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
         kx[e] = kk.x; kx[e + 1] = kk.y; vx[e] = vv.x; vx[e + 1] = vv.y;
       }
     }
-    if (w == 0 && sub == 0) {
+    if constexpr (IsFp8<TK>::v) {
+      // row scale = amax / 448 over the 64 dims of the row (the LPR lanes of lane group 0 hold them); whole warp 0 runs
+      // the shuffles, lane group 0 stores
+      if (w == 0) {
+        float ka = 0.0f, va = 0.0f;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) { ka = fmaxf(ka, fabsf(kx[e])); va = fmaxf(va, fabsf(vx[e])); }
+#pragma unroll
+        for (int o = 1; o < LPR; o <<= 1) {
+          ka = fmaxf(ka, __shfl_xor_sync(0xffffffffu, ka, o));
+          va = fmaxf(va, __shfl_xor_sync(0xffffffffu, va, o));
+        }
+        if (sub == 0) {
+          const float ks = fp8_scale(ka), vs = fp8_scale(va), kinv = 1.0f / ks, vinv = 1.0f / vs;
+#pragma unroll
+          for (int e = 0; e < EPL; ++e) { kx[e] *= kinv; vx[e] *= vinv; }
+          KvVec<TK>::store(kv_row<TK>(g, layer, slot, 0, h, pos) + ch * EPL, kx);
+          KvVec<TK>::store(kv_row<TK>(g, layer, slot, 1, h, pos) + ch * EPL, vx);
+          if (ch == 0) { *kv_scale_row(g, layer, slot, 0, h, pos) = ks; *kv_scale_row(g, layer, slot, 1, h, pos) = vs; }
+        }
+      }
+    } else if (w == 0 && sub == 0) {
       KvVec<TK>::store(kv_row<TK>(g, layer, slot, 0, h, pos) + ch * EPL, kx);
       KvVec<TK>::store(kv_row<TK>(g, layer, slot, 1, h, pos) + ch * EPL, vx);
     }
@@ -205,6 +270,8 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
 
   const TK* kbase = kv_row<TK>(g, layer, slot, 0, h, 0) + ch * EPL;
   const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0) + ch * EPL;
+  const float* ksbase = IsFp8<TK>::v ? kv_scale_row(g, layer, slot, 0, h, 0) : nullptr;
+  const float* vsbase = IsFp8<TK>::v ? kv_scale_row(g, layer, slot, 1, h, 0) : nullptr;
   const int L = pos + 1;
   float m = -INFINITY, l = 0.0f, acc[EPL];
 #pragma unroll
@@ -212,6 +279,7 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
   constexpr int STEP = NW * U * RPL;   // positions per block iteration
   for (int p0 = w * U * RPL; p0 < L; p0 += STEP) {
     typename KvVec<TK>::Raw kr[U], vr[U];   // rows stay packed until they are used: U loads of K and of V in flight
+    float ksc[IsFp8<TK>::v ? U : 1], vsc[IsFp8<TK>::v ? U : 1];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int p = p0 + u * RPL + sub;
@@ -219,8 +287,13 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
         const long long o = (long long)p * 64 + ((SH && p < plen) ? dsh : 0);
         kr[u] = KvVec<TK>::load_raw(kbase + o);
         vr[u] = KvVec<TK>::load_raw(vbase + o);
+        if constexpr (IsFp8<TK>::v) {
+          const long long so = (long long)p + ((SH && p < plen) ? dsh / 64 : 0);
+          ksc[u] = ksbase[so]; vsc[u] = vsbase[so];
+        }
       } else {
         kr[u] = KvVec<TK>::zero(); vr[u] = KvVec<TK>::zero();
+        if constexpr (IsFp8<TK>::v) { ksc[u] = 0.0f; vsc[u] = 0.0f; }
       }
     }
     float sc[U];
@@ -241,6 +314,7 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
     float mx = m;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
+      if constexpr (IsFp8<TK>::v) sc[u] *= ksc[u];
       if (p0 + u * RPL + sub >= L) sc[u] = -INFINITY;
       mx = fmaxf(mx, sc[u]);
     }
@@ -255,8 +329,9 @@ attn_decode_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
         l += pr;
         float vf[EPL];
         KvVec<TK>::unpack(vr[u], vf);
+        const float pv = IsFp8<TK>::v ? pr * vsc[IsFp8<TK>::v ? u : 0] : pr;
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) acc[e] = fmaf(pr, vf[e], acc[e]);
+        for (int e = 0; e < EPL; ++e) acc[e] = fmaf(pv, vf[e], acc[e]);
       }
       m = mx;
     }
@@ -506,6 +581,13 @@ cudaError_t launch_attn_decode(const float* qkv, const float* rope_freqs, const 
                                const int* slot_ids, KvGeom kv, int layer, void* out, int out_type,
                                int n, cudaStream_t st) {
   if (kv.D != 64) return cudaErrorInvalidValue;
+  if (kv.type == 2) {   // FP8 cache: per-lane form (16 dims per lane), with or without a shared prefix
+    if (out_type != 1 || !kv.scale) return cudaErrorInvalidValue;
+    dim3 grid(kv.H, n);
+    if (kv.pfx_slot) launch_k(attn_decode_kernel<fp8e4, bf16, 4, true>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+    else launch_k(attn_decode_kernel<fp8e4, bf16, 4, false>, grid, 128, 0, st, qkv, rope_freqs, offsets, slot_ids, kv, layer, (bf16*)out);
+    return cudaGetLastError();
+  }
   if (kv.pfx_slot) {   // some stream of the batch reads a shared voice prefix: per-lane form with the row select
     dim3 grid(kv.H, n);
     if (kv.type == 0 && out_type == 0)
@@ -570,8 +652,13 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
     float* row = qkv + (long long)(r0 + t) * 3 * d_model + h * 64 + 2 * lane;
     const float pos = (float)(off + t);
     store2(row, rope_pair(load2(row), pos, fr));
-    const float2 k = rope_pair(load2(row + d_model), pos, fr);
-    const float2 v = load2(row + 2 * d_model);
+    float2 k = rope_pair(load2(row + d_model), pos, fr);
+    float2 v = load2(row + 2 * d_model);
+    if constexpr (IsFp8<TK>::v) {
+      const float ks = fp8_scale(warp_max(fmaxf(fabsf(k.x), fabsf(k.y)))), vs = fp8_scale(warp_max(fmaxf(fabsf(v.x), fabsf(v.y))));
+      k.x /= ks; k.y /= ks; v.x /= vs; v.y /= vs;
+      if (lane == 0) { *kv_scale_row(g, layer, slot, 0, h, off + t) = ks; *kv_scale_row(g, layer, slot, 1, h, off + t) = vs; }
+    }
     store2(kv_row<TK>(g, layer, slot, 0, h, off + t) + 2 * lane, k);
     store2(kv_row<TK>(g, layer, slot, 1, h, off + t) + 2 * lane, v);
   }
@@ -582,6 +669,8 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
   const TK* vbase = kv_row<TK>(g, layer, slot, 1, h, 0);
   int plen = 0;
   const long long dsh = pfx_delta(g, slot, plen);   // shared voice prefix (never with ring storage)
+  const float* ksbase = IsFp8<TK>::v ? kv_scale_row(g, layer, slot, 0, h, 0) : nullptr;
+  const float* vsbase = IsFp8<TK>::v ? kv_scale_row(g, layer, slot, 1, h, 0) : nullptr;
   const int t_first = mode == 2 ? (int)blockIdx.z * NW + w : w;
   const int t_step = mode == 2 ? T : NW;        // mode 2: exactly one query per warp
   for (int t = t_first; t < T; t += t_step) {
@@ -602,7 +691,7 @@ attn_chunk_kernel(float* __restrict__ qkv, const float* __restrict__ freqs,
           attend4<TK>(s, kbase, vbase, i0, cnt, q, 0.125f, lane);
         }
       } else {
-        attend4<TK>(s, kbase, vbase, p0, cnt, q, 0.125f, lane, plen, dsh);
+        attend4<TK>(s, kbase, vbase, p0, cnt, q, 0.125f, lane, plen, dsh, ksbase, vsbase);
       }
     }
     const float inv = 1.0f / s.l;
@@ -626,6 +715,8 @@ cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* of
       launch_k(attn_chunk_kernel<bf16, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out, pass);
     else if (kv.type == 0 && out_type == 1)
       launch_k(attn_chunk_kernel<float, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out, pass);
+    else if (kv.type == 2 && out_type == 1 && !kv.ring && kv.scale)
+      launch_k(attn_chunk_kernel<fp8e4, bf16>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (bf16*)out, pass);
     else
       return cudaErrorInvalidValue;
   }
@@ -896,8 +987,52 @@ __global__ void kv_fork_kernel(KvGeom g, int n_layers, int src, int dst, int p0,
   for (int idx = threadIdx.x * 4; idx < total; idx += blockDim.x * 4) store4(d + idx, load4(s + idx));
 }
 
+// ---- FP8 cache: one warp per (k|v, position, head) row
+__global__ void kv_import_fp8_kernel(const float* __restrict__ ref, KvGeom g, int layer, int slot, int P) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const long long rows = 2LL * P * g.H;
+  for (long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < rows; r += (long long)gridDim.x * (blockDim.x >> 5)) {
+    const int h = (int)(r % g.H), p = (int)((r / g.H) % P), kv = (int)(r / ((long long)g.H * P));
+    float2 v = load2(ref + r * 64 + 2 * lane);
+    const float sc = fp8_scale(warp_max(fmaxf(fabsf(v.x), fabsf(v.y))));
+    v.x /= sc; v.y /= sc;
+    store2(kv_row<fp8e4>(g, layer, slot, kv, h, p) + 2 * lane, v);
+    if (lane == 0) *kv_scale_row(g, layer, slot, kv, h, p) = sc;
+  }
+}
+__global__ void kv_export_fp8_kernel(float* __restrict__ ref, KvGeom g, int layer, int slot, int P, int p0, int p1) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31, np = p1 - p0;
+  const long long rows = 2LL * np * g.H;
+  for (long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < rows; r += (long long)gridDim.x * (blockDim.x >> 5)) {
+    const int h = (int)(r % g.H), p = p0 + (int)((r / g.H) % np), kv = (int)(r / ((long long)g.H * np));
+    float2 v = load2(kv_row<fp8e4>(g, layer, slot, kv, h, p) + 2 * lane);
+    const float sc = *kv_scale_row(g, layer, slot, kv, h, p);
+    store2(ref + (((long long)kv * P + p) * g.H + h) * 64 + 2 * lane, make_float2(v.x * sc, v.y * sc));
+  }
+}
+__global__ void kv_fork_fp8_kernel(KvGeom g, int src, int dst, int p0, int p1) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int seg = blockIdx.x;  // layer*2*H + kv*H + h
+  const int h = seg % g.H, kv = (seg / g.H) % 2, layer = seg / (2 * g.H);
+  const uint32_t* s = reinterpret_cast<const uint32_t*>(kv_row<fp8e4>(g, layer, src, kv, h, p0));
+  uint32_t* d = reinterpret_cast<uint32_t*>(kv_row<fp8e4>(g, layer, dst, kv, h, p0));
+  for (int idx = threadIdx.x; idx < (p1 - p0) * 16; idx += blockDim.x) d[idx] = s[idx];
+  const float* ss = kv_scale_row(g, layer, src, kv, h, p0);
+  float* ds = kv_scale_row(g, layer, dst, kv, h, p0);
+  for (int idx = threadIdx.x; idx < p1 - p0; idx += blockDim.x) ds[idx] = ss[idx];
+}
+
 cudaError_t launch_kv_import(const float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st) {
   if (P <= 0) return cudaSuccess;
+  if (kv.type == 2) {
+    launch_k(kv_import_fp8_kernel, (int)min(1024LL, (2LL * P * kv.H + 7) / 8), 256, 0, st, ref, kv, layer, slot, P);
+    return cudaGetLastError();
+  }
   const int blocks = (int)min(1024LL, (2LL * P * kv.H * kv.D + 255) / 256);
   if (kv.type == 0) launch_k(kv_import_kernel<float>, blocks, 256, 0, st, ref, kv, layer, slot, P);
   else launch_k(kv_import_kernel<bf16>, blocks, 256, 0, st, ref, kv, layer, slot, P);
@@ -905,6 +1040,7 @@ cudaError_t launch_kv_import(const float* ref, KvGeom kv, int layer, int slot, i
 }
 cudaError_t launch_kv_export(float* ref, KvGeom kv, int layer, int slot, int P, cudaStream_t st) {
   if (P <= 0) return cudaSuccess;
+  if (kv.type == 2) return launch_kv_export_range(ref, kv, layer, slot, P, 0, P, st);
   const int blocks = (int)min(1024LL, (2LL * P * kv.H * kv.D + 255) / 256);
   if (kv.type == 0) launch_k(kv_export_kernel<float>, blocks, 256, 0, st, ref, kv, layer, slot, P);
   else launch_k(kv_export_kernel<bf16>, blocks, 256, 0, st, ref, kv, layer, slot, P);
@@ -912,6 +1048,10 @@ cudaError_t launch_kv_export(float* ref, KvGeom kv, int layer, int slot, int P, 
 }
 cudaError_t launch_kv_export_range(float* ref, KvGeom kv, int layer, int slot, int P, int p0, int p1, cudaStream_t st) {
   if (p1 <= p0) return cudaSuccess;
+  if (kv.type == 2) {
+    launch_k(kv_export_fp8_kernel, (int)min(1024LL, (2LL * (p1 - p0) * kv.H + 7) / 8), 256, 0, st, ref, kv, layer, slot, P, p0, p1);
+    return cudaGetLastError();
+  }
   const int blocks = (int)min(1024LL, (2LL * (p1 - p0) * kv.H * kv.D + 255) / 256);
   if (kv.type == 0) launch_k(kv_export_range_kernel<float>, blocks, 256, 0, st, ref, kv, layer, slot, P, p0, p1);
   else launch_k(kv_export_range_kernel<bf16>, blocks, 256, 0, st, ref, kv, layer, slot, P, p0, p1);
@@ -921,6 +1061,7 @@ cudaError_t launch_kv_export_range(float* ref, KvGeom kv, int layer, int slot, i
 cudaError_t launch_kv_fork_range(KvGeom kv, int n_layers, int src, int dst, int p0, int p1, cudaStream_t st);
 cudaError_t launch_kv_fork(KvGeom kv, int n_layers, int src, int dst, int P, cudaStream_t st) {
   if (P <= 0) return cudaSuccess;
+  if (kv.type == 2) return launch_kv_fork_range(kv, n_layers, src, dst, 0, P, st);
   const int blocks = n_layers * 2 * kv.H;
   if (kv.type == 0) launch_k(kv_fork_kernel<float>, blocks, 256, 0, st, kv, n_layers, src, dst, 0, P);
   else launch_k(kv_fork_kernel<bf16>, blocks, 256, 0, st, kv, n_layers, src, dst, 0, P);
@@ -929,6 +1070,10 @@ cudaError_t launch_kv_fork(KvGeom kv, int n_layers, int src, int dst, int P, cud
 cudaError_t launch_kv_fork_range(KvGeom kv, int n_layers, int src, int dst, int p0, int p1, cudaStream_t st) {
   if (p1 <= p0) return cudaSuccess;
   const int blocks = n_layers * 2 * kv.H;
+  if (kv.type == 2) {
+    launch_k(kv_fork_fp8_kernel, blocks, 256, 0, st, kv, src, dst, p0, p1);
+    return cudaGetLastError();
+  }
   if (kv.type == 0) launch_k(kv_fork_kernel<float>, blocks, 256, 0, st, kv, n_layers, src, dst, p0, p1);
   else launch_k(kv_fork_kernel<bf16>, blocks, 256, 0, st, kv, n_layers, src, dst, p0, p1);
   return cudaGetLastError();

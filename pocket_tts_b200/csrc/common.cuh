@@ -1,12 +1,15 @@
 // Shared device helpers for the pocket_tts_b200 kernels (sm_100a only).
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp8.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace ptts {
 
 typedef __nv_bfloat16 bf16;
+// FP8 (e4m3) KV-cache element (PTTS kv_fp8 mode): one byte, paired with an fp32 scale per cached row
+struct fp8e4 { uint8_t b; };
 
 // ---- activation codes used by GEMM epilogues
 enum Act : int { ACT_NONE = 0, ACT_GELU = 1, ACT_SILU = 2, ACT_ELU = 3 };
@@ -55,6 +58,13 @@ __device__ __forceinline__ void store4(bf16* p, float4 v) {
 __device__ __forceinline__ float2 load2(const float* p) { return *reinterpret_cast<const float2*>(p); }
 __device__ __forceinline__ float2 load2(const bf16* p) {
   return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+}
+__device__ __forceinline__ float2 load2(const fp8e4* p) {   // two e4m3 values (unscaled)
+  const __half2_raw h = __nv_cvt_fp8x2_to_halfraw2(*reinterpret_cast<const __nv_fp8x2_storage_t*>(p), __NV_E4M3);
+  return __half22float2(*reinterpret_cast<const __half2*>(&h));
+}
+__device__ __forceinline__ void store2(fp8e4* p, float2 v) {
+  *reinterpret_cast<__nv_fp8x2_storage_t*>(p) = __nv_cvt_float2_to_fp8x2(v, __NV_SATFINITE, __NV_E4M3);
 }
 __device__ __forceinline__ void store2(float* p, float2 v) { *reinterpret_cast<float2*>(p) = v; }
 __device__ __forceinline__ void store2(bf16* p, float2 v) {

@@ -188,7 +188,16 @@ int Engine::init() {
   kv_flow = KvGeom{nullptr, S, c.n_heads, c.kv_capacity, 64, act_type, 0, 1};
   if (const char* f = getenv("PTTS_ATTN")) kv_flow.prefetch = f[0] >= '0' && f[0] <= '2' ? f[0] - '0' : 1;   // 0 per-lane loads, 1 + L2 prefetch before the wait, 2 bulk-copy kernel
   const size_t kvf = (size_t)c.n_layers * S * 2 * c.n_heads * c.kv_capacity * 64;
-  kv_flow.base = act_alloc(kvf);
+  if (c.kv_fp8) {
+    if (act_type != 1) PTTS_FAIL(PTTS_EINVAL, "kv_fp8 needs PTTS_PRECISION_BF16");
+    kv_flow.type = 2;
+    kv_flow.base = dmalloc<uint8_t>(allocs, kvf, stream);
+    kv_flow.scale = dmalloc<float>(allocs, kvf / 64, stream);
+    kv_flow.prefetch = 1;
+    if (!kv_flow.scale) PTTS_FAIL(PTTS_ECUDA, "out of device memory for stream state");
+  } else {
+    kv_flow.base = act_alloc(kvf);
+  }
   int ring = 256;
   while (ring < c.mimi_context + U) ring *= 2;
   kv_mimi = KvGeom{nullptr, S, c.mimi_heads, ring, 64, act_type, 1, 0};

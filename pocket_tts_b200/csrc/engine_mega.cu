@@ -14,7 +14,7 @@ const unsigned* mega_diag_words() { return g_mega_diag; }
 
 bool Engine::mega_eligible(int n) const {
   const ptts_config& c = cfg;
-  return use_mega && !batch_shared && act_type == 1 && use_tc && n <= mega_rows_pad && c.d_model == 1024 && c.flow_dim == 512 &&
+  return use_mega && !batch_shared && kv_flow.type != 2 && act_type == 1 && use_tc && n <= mega_rows_pad && c.d_model == 1024 && c.flow_dim == 512 &&
          c.ldim == 32 && c.ffn % 64 == 0 && c.n_heads * 64 == c.d_model;
 }
 

@@ -12,7 +12,7 @@ namespace ptts {
 struct KvGeom {
   void* base;
   int n_slots, H, cap, D;
-  int type;        // 0 float, 1 bf16
+  int type;        // 0 float, 1 bf16, 2 fp8 e4m3 with one fp32 scale per cached row (`scale`, FlowLM cache only)
   int ring;        // 1: pos stored at pos & (cap-1) (Mimi sliding window), 0: linear
   int prefetch;    // decode attention form (PTTS_ATTN): 0 per-lane loads, 1 + L2 prefetch before the producer wait, 2 bulk-copy kernel
   // Shared voice prefix (ptts_stream_fork_shared): positions [0, pfx_len[slot]) of a slot with pfx_slot[slot] >= 0 are
@@ -20,6 +20,7 @@ struct KvGeom {
   // from it); nullptr: no stream of the launch shares a prefix.
   const int* pfx_slot = nullptr;
   const int* pfx_len = nullptr;
+  float* scale = nullptr;   // type 2: scale of row (layer, slot, kv, h, pos) at the row's index (same layout without D)
 };
 
 // h[i,:] = input_linear(where(isnan(prev), bos, prev))            flow_lm.py:121-122

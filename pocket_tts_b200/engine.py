@@ -80,7 +80,8 @@ class GenerationEngine:
     """One engine per GPU: weights, stream slots, frame step."""
 
     def __init__(self, cfg: ModelConfig, state_dict: dict, *, max_streams: int = 64, kv_capacity: int = 1024,
-                 precision: str = "fp32", device: int = 0, lsd_steps: int = 1, max_prefill_rows: int = 4096):
+                 precision: str = "fp32", device: int = 0, lsd_steps: int = 1, max_prefill_rows: int = 4096,
+                 kv_dtype: str | None = None):
         self.cfg = cfg
         self.lib = N.lib()
         self.device = torch.device("cuda", device)
@@ -99,6 +100,12 @@ class GenerationEngine:
         pc.max_prefill_rows, pc.max_lsd_steps = max_prefill_rows, lsd_steps
         pc.precision = {"fp32": N.PRECISION_FP32, "bf16": N.PRECISION_BF16}[precision]
         pc.device = device
+        if kv_dtype not in (None, "fp8"):
+            raise ValueError("kv_dtype is None (cache in the activation type) or 'fp8'")
+        if kv_dtype == "fp8" and precision != "bf16":
+            raise ValueError("the FP8 KV cache belongs to the bf16 mode")
+        pc.kv_fp8 = 1 if kv_dtype == "fp8" else 0
+        self.kv_dtype = kv_dtype
         h = C.c_void_p()
         N.check(self.lib.ptts_engine_create(C.byref(pc), C.byref(h)))
         self._h = h
