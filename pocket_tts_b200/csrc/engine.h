@@ -282,7 +282,7 @@ class Engine {
   bool use_side_branch = true;               // PTTS_SIDE=0 disables
   bool use_kv_side_prefetch = false;         // PTTS_KV_SIDE=1: the QKV GEMM's idle epilogue warps prefetch the layer's K/V rows for the attention kernel (measured: attention 13.2 -> 12.8 us but the GEMM 8.5 -> 10.6 us on the chain, so off)
   bool use_fused_stage2 = true;              // PTTS_SEANET_FUSED=0: last SEANet stage as separate GEMM launches + last_conv (the fp32 mode always does)
-  int fused_sms = 0;                         // PTTS_FUSED_SMS: 0 one tile per CTA (default), -1 persistent on every SM, k > 0 persistent on k SMs
+  int fused_sms = 0;                         // PTTS_FUSED_SMS: 0 persistent, one CTA per SM (default: 112 vs 140 us per 4-frame pass), k > 0 persistent on k SMs, -1 one tile per CTA
   FusedStage2Consts fused2_consts{};
   bool use_ln_fold = true;                   // PTTS_LNFOLD=0: separate LayerNorm launches in the FlowLM decode layers
   int head_mode = 3;                         // PTTS_HEAD: 0 flow head as separate launches, 1 cluster kernel on mma.sync (flow_head.cu), 2 feature-split cluster kernel on tcgen05 (flow_head_tc.cu), 3 stream-split tcgen05 kernel without cross-CTA exchange (flow_head_ss.cu, default)

@@ -309,7 +309,7 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
       LAUNCH("seanet.stage2_fused",
              launch_seanet_stage2_fused((const bf16*)b_tr[2], stages[2].tr.b16, stages[2].c3.b16, stages[2].c1.b16, fused2_consts,
                                         (bf16*)b_res[2], (bf16*)b_last, pcm_out, n, T,
-                                        fused_sms > 0 ? std::min(fused_sms, n_sms) : (fused_sms < 0 ? n_sms : 1 << 30), pdl_enabled(), stream));
+                                        fused_sms > 0 ? std::min(fused_sms, n_sms) : (fused_sms < 0 ? 1 << 30 : n_sms), pdl_enabled(), stream));
       LAUNCH("seanet.hist_scatter", launch_hist_scatter(tab, d_slot_ids, act_type, n, stream));
       return PTTS_OK;
     }
