@@ -157,6 +157,12 @@ int Engine::init() {
       }
     }
   }
+  // developer timing probes that produce WRONG audio (skipped kernels, no GELU, one branch of the loop only): never
+  // silent - every engine created under them says so on stderr
+  for (const char* probe : {"PTTS_SKIP_TAGS", "PTTS_DEBUG_NOGELU", "PTTS_PROFILE_PART"})
+    if (const char* v = getenv(probe))
+      if (v[0] && !(probe[5] == 'P' && v[0] == '0'))
+        fprintf(stderr, "[pocket_tts_b200] WARNING: %s=%s is set - developer timing probe, outputs of this engine are NOT valid audio\n", probe, v);
   if (const char* f = getenv("PTTS_FORCE_SIMT")) use_tc = !(f[0] == '1');
   if (const char* f = getenv("PTTS_MIMI_GROUP")) mimi_gmax = std::max(1, std::min(8, atoi(f)));
   PTTS_CUDA_CHECK(cudaStreamCreateWithPriority(&copy_stream, cudaStreamNonBlocking, prio_lo));

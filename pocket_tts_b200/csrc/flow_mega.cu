@@ -846,6 +846,17 @@ cudaError_t flow_mega_launch(const MegaParams& P, cudaStream_t st) {
   cfg.stream = st;
   cfg.attrs = nullptr;
   cfg.numAttrs = 0;
+  {  // the kernel spins on software grid barriers: every CTA must be resident at once
+    static int max_ctas = -1;
+    if (max_ctas < 0) {
+      int per_sm = 0, sms = 0, dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, flow_mega_kernel, (int)cfg.blockDim.x, cfg.dynamicSmemBytes) != cudaSuccess) per_sm = 0;
+      max_ctas = per_sm * sms;
+    }
+    if ((int)cfg.gridDim.x > max_ctas) return cudaErrorCooperativeLaunchTooLarge;
+  }
   return cudaLaunchKernelEx(&cfg, flow_mega_kernel, P);
 }
 

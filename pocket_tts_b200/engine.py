@@ -250,6 +250,10 @@ class GenerationEngine:
         """Device-resident loop: noise_dev [F, n, ldim] on the GPU; asynchronous."""
         assert noise_dev.is_cuda and noise_dev.dtype == torch.float32 and noise_dev.is_contiguous()
         F, n, _ = noise_dev.shape
+        # the call is asynchronous on the engine's own streams: keep the tensors alive until synchronize(), or torch's
+        # caching allocator may hand their memory to someone else while the engine still reads / writes it
+        self._inflight = getattr(self, "_inflight", [])
+        self._inflight.append((noise_dev, out_pcm, out_latents))
         N.check(self.lib.ptts_run_frames(self._h, n, _i32(slots), F, _ptr(noise_dev), lsd_steps or self.lsd_steps,
                                          _ptr(out_pcm), _ptr(out_latents)))
 
@@ -314,6 +318,7 @@ class GenerationEngine:
 
     def synchronize(self) -> None:
         N.check(self.lib.ptts_synchronize(self._h))
+        self._inflight = []
 
     @property
     def launch_count(self) -> int:

@@ -176,13 +176,16 @@ class TTSModel:
         if not getattr(ref, "has_voice_cloning", False):   # encoder weights of such a checkpoint are uninitialised
             sd = {k: v for k, v in sd.items() if not k.startswith(("mimi.encoder", "mimi.downsample"))}
         enc = None
-        return cls(cfg, sd, ReferenceTokenizerAdapter(ref.flow_lm.conditioner.tokenizer),
+        origin = getattr(ref, "origin", None)
+        m = cls(cfg, sd, ReferenceTokenizerAdapter(ref.flow_lm.conditioner.tokenizer),
                    temp=ref.temp, lsd_decode_steps=ref.lsd_decode_steps, noise_clamp=ref.noise_clamp,
                    eos_threshold=ref.eos_threshold,
                    pad_with_spaces_for_short_inputs=getattr(ref, "pad_with_spaces_for_short_inputs", False),
                    remove_semicolons=getattr(ref, "remove_semicolons", False),
                    model_recommended_frames_after_eos=getattr(ref, "model_recommended_frames_after_eos", None),
                    audio_encoder=enc, **engine_kwargs)
+        m.origin = origin          # config path of the language: predefined voices are resolved against it
+        return m
 
     @classmethod
     def from_state_dict(cls, cfg: ModelConfig, state_dict: dict, tokenizer: Tokenizer | str | Path | None = None,
@@ -272,6 +275,8 @@ class TTSModel:
         [channels, samples] / audio file (encoded on the device by the engine's Mimi encoder, ptts_encode_audio =
         _encode_audio tts_model.py:379-388), or - extension - an already encoded conditioning tensor
         [P, d_model] / [1, P, d_model]."""
+        if isinstance(audio_conditioning, str) and not Path(audio_conditioning).exists():
+            audio_conditioning = self._resolve_voice_reference(audio_conditioning)   # predefined name / URL
         if isinstance(audio_conditioning, (str, Path)) and str(audio_conditioning).endswith(".safetensors"):
             return import_model_state(audio_conditioning)
         if isinstance(audio_conditioning, (str, Path)):
@@ -313,6 +318,28 @@ class TTSModel:
         finally:
             if not keep:
                 self.engine.close_stream(slot)
+
+    def _resolve_voice_reference(self, name: str):
+        """Predefined voice names and http(s):// / hf:// URLs (tts_model.py:846-876) are resolved by the reference
+        package's own resolver / downloader - host-side pieces that stay as they are; returns a local path."""
+        is_url = name.startswith(("http://", "https://", "hf://"))
+        try:
+            from pocket_tts.utils.utils import _ORIGINS_OF_PREDEFINED_VOICES, download_if_necessary, get_predefined_voice
+        except ImportError as e:
+            if is_url or "/" not in name:
+                raise ValueError(f"{name!r} is a predefined voice name or a URL: those are resolved by the reference package "
+                                 "(pocket_tts.utils.utils), which is not importable here; pass a local .wav / .safetensors "
+                                 "path or a conditioning tensor") from e
+            raise FileNotFoundError(name) from e
+        if name in _ORIGINS_OF_PREDEFINED_VOICES:
+            origin = getattr(self, "origin", None)
+            if origin is None:
+                raise ValueError("Cannot use predefined voices when the model is not loaded from a config associated with "
+                                 "a language (tts_model.py:858-863)")
+            return download_if_necessary(get_predefined_voice(language=Path(origin).stem, name=name))
+        if is_url:
+            return download_if_necessary(name)
+        raise FileNotFoundError(name)
 
     def _make_room_for_voice(self) -> bool:
         """Evict the oldest resident voice prefixes that no live stream reads until one more fits."""

@@ -135,6 +135,8 @@ def test_api_error_conventions():
             m.generate_audio(state, "   ")
         with pytest.raises(ValueError):
             m.get_state_for_audio_prompt(torch.zeros(1, 24000))      # raw audio without a host encoder
+        with pytest.raises(ValueError):                               # predefined voice name: the reference's resolver is
+            m.get_state_for_audio_prompt("alba")                      # absent on the GPU box / no language origin here
         with pytest.raises(ValueError):
             m.generate_audio_batch([state], ["a.", "b."])
         with pytest.raises(ValueError):                               # KV capacity: 5 + 400 + frames > 512
