@@ -6,6 +6,7 @@
 // (2*lane, 2*lane+1) of the 64-wide head, so a K or V row is one coalesced 256 B (fp32) /
 // 128 B (bf16) warp load, the rotation needs no shuffles, and the score is a 5-step
 // butterfly.  Warps split the positions and are merged with a log-sum-exp combine.
+#include <algorithm>
 #include <cstdlib>
 
 #include "kernels.cuh"
@@ -891,13 +892,16 @@ cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const 
   const bool use_mma = !env_mma || atoi(env_mma) != 0;
   const int NQ = frames * T;
   if (use_mma && kv.type == 1 && out_type == 1 && T == 16 && NQ <= 64 && context - 1 + NQ <= WM_MAXW) {
+    // PTTS_MIMI_HALF=1 (probe): one CTA per SM (shared memory padded past half an SM) so that a kernel of the
+    // latency-critical FlowLM branch always finds room beside it
+    static const bool half_sm = [] { const char* e = getenv("PTTS_MIMI_HALF"); return e && e[0] == '1'; }();
+    const size_t wsmem = half_sm ? std::max<size_t>(attn_window_mma_smem(), 118 * 1024) : attn_window_mma_smem();
     static DeviceOnce attr;
     if (attr.first()) {
-      cudaError_t e = cudaFuncSetAttribute(attn_window_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)attn_window_mma_smem());
+      cudaError_t e = cudaFuncSetAttribute(attn_window_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
       if (e != cudaSuccess) return e;
     }
-    launch_k(attn_window_mma_kernel, dim3(kv.H, n), WM_THREADS, attn_window_mma_smem(), st, qkv, rope_freqs, offsets,
+    launch_k(attn_window_mma_kernel, dim3(kv.H, n), WM_THREADS, wsmem, st, qkv, rope_freqs, offsets,
              slot_ids, kv, layer, context, NQ, (bf16*)out);
     return cudaGetLastError();
   }

@@ -285,7 +285,7 @@ class Engine {
   int fused_sms = 0;                         // PTTS_FUSED_SMS: 0 persistent, one CTA per SM (default: 112 vs 140 us per 4-frame pass), k > 0 persistent on k SMs, -1 one tile per CTA
   FusedStage2Consts fused2_consts{};
   bool use_ln_fold = true;                   // PTTS_LNFOLD=0: separate LayerNorm launches in the FlowLM decode layers
-  int head_mode = 3;                         // PTTS_HEAD: 0 flow head as separate launches, 1 cluster kernel on mma.sync (flow_head.cu), 2 feature-split cluster kernel on tcgen05 (flow_head_tc.cu), 3 stream-split tcgen05 kernel without cross-CTA exchange (flow_head_ss.cu, default)
+  int head_mode = 3;                         // PTTS_HEAD: 0 flow head as separate launches (A/B reference), 2 feature-split 8-CTA cluster kernel on tcgen05 (flow_head_tc.cu), 3 stream-split kernel without cross-CTA exchange (flow_head_ss.cu, default); the first cluster form on mma.sync (1) was retired in round 2
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph
   cudaEvent_t ev_lat[2] = {}, ev_mimi[2] = {}, ev_copied_lat[2] = {}, ev_copied_pcm[2] = {};
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)

@@ -174,7 +174,7 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
   // u = input_proj(x_0) of the first Euler step depends on nothing but the noise: it runs on a side branch beside
   // the transformer layers instead of sitting in the dependent chain of the flow head
   // bf16 mode: everything after the AdaLN modulation GEMM of an Euler step is one cluster kernel (flow_head.cu)
-  const bool head_cluster = head_mode != 0 && act_type == 1 && use_tc && flow_head_cluster_supported(F, Ld, c.flow_depth);
+  const bool head_cluster = head_mode != 0 && act_type == 1 && use_tc && flow_head_ss_supported(F, Ld, c.flow_depth);
   const bool side_u = use_side_branch && side_stream != nullptr && !head_cluster;
   if (side_u) {
     PTTS_CUDA_CHECK(cudaEventRecord(ev_side_fork, stream));
@@ -230,14 +230,12 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
         tp.h = hp;
         if (!flow_head_ss_prepare(&tp)) PTTS_FAIL(PTTS_ECUDA, "tensor map encode failed (flow head)");
         LAUNCH("head.cluster", launch_flow_head_ss(tp, stream));
-      } else if (head_mode >= 2) {
+      } else {
         FlowHeadTcParams tp;
         tp.h = hp;
         tp.xchg = head_l2_exchange ? head_xchg : nullptr;
         if (!flow_head_tc_prepare(&tp)) PTTS_FAIL(PTTS_ECUDA, "tensor map encode failed (flow head)");
         LAUNCH("head.cluster", launch_flow_head_tc(tp, stream));
-      } else {
-        LAUNCH("head.cluster", launch_flow_head_cluster(hp, stream));
       }
       continue;
     }
@@ -284,6 +282,11 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
   if (!pcm_out) pcm_out = pcm;
   HistTable tab = hist_tab;
   for (int k = 0; k < tab.count; ++k) tab.d[k].T *= frames;
+  {  // developer probe (PTTS_MIMI_PAD_NODES=k): k extra trivial kernel nodes per Mimi pass - measures what a graph node of the
+     // Mimi branch costs the FlowLM chain through the shared launch front end
+    static const int pad = [] { const char* e = getenv("PTTS_MIMI_PAD_NODES"); return e ? atoi(e) : 0; }();
+    for (int k = 0; k < pad; ++k) LAUNCH("advance", launch_advance(mimi_offsets, d_slot_ids, nullptr, 0, n, stream));
+  }
   LAUNCH("mimi.embed_upsample", launch_mimi_embed(latents, d_slot_ids, emb_std, emb_mean, wq, wup, e_prev, xm, n, Md, c.ldim, c.upsample_stride, frames, stream));
   for (int l = 0; l < c.mimi_layers; ++l)
     if ((rc = transformer_layer_common(mimi_layers[l], xm, n * U, Md, c.mimi_ffn, m_ln, mqkv, m_attn, m_mid, true, l, n)) != PTTS_OK)

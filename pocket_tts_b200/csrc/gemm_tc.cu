@@ -706,6 +706,10 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
   size_t smem = (size_t)P.stages * (BM_TC * 128 + BN * 128) + (clustered ? (size_t)BN * BM_TC * sizeof(float) : 0);
   if (!SWAP) smem = std::max(smem, EPI_SMEM_BYTES);   // the epilogue staging reuses the (drained) pipeline buffers
   smem += 1024;
+  // PTTS_MIMI_HALF=1 (probe): row-major GEMMs (the Mimi branch) take more than half an SM's shared memory, i.e. one CTA
+  // per SM, so that a CTA of the latency-critical FlowLM branch always finds room beside it
+  static const bool half_sm = [] { const char* e = getenv("PTTS_MIMI_HALF"); return e && e[0] == '1'; }();
+  if (!SWAP && half_sm) smem = std::max<size_t>(smem, 118 * 1024);
   static DeviceOnce attr_done;
   auto kern = gemm_tc_kernel<BN, SWAP, TO>;
   if (attr_done.first()) {

@@ -113,10 +113,56 @@ ln_rows_kernel(const float* __restrict__ x, const float* __restrict__ w, const f
   }
 }
 
+// d <= 512 (Mimi transformers: thousands of rows per pass): one WARP per row, 8 rows per CTA, no block barriers;
+// the choice depends on d only, so a row is normalised by the same arithmetic whatever the pass size
+template <typename TO>
+__global__ void __launch_bounds__(256)
+ln_rows_warp_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, float eps,
+                    TO* __restrict__ y, int rows, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float* xr = x + row * d;
+  float4 v[4];
+  float s = 0.0f;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = (lane + j * 32) * 4;
+    v[j] = (c < d) ? load4(xr + c) : make_float4(0, 0, 0, 0);
+    s += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+  }
+  const float mu = warp_sum(s) / (float)d;
+  float q = 0.0f;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    if ((lane + j * 32) * 4 < d) {
+      const float a0 = v[j].x - mu, a1 = v[j].y - mu, a2 = v[j].z - mu, a3 = v[j].w - mu;
+      q += (a0 * a0 + a1 * a1) + (a2 * a2 + a3 * a3);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)d + eps);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = (lane + j * 32) * 4;
+    if (c < d) {
+      const float4 wv = load4(w + c), bv = load4(b + c);
+      store4(y + row * d + c, make_float4((v[j].x - mu) * rstd * wv.x + bv.x, (v[j].y - mu) * rstd * wv.y + bv.y,
+                                          (v[j].z - mu) * rstd * wv.z + bv.z, (v[j].w - mu) * rstd * wv.w + bv.w));
+    }
+  }
+}
+
 cudaError_t launch_ln_rows(const float* x, const float* w, const float* b, float eps, void* y,
                            int y_type, int rows, int d, cudaStream_t st) {
   if (rows <= 0) return cudaSuccess;
   if (d % 4 || d > 1024) return cudaErrorInvalidValue;
+  if (d <= 512) {
+    if (y_type == 0) launch_k(ln_rows_warp_kernel<float>, (rows + 7) / 8, 256, 0, st, x, w, b, eps, (float*)y, rows, d);
+    else launch_k(ln_rows_warp_kernel<bf16>, (rows + 7) / 8, 256, 0, st, x, w, b, eps, (bf16*)y, rows, d);
+    return cudaGetLastError();
+  }
   if (y_type == 0) launch_k(ln_rows_kernel<float, 2>, rows, 128, 0, st, x, w, b, eps, (float*)y, d);
   else launch_k(ln_rows_kernel<bf16, 2>, rows, 128, 0, st, x, w, b, eps, (bf16*)y, d);
   return cudaGetLastError();

@@ -75,7 +75,7 @@ cudaError_t launch_ln_modulate(const float* u, const float* w, const float* b, c
                                const float* scale, int mod_ld, void* g, int g_type, int n, int d,
                                cudaStream_t st);
 
-// One Euler step of the flow head after the AdaLN modulation GEMM, as a single cluster kernel (flow_head.cu,
+// One Euler step of the flow head after the AdaLN modulation GEMM, as a single kernel (flow_head_ss.cu / flow_head_tc.cu,
 // bf16 mode, flow_dim 512, ldim 32): input_proj, the ResBlocks, the final layer and the latent commit.
 #define PTTS_HEAD_MAX_DEPTH 8
 struct FlowHeadBlock {
@@ -97,8 +97,6 @@ struct FlowHeadParams {
   float* prev_latent;                    // nullable
   float* commit_out;                     // nullable
 };
-bool flow_head_cluster_supported(int flow_dim, int ldim, int depth);
-cudaError_t launch_flow_head_cluster(const FlowHeadParams& p, cudaStream_t st);
 // tcgen05 form (flow_head_tc.cu): the same step with TMEM accumulators, a TMA weight ring and bulk DSMEM operand
 // exchange.  `maps`: one SWIZZLE_128B tensor map per matrix (mlp.0 / mlp.2 of every block, then the final layer).
 struct FlowHeadTcParams {

@@ -396,30 +396,30 @@ def test_persistent_step_kernel_vs_reference_fixture(monkeypatch):
 
 
 def test_flow_head_cluster_kernel(monkeypatch):
-    """bf16 mode runs the flow head (input_proj, ResBlocks, final layer, commit) as one cluster kernel: tcgen05
-    form (flow_head_tc.cu, PTTS_HEAD=2, default) or mma.sync form (flow_head.cu, PTTS_HEAD=1).  Both must meet
-    the reference gate (lsd 1 and 2) and agree with the kernel-per-op form (PTTS_HEAD=0) far inside it,
-    including a batch that spans two clusters with a ragged tail (70 streams)."""
-    for mode in ("2", "1"):
+    """bf16 mode runs the flow head (input_proj, ResBlocks, final layer, commit) as one kernel: the stream-split
+    form (flow_head_ss.cu, PTTS_HEAD=3, default) or the feature-split tcgen05 cluster form (flow_head_tc.cu,
+    PTTS_HEAD=2).  Both must meet the reference gate (lsd 1 and 2) and agree with the kernel-per-op form
+    (PTTS_HEAD=0) far inside it, including a batch that spans two clusters with a ragged tail (70 streams)."""
+    for mode in ("3", "2"):
         monkeypatch.setenv("PTTS_HEAD", mode)
         for name in ("gen_2l", "gen_2l_lsd2", "gen_english_6l"):
             _check_case(name, "bf16", teacher=True, tol=TOL_BF16, snr_min=None)
     case = load_case("gen_2l_lsd2")
     outs = {}
-    for flag in ("2", "1", "0"):
+    for flag in ("2", "3", "0"):
         monkeypatch.setenv("PTTS_HEAD", flag)
         eng = make_engine(2, precision="bf16", lsd_steps=2)
         outs[flag] = _run_engine_case(eng, case, teacher=True)
         eng.close()
     assert po.rel_l2(outs["2"][0], outs["0"][0]) <= 2e-3
-    assert po.rel_l2(outs["1"][0], outs["0"][0]) <= 2e-3
+    assert po.rel_l2(outs["3"][0], outs["0"][0]) <= 2e-3
     B, G = 70, 2
     g = torch.Generator().manual_seed(11)
     orc = oracle_for(2)
     conds = [torch.randn(3 + i % 4, 1024, generator=g) * 0.3 for i in range(B)]
     noise = torch.randn(G, B, 32, generator=g) * 0.7 ** 0.5
     lats = {}
-    for flag in ("2", "1", "0"):
+    for flag in ("2", "3", "0"):
         monkeypatch.setenv("PTTS_HEAD", flag)
         eng = make_engine(2, precision="bf16", max_streams=B)
         slots = [eng.open_stream() for _ in range(B)]
@@ -428,7 +428,7 @@ def test_flow_head_cluster_kernel(monkeypatch):
         eng.close()
     for i in range(B):
         assert po.rel_l2(lats["2"][:, i], lats["0"][:, i]) <= 5e-3, i
-        assert po.rel_l2(lats["1"][:, i], lats["0"][:, i]) <= 5e-3, i
+        assert po.rel_l2(lats["3"][:, i], lats["0"][:, i]) <= 5e-3, i
 
 
 def test_layernorm_folded_decode_gemms(monkeypatch):
