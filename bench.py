@@ -429,6 +429,9 @@ def run_cfg5(args, rank, world, local_rank):
     from pocket_tts_b200.tts_model import TTSModel
 
     torch.cuda.set_device(local_rank)
+    # the scheduler's host work (PCM block copies, noise draws) is torch CPU code: torchrun pins every rank to one OpenMP
+    # thread by default, which made 8 ranks host-bound; give each rank its share of the box's cores
+    torch.set_num_threads(max(1, (os.cpu_count() or 8) // max(1, world)))
     dims = po.PRESETS["english"]
     W = dict(po.make_weights(dims, seed=0))
     W.update(po.make_encoder_weights(dims, seed=0))

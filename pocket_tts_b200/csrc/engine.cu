@@ -180,6 +180,7 @@ int Engine::init() {
   if (const char* f = getenv("PTTS_LNFOLD")) use_ln_fold = !(f[0] == '0');
   if (const char* f = getenv("PTTS_SEANET_FUSED")) use_fused_stage2 = !(f[0] == '0');
   if (const char* f = getenv("PTTS_FUSED_SMS")) fused_sms = atoi(f);
+  if (const char* f = getenv("PTTS_RESBLOCK_FUSED")) use_fused_resblock = !(f[0] == '0');
   if (const char* f = getenv("PTTS_HEAD")) head_mode = (f[0] == '0' || f[0] == '2' || f[0] == '3') ? f[0] - '0' : 3;
   for (int k = 0; k < 2; ++k) {
     for (cudaEvent_t* e : {&ev_lat[k], &ev_mimi[k], &ev_copied_lat[k], &ev_copied_pcm[k]})

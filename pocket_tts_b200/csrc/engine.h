@@ -284,6 +284,8 @@ class Engine {
   bool use_fused_stage2 = true;              // PTTS_SEANET_FUSED=0: last SEANet stage as separate GEMM launches + last_conv (the fp32 mode always does)
   int fused_sms = 0;                         // PTTS_FUSED_SMS: 0 persistent, one CTA per SM (default: 112 vs 140 us per 4-frame pass), k > 0 persistent on k SMs, -1 one tile per CTA
   FusedStage2Consts fused2_consts{};
+  bool use_fused_resblock = true;            // PTTS_RESBLOCK_FUSED=0: ResBlocks of stages 0 / 1 as two GEMM launches each
+  std::vector<float> res_b3_host[3], res_b1_host[3];   // host copies of the ResBlock biases (kernel parameters of the fused form)
   bool use_ln_fold = true;                   // PTTS_LNFOLD=0: separate LayerNorm launches in the FlowLM decode layers
   int head_mode = 3;                         // PTTS_HEAD: 0 flow head as separate launches (A/B reference), 2 feature-split 8-CTA cluster kernel on tcgen05 (flow_head_tc.cu), 3 stream-split kernel without cross-CTA exchange (flow_head_ss.cu, default); the first cluster form on mma.sync (1) was retired in round 2
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph

@@ -323,6 +323,14 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
       ep.out = off(b_res[i], (long long)rk * C2); ep.out_map = batched((long long)(rk + T2) * C2, rpb, T, r * C2);
       if ((rc = gemm(kTrTag[i], b_tr[i], true, batched((long long)rpb * C, rpb, T, C), stages[i].tr, n * rpb, ep, true)) != PTTS_OK) return rc;
     }
+    if (i < 2 && use_fused_resblock && act_type == 1 && use_tc && seanet_resblock_fused_supported(C2, C2 / 2, hc, c.res_kernel)) {
+      // conv3 -> ELU -> conv1 + skip -> ELU in one persistent kernel, hidden tensor on chip (seanet_fused.cu)
+      LAUNCH("seanet.resblock_fused",
+             launch_seanet_resblock_fused(C2, (const bf16*)b_res[i], (const bf16*)b_raw[i], stages[i].c3.b16, stages[i].c1.b16,
+                                          res_b3_host[i].data(), res_b1_host[i].data(), (bf16*)b_tr[i + 1], 1, n, T2, n_sms, pdl_enabled(), stream));
+      T = T2; C = C2;
+      continue;
+    }
     {  // ResBlock conv K3 C2 -> C2/2 on ELU(x), ELU on the way out (seanet.py:27-41)
       const int rpb = rk + T2;
       GemmEpilogue ep; ep.bias = stages[i].c3_b; ep.act_post = ACT_ELU;

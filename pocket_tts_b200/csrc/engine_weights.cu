@@ -242,8 +242,10 @@ int Engine::finalize() {
       if ((rc = make_mat_from(p3, hp, k3, &stages[i].c3)) != PTTS_OK) return rc;
       if ((rc = make_mat_from(p1, C2, hp, &stages[i].c1)) != PTTS_OK) return rc;
       stages[i].c3_b = upload(b3);
+      res_b3_host[i] = b3;
     }
     GETV(stages[i].c1_b, pr + "3.conv.bias", C2);
+    res_b1_host[i] = host_w[pr + "3.conv.bias"].data;
     C = C2;
     idx += 3;
   }

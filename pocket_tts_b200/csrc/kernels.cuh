@@ -161,6 +161,12 @@ cudaError_t launch_seanet_stage2_fused(const bf16* x_buf, const bf16* w_tr, cons
                                        bf16* res_buf, bf16* last_buf, float* pcm, int n, int T, int grid_cap, bool pdl, cudaStream_t st,
                                        unsigned long long* trace = nullptr);
 
+// SEANet ResBlock of stages 0 / 1 as one persistent tcgen05 kernel (conv3 -> ELU -> conv1 + skip -> ELU, hidden tensor kept
+// on chip): e_buf [n][2 + T][C] = ELU(y) behind two history rows, raw [n][T][C] = y, out [n][out_hist + T][C]; C = 128 | 256
+bool seanet_resblock_fused_supported(int C, int hid, int hid_padded, int res_kernel);
+cudaError_t launch_seanet_resblock_fused(int C, const bf16* e_buf, const bf16* raw, const bf16* w3, const bf16* w1, const float* b3_host,
+                                         const float* b1_host, bf16* out, int out_hist, int n, int T, int n_sms, bool pdl, cudaStream_t st);
+
 // data/audio.py:77-78: (clamp(x, -1, 1) * 32767) truncated to int16
 cudaError_t launch_pcm_to_int16(const float* pcm, short* out, long long n, cudaStream_t st);
 

@@ -389,4 +389,247 @@ cudaError_t launch_seanet_stage2_fused(const bf16* x_buf, const bf16* w_tr, cons
   return cudaLaunchKernelEx(&cfg, seanet_stage2_fused_kernel, tx, twtr, tw3, tw1, P);
 }
 
+
+// =====================================================================================================================
+// Fused SEANet ResBlock (stages 0 and 1 of the decoder, bf16 mode):  out = ELU( y + b1 + W1 . ELU( b3 + W3 . (e[t-2] | e[t-1] | e[t]) ) )
+// with e = ELU(y) (seanet.py:20-41).  The unfused form ran conv3 and conv1 as two GEMM launches with the hidden tensor
+// (padded to 64 channels) written to and read back from L2 / HBM in between.  Here one persistent CTA per SM walks
+// tiles of 128 time steps: GEMM-B (K = 3C through a TMA ring, A rows overlap in the tensor map) -> D_B in TMEM ->
+// epilogue writes bf16(ELU(D_B + b3)) into shared memory in the K-major SWIZZLE_128B form -> GEMM-C with the resident
+// W1 -> D_C -> epilogue adds bias + skip (raw y from global) and stores ELU(.) as the next transposed conv's input.
+// C = 128 (stage 1): TMEM 2 x (64 + 128) columns, two tiles in flight (GEMM-B of tile t+1 runs beside the epilogues of
+// tile t); C = 256 (stage 0): 128 + 256 columns, one tile in flight.
+// =====================================================================================================================
+struct ResBlockParams {
+  int n, T, tiles_per_stream, n_tiles;
+  float b3[128];       // conv3 bias (hidden width <= 128)
+  float b1[256];       // conv1 bias
+  const bf16* raw;     // [n][T][C]   y (skip)
+  bf16* out;           // [n][out_hist + T][C]: ELU(out) behind the next conv's history rows
+  int out_hist;
+};
+
+template <int C, int NBUF>
+__global__ void __launch_bounds__(FS_THREADS, 1)
+seanet_resblock_fused_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_w3,
+                             const __grid_constant__ CUtensorMap tm_w1, const __grid_constant__ ResBlockParams P) {
+  constexpr int HP = C / 2;                       // hidden channels (64 / 128)
+  constexpr int NKB = 3 * C / 64;                 // k-blocks of GEMM-B
+  constexpr int HKB = HP / 64;                    // k-blocks of GEMM-C
+  constexpr uint32_t A_BYTES = 128 * 128, W3_BYTES = HP * 128, STAGE = A_BYTES + W3_BYTES;
+  constexpr int STAGES = C == 128 ? 4 : 3;
+  constexpr uint32_t OFF_H = STAGES * STAGE;                         // [NBUF][HKB][128 rows][128 B]
+  constexpr uint32_t OFF_W1 = OFF_H + NBUF * HKB * 16384;            // [HKB][C rows][128 B]
+  constexpr uint32_t TM_DB = 0, TM_DC = HP, TM_STRIDE = HP + C;      // per buffer: D_B | D_C
+  constexpr uint32_t TM_COLS = 512;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* sm = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  __shared__ __align__(8) uint64_t full_bar[4], empty_bar[4];
+  __shared__ __align__(8) uint64_t w_bar, db_full[2], h_ready[2], dc_full[2], tmem_free[2];
+  __shared__ uint32_t tmem_base_smem;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_launch_dependents();
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_w3) : "memory");
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(&w_bar, 1);
+    for (int b = 0; b < 2; ++b) { mbar_init(&db_full[b], 1); mbar_init(&h_ready[b], 8); mbar_init(&dc_full[b], 1); mbar_init(&tmem_free[b], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_expect_tx(&w_bar, HKB * C * 128);
+    for (int j = 0; j < HKB; ++j) tma_load_2d(sm + OFF_W1 + j * C * 128, &tm_w1, &w_bar, j * 64, 0);
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_smem)), "n"(TM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  pdl_wait();
+  const uint32_t tmem_base = tmem_base_smem;
+  const uint32_t sm_a = smem_u32(sm);
+  const uint32_t full_a = smem_u32(&full_bar[0]), empty_a = smem_u32(&empty_bar[0]);
+
+  if (warp == 0) {
+    // ===== TMA producer: NKB k-blocks of (A 128 x 64, W3 HP x 64) per tile =====
+    uint32_t s = 0, ph = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      const int i = tile / P.tiles_per_stream, k = tile - i * P.tiles_per_stream;
+      const int row0 = i * (2 + P.T) + k * 128;        // A row t = buffer rows t .. t+2 = e[t-2 .. t]
+      for (int kb = 0; kb < NKB; ++kb) {
+        mbar_wait_a(empty_a + 8u * s, ph ^ 1u);
+        if (lane == 0) {
+          const uint32_t st = sm_a + s * STAGE, fb = full_a + 8u * s;
+          mbar_expect_tx_a(fb, STAGE);
+          tma_load_2d_a(st, &tm_a, fb, kb * 64, row0);
+          tma_load_2d_a(st + A_BYTES, &tm_w3, fb, kb * 64, 0);
+        }
+        __syncwarp();
+        if (++s == STAGES) { s = 0; ph ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: B(0), B(1), C(0), B(2), C(1), ... with NBUF = 2; B(t), C(t) with NBUF = 1 =====
+    const uint32_t idesc_b = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(HP >> 3) << 17) | ((128u >> 4) << 24);
+    const uint32_t idesc_c = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(C >> 3) << 17) | ((128u >> 4) << 24);
+    const uint64_t d_ring = make_sw128_desc(sm_a), d_h = make_sw128_desc(sm_a + OFF_H), d_w1 = make_sw128_desc(sm_a + OFF_W1);
+    uint32_t s = 0, ph = 0;
+    mbar_wait(&w_bar, 0);
+    int n_mine = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) ++n_mine;
+    auto gemm_b = [&](int t) {
+      const uint32_t b = NBUF == 2 ? (uint32_t)(t & 1) : 0u, use = (uint32_t)(t / NBUF);
+      mbar_wait(&tmem_free[b], (use & 1u) ^ 1u);       // the epilogue drained this buffer (first use: passes)
+      tc_fence_after();
+      for (int kb = 0; kb < NKB; ++kb) {
+        mbar_wait_a(full_a + 8u * s, ph);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint64_t soff = (uint64_t)((s * STAGE) >> 4);
+          const uint64_t ad = d_ring + soff, bd = d_ring + soff + (uint64_t)(A_BYTES >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc_mma_bf16(tmem_base + b * TM_STRIDE + TM_DB, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), idesc_b, (kb | k) != 0);
+          tc_commit_a(empty_a + 8u * s);
+          if (kb == NKB - 1) tc_commit(&db_full[b]);
+        }
+        __syncwarp();
+        if (++s == STAGES) { s = 0; ph ^= 1u; }
+      }
+    };
+    auto gemm_c = [&](int t) {
+      const uint32_t b = NBUF == 2 ? (uint32_t)(t & 1) : 0u, use = (uint32_t)(t / NBUF);
+      mbar_wait(&h_ready[b], use & 1u);
+      tc_fence_after();
+      if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < HKB; ++j) {
+          const uint64_t ad = d_h + (uint64_t)(((b * HKB + j) * 16384) >> 4), bd = d_w1 + (uint64_t)((j * C * 128) >> 4);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            tc_mma_bf16(tmem_base + b * TM_STRIDE + TM_DC, ad + (uint64_t)(k * 2), bd + (uint64_t)(k * 2), idesc_c, (j | k) != 0);
+        }
+        tc_commit(&dc_full[b]);
+      }
+      __syncwarp();
+    };
+    if (NBUF == 2) {
+      for (int t = 0; t < n_mine; ++t) {
+        gemm_b(t);
+        if (t > 0) gemm_c(t - 1);
+      }
+      if (n_mine > 0) gemm_c(n_mine - 1);
+    } else {
+      for (int t = 0; t < n_mine; ++t) { gemm_b(t); gemm_c(t); }
+    }
+  } else {
+    // ===== epilogue warps 2..9: TMEM lane quarter q, column half hh =====
+    const int q = warp & 3, hh = (warp - 2) >> 2;
+    const int r = q * 32 + lane;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
+    int t = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++t) {
+      const uint32_t b = NBUF == 2 ? (uint32_t)(t & 1) : 0u, par = (uint32_t)(t / NBUF) & 1u;
+      const int i = tile / P.tiles_per_stream, k = tile - i * P.tiles_per_stream;
+      const int ts = k * 128 + r;                       // time step of this row
+      const bool valid = ts < P.T;
+      // ---- epi-B: hidden = bf16(ELU(D_B + b3)) -> H[b]
+      mbar_wait(&db_full[b], par);
+      tc_fence_after();
+#pragma unroll
+      for (int c0 = 0; c0 < HP / 2; c0 += 32) {
+        const int col = hh * (HP / 2) + c0;
+        float v[32];
+        tmem_ld<32>(t_lane + b * TM_STRIDE + TM_DB + col, v);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = elu_call(v[j] + P.b3[col + j]);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int chunk = (col >> 3) + c;             // 16-byte chunk of the hidden row
+          *reinterpret_cast<uint4*>(sm + OFF_H + (b * HKB + (chunk >> 3)) * 16384 + sw128_off(r, chunk & 7)) = pack8(v + 8 * c);
+        }
+      }
+      fence_async_smem();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(smem_u32(&h_ready[b]));
+      // ---- epi-C: out = ELU(D_C + b1 + y)
+      const bf16* raw = P.raw + ((size_t)i * P.T + (valid ? ts : 0)) * C + hh * (C / 2);
+      bf16* dst = P.out + ((size_t)i * (P.out_hist + P.T) + P.out_hist + (valid ? ts : 0)) * C + hh * (C / 2);
+      mbar_wait(&dc_full[b], par);
+      tc_fence_after();
+#pragma unroll
+      for (int c0 = 0; c0 < C / 2; c0 += 32) {
+        float v[32], y[32];
+        tmem_ld<32>(t_lane + b * TM_STRIDE + TM_DC + hh * (C / 2) + c0, v);
+        if (valid) {
+          row_load<32>(raw + c0, y);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = elu_call(v[j] + P.b1[hh * (C / 2) + c0 + j] + y[j]);
+          row_store<32>(dst + c0, v);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(smem_u32(&tmem_free[b]));
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TM_COLS) : "memory");
+  }
+}
+
+bool seanet_resblock_fused_supported(int C, int hid, int hid_padded, int res_kernel) {
+  return (C == 128 || C == 256) && hid * 2 == C && hid_padded == hid && res_kernel == 3;
+}
+
+// e_buf [n][2 + T][C] (ELU(y) behind two history rows), raw [n][T][C], w3 [C/2][3C], w1 [C][C/2]; out [n][out_hist + T][C]
+template <int C, int NBUF>
+static cudaError_t launch_resblock_t(const bf16* e_buf, const bf16* raw, const bf16* w3, const bf16* w1, const float* b3, const float* b1,
+                                     bf16* out, int out_hist, int n, int T, int n_sms, bool pdl, cudaStream_t st) {
+  constexpr int HP = C / 2;
+  CUtensorMap ta, tw3, tw1;
+  if (!tc_make_map(&ta, e_buf, (long long)n * (2 + T) - 2, 3 * C, C, 128)) return cudaErrorUnknown;
+  if (!tc_make_map(&tw3, w3, HP, 3 * C, 3 * C, HP)) return cudaErrorUnknown;
+  if (!tc_make_map(&tw1, w1, C, HP, HP, C)) return cudaErrorUnknown;
+  ResBlockParams P{};
+  P.n = n; P.T = T;
+  P.tiles_per_stream = (T + 127) / 128;
+  P.n_tiles = n * P.tiles_per_stream;
+  for (int j = 0; j < HP; ++j) P.b3[j] = b3[j];
+  for (int j = 0; j < C; ++j) P.b1[j] = b1[j];
+  P.raw = raw; P.out = out; P.out_hist = out_hist;
+  constexpr int STAGES = C == 128 ? 4 : 3, HKB = HP / 64;
+  const size_t smem = (size_t)STAGES * (128 * 128 + HP * 128) + (size_t)NBUF * HKB * 16384 + (size_t)HKB * C * 128 + 1024;
+  auto kern = seanet_resblock_fused_kernel<C, NBUF>;
+  static DeviceOnce attr_done;
+  if (attr_done.first()) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(P.n_tiles < n_sms ? P.n_tiles : n_sms, 1, 1);
+  cfg.blockDim = dim3(FS_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, ta, tw3, tw1, P);
+}
+
+cudaError_t launch_seanet_resblock_fused(int C, const bf16* e_buf, const bf16* raw, const bf16* w3, const bf16* w1, const float* b3_host,
+                                         const float* b1_host, bf16* out, int out_hist, int n, int T, int n_sms, bool pdl, cudaStream_t st) {
+  if (n <= 0 || T <= 0) return cudaSuccess;
+  if (C == 128) return launch_resblock_t<128, 2>(e_buf, raw, w3, w1, b3_host, b1_host, out, out_hist, n, T, n_sms, pdl, st);
+  if (C == 256) return launch_resblock_t<256, 1>(e_buf, raw, w3, w1, b3_host, b1_host, out, out_hist, n, T, n_sms, pdl, st);
+  return cudaErrorInvalidValue;
+}
+
 }  // namespace ptts
