@@ -454,14 +454,14 @@ def run_cfg5(args, rank, world, local_rank):
     limits = [rnd.randint(117, 234) for _ in range(R)]
     states = [voices[r % NV] for r in range(R)]
     # warm-up: captures the graphs of the full batch and touches every kernel module
-    m.generate_audio_batch(states, [t[:1] for t in texts], frame_limits=[12] * R)
+    m.generate_audio_batch(states, [t[:1] for t in texts], frame_limits=[2 * args.block] * R, block=args.block)
     sampler = ClockSampler(local_rank)
     sampler.start()
     if dist:
         td.barrier()
     launches0 = m.engine.launch_count
     t0 = time.perf_counter()
-    out = m.generate_audio_batch(states, texts, frame_limits=limits)
+    out = m.generate_audio_batch(states, texts, frame_limits=limits, block=args.block)
     wall = time.perf_counter() - t0
     clocks = sampler.stop()
     st = m.last_batch_stats
@@ -514,7 +514,7 @@ def run_cfg5(args, rank, world, local_rank):
         "e2e": {"value": round(value, 1), "unit": "audio-s/s", "h2d_bytes_per_step": S * dims.ldim * 4,
                 "d2h_bytes_per_step": S * (4 + dims.frame_samples * 4), "ms_per_step": round(ms_per_step, 4),
                 "api": "TTSModel.generate_audio_batch: token ids and noise from host tensors, PCM and EOS logits back to pinned host "
-                       "memory every block of 8 frames; the whole call is the timed region (value == e2e: there is no device-only form)"},
+                       f"memory every block of {args.block} frames; the whole call is the timed region (value == e2e: there is no device-only form)"},
         "host_split": {"generate_frames_s": round(st["engine_s"], 3), "prefill_tokens_s": round(st["prefill_s"], 3), "call_s": round(st["total_s"], 3)},
         "first_chunk": {"batch_admission_to_first_block_p50_ms": pct(0.5), "batch_admission_to_first_block_p95_ms": pct(0.95),
                         "chunks": st["chunks"], "voice_prompt_encode_and_prefill_ms": round(voice_ms, 2), **first},
@@ -654,6 +654,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--block", type=int, default=8, help="cfg5: frames per engine call of the batch scheduler")
     ap.add_argument("--kv", default="act", choices=["act", "fp8"],
                     help="FlowLM KV cache storage: the activation type (default) or FP8 e4m3 with per-row scales (bf16 mode)")
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg5"],

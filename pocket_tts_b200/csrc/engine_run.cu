@@ -188,7 +188,8 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
     PTTS_CUDA_CHECK(cudaEventRecord(ev_side_join, side_stream));
   }
   LAUNCH("flow.embed", launch_flow_embed(prev_latent, d_slot_ids, bos_emb, w_in, h, n, D, Ld, stream));
-  const bool ln_fold = use_ln_fold && act_type == 1 && use_tc && n <= 128 && D % 64 == 0;
+  static const int ln_fold_max = [] { const char* e = getenv("PTTS_LNFOLD_MAX"); return e ? std::min(atoi(e), 128) : 128; }();   // measured at 256 rows: +1.8 % for the fold, -4 % for the ring stage its statistics table costs
+  const bool ln_fold = use_ln_fold && act_type == 1 && use_tc && n <= ln_fold_max && D % 64 == 0;
   for (int l = 0; l < c.n_layers; ++l)
     if ((rc = ln_fold ? flow_layer_decode_folded(l, n)
                       : transformer_layer_common(flow_layers[l], h, n, D, c.ffn, a_ln, qkv, attn_o, mid, false, l, n)) != PTTS_OK)

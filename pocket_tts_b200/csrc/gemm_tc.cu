@@ -359,7 +359,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant
   __shared__ __align__(8) uint64_t empty_bar[MAX_STAGES];
   __shared__ __align__(8) uint64_t tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
-  __shared__ float2 ln_stat[SWAP ? (BN < 128 ? BN : 128) : 1];   // folded LayerNorm: (mean, rstd) per operand row (M <= 128)
+  __shared__ float2 ln_stat[SWAP ? (BN < 128 ? BN : 128) : 1];   // folded LayerNorm: (mean, rstd) per operand row (M <= 128: a 256-row table would push the 256-stream GEMMs, whose slab is 128 KB, from 2 ring stages to 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (warp == 2) TC_TRACE(4);
@@ -713,7 +713,12 @@ static cudaError_t launch_cfg(const CUtensorMap& tr, const CUtensorMap& tc, cons
   static DeviceOnce attr_done;
   auto kern = gemm_tc_kernel<BN, SWAP, TO>;
   if (attr_done.first()) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_LIMIT + 1024);
+    // opt-in limit is 227 KB for static + dynamic together: the static part (barriers, LayerNorm statistics) varies with BN
+    cudaFuncAttributes fa{};
+    cudaError_t e = cudaFuncGetAttributes(&fa, kern);
+    if (e != cudaSuccess) return e;
+    const int dyn_max = std::min((int)TC_SMEM_LIMIT + 1024, 232448 - (int)fa.sharedSizeBytes);
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, dyn_max);
     if (e != cudaSuccess) return e;
     prefer_max_smem_carveout(reinterpret_cast<const void*>(kern));
   }

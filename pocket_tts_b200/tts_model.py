@@ -260,8 +260,8 @@ class TTSModel:
             raise ValueError("this model was built without a tokenizer; pass token ids instead of text")
         return self.tokenizer
 
-    def _buffers(self, n: int, F: int):
-        key = (n, F)
+    def _buffers(self, n: int, F: int, rot: int = 0):
+        key = (n, F, rot)
         if key not in self._outs:
             if len(self._outs) > 64:
                 self._outs.clear()
@@ -531,6 +531,10 @@ class TTSModel:
         admitted: list = []
         t_engine = t_prefill = 0.0
         t_call = _time.perf_counter()
+        from concurrent.futures import ThreadPoolExecutor
+        copier = ThreadPoolExecutor(max_workers=1)
+        pending = [None, None, None]
+        n_blocks = 0
         try:
             for st in model_states:          # one resident slot per distinct voice state
                 if id(st) not in voices:
@@ -574,11 +578,18 @@ class TTSModel:
                         nz[:, i] = j.noise[j.done:j.done + F] if j.noise is not None else self._draw_noise(F)
                 else:
                     nz = self._draw_noise(F * n).view(F, n, self.cfg.ldim)   # one draw for the whole block
+                # three sets of pinned result buffers in rotation: the copy of block k out of its buffer runs on a helper
+                # thread (memcpy releases the GIL) beside the GPU's block k+1; a buffer is reused only after its copy
+                rot = n_blocks % 3
+                n_blocks += 1
+                if pending[rot] is not None:
+                    pending[rot].result()
                 _t = _time.perf_counter()
-                pcm, _, eos = eng.generate_frames([j.slot for j in active], nz, out=self._buffers(n, F),
+                pcm, _, eos = eng.generate_frames([j.slot for j in active], nz, out=self._buffers(n, F, rot),
                                                   want_latents=False)
                 t_engine += _time.perf_counter() - _t
-                pcm = pcm.clone()                      # one copy out of the reusable pinned buffer; jobs keep views
+                eos = eos.clone()
+                pcm = pending[rot] = copier.submit(pcm.clone)     # jobs keep (future, row, samples) and resolve it at the end
                 hit = eos > self.eos_threshold         # [F, n]; EOS bookkeeping of tts_model.py:761-764 for the block
                 any_hit, first_hit = hit.any(dim=0).tolist(), hit.to(torch.int8).argmax(dim=0).tolist()
                 still = []
@@ -588,7 +599,7 @@ class TTSModel:
                         j.limit = min(j.max_gen_len, j.eos_step + j.frames_after_eos)
                     upto = min(j.done + F, j.target())
                     if upto > j.done:
-                        j.pcm.append(pcm[i, : (upto - j.done) * fs])
+                        j.pcm.append((pcm, i, (upto - j.done) * fs))
                         if j.t_first is None:
                             j.t_first = _time.perf_counter()
                     j.done += F
@@ -599,11 +610,15 @@ class TTSModel:
                         still.append(j)
                 active = still
         finally:
+            copier.shutdown(wait=True)
             for j in active + admitted:
                 if j.slot >= 0:
                     eng.close_stream(j.slot)
             for v in temp_voices:
                 eng.close_stream(v)
+        for jobs in per_request:             # resolve the block copies into per-job views
+            for j in jobs:
+                j.pcm = [fut.result()[row, :ns] for fut, row, ns in j.pcm]
         lat = sorted((j.t_first - j.t_admit) * 1e3 for jobs in per_request for j in jobs if j.t_first is not None)
         self.last_batch_stats = {"chunks": len(lat), "first_block_ms": lat, "engine_s": t_engine, "prefill_s": t_prefill,
                                  "total_s": _time.perf_counter() - t_call,
