@@ -623,6 +623,11 @@ cudaError_t launch_attn_decode(const float* qkv, const float* rope_freqs, const 
   return cudaGetLastError();
 }
 
+}  // namespace ptts
+#include "attn_window_mma.cuh"
+#include "attn_prefill_mma.cuh"
+namespace ptts {
+
 // =====================================================================================
 // chunk: len[i] new positions per stream (prefill, Mimi's 16 tokens per frame).
 // grid (H, n), 256 threads.  Phase 1 rotates q in place and appends rotated k / v;
@@ -708,7 +713,16 @@ cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* of
   // chunks longer than one query per warp: an append pass, then an attend pass with one warp per query
   static const bool split_on = [] { const char* e = getenv("PTTS_PREFILL_SPLIT"); return !(e && e[0] == '0'); }();
   const bool split = split_on && max_len > 8 && !kv.ring;
+  // bf16 chunks of 16 tokens and more: the attend pass runs on the tensor cores (attn_prefill_mma.cuh); PTTS_PREFILL_MMA=0
+  // keeps the one-warp-per-query form
+  static const bool mma_on = [] { const char* e = getenv("PTTS_PREFILL_MMA"); return !(e && e[0] == '0'); }();
+  const bool mma = mma_on && split && max_len >= 16 && kv.type == 1 && out_type == 1;
   for (int pass = split ? 1 : 0; pass <= (split ? 2 : 0); ++pass) {
+    if (pass == 2 && mma) {
+      launch_k(attn_prefill_mma_kernel, dim3(kv.H, n, (max_len + 63) / 64), 128, 0, st, (const float*)qkv, offsets, slot_ids, row_start, lens,
+               kv, layer, (bf16*)out);
+      break;
+    }
     dim3 grid(kv.H, n, pass == 2 ? (max_len + 7) / 8 : 1);
     if (kv.type == 0 && out_type == 0)
       launch_k(attn_chunk_kernel<float, float>, grid, 256, 0, st, qkv, rope_freqs, offsets, slot_ids, row_start, lens, kv, layer, context, (float*)out, pass);
@@ -878,7 +892,6 @@ attn_window_kernel(const float* __restrict__ qkv, const float* __restrict__ freq
 }
 
 }  // namespace ptts
-#include "attn_window_mma.cuh"
 namespace ptts {
 
 cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets, const int* slot_ids,
