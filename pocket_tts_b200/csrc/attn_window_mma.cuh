@@ -67,18 +67,34 @@ attn_window_mma_kernel(const float* __restrict__ qkv, const float* __restrict__ 
   // ---- the pass's own tokens: rotate, round, stage, append to the ring; q rotated and staged
   {
     const float fr = freqs[lane];
-    for (int t = w; t < NQ; t += WM_THREADS / 32) {
-      const float* row = qkv + (long long)(r_pass + t) * 3 * d_model + h * 64 + 2 * lane;
-      const float pos = (float)(off0 + t);
-      const float2 q = rope_pair(load2(row), pos, fr);
-      const float2 k = rope_pair(load2(row + d_model), pos, fr);
-      const float2 v = load2(row + 2 * d_model);
-      const uint32_t kb = pack_bf16(k.x, k.y), vb = pack_bf16(v.x, v.y);
-      reinterpret_cast<uint32_t*>(Qs + t * WM_LD)[lane] = pack_bf16(q.x, q.y);
-      reinterpret_cast<uint32_t*>(Ks + (n_ring + t) * WM_LD)[lane] = kb;
-      reinterpret_cast<uint32_t*>(Vs + (n_ring + t) * WM_LD)[lane] = vb;
-      reinterpret_cast<uint32_t*>(kv_row<bf16>(g, layer, slot, 0, h, off0 + t))[lane] = kb;
-      reinterpret_cast<uint32_t*>(kv_row<bf16>(g, layer, slot, 1, h, off0 + t))[lane] = vb;
+    // a warp takes tokens w, w + 4, ...: the three projection rows of FOUR tokens are requested before the first is
+    // used (one token per iteration was 16 serial global round trips per CTA at 64 tokens, the longest phase of the kernel)
+    constexpr int TB = 4, WARPS = WM_THREADS / 32;
+    for (int t0 = w; t0 < NQ; t0 += TB * WARPS) {
+      float2 qv[TB], kv[TB], vv[TB];
+#pragma unroll
+      for (int u = 0; u < TB; ++u) {
+        const int t = t0 + u * WARPS;
+        if (t < NQ) {
+          const float* row = qkv + (long long)(r_pass + t) * 3 * d_model + h * 64 + 2 * lane;
+          qv[u] = load2(row); kv[u] = load2(row + d_model); vv[u] = load2(row + 2 * d_model);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < TB; ++u) {
+        const int t = t0 + u * WARPS;
+        if (t < NQ) {
+          const float pos = (float)(off0 + t);
+          const float2 q = rope_pair(qv[u], pos, fr);
+          const float2 k = rope_pair(kv[u], pos, fr);
+          const uint32_t kb = pack_bf16(k.x, k.y), vb = pack_bf16(vv[u].x, vv[u].y);
+          reinterpret_cast<uint32_t*>(Qs + t * WM_LD)[lane] = pack_bf16(q.x, q.y);
+          reinterpret_cast<uint32_t*>(Ks + (n_ring + t) * WM_LD)[lane] = kb;
+          reinterpret_cast<uint32_t*>(Vs + (n_ring + t) * WM_LD)[lane] = vb;
+          reinterpret_cast<uint32_t*>(kv_row<bf16>(g, layer, slot, 0, h, off0 + t))[lane] = kb;
+          reinterpret_cast<uint32_t*>(kv_row<bf16>(g, layer, slot, 1, h, off0 + t))[lane] = vb;
+        }
+      }
     }
     // rows of the last key block past the window: finite values (their probabilities are zero)
     for (int idx = threadIdx.x; idx < (Wp - W) * 32; idx += WM_THREADS) {

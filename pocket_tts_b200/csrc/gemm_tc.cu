@@ -61,6 +61,17 @@ struct TcParams {
 };
 #define TC_TRACE(slot) do { if (P.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0) P.trace[slot] = clock64(); } while (0)
 
+// developer trace of CTA 0 (profiles/probes/gemm_rows_bench.cu defines TC_ROWS_TRACE and the buffer): SM clock stamps per tile
+#ifdef TC_ROWS_TRACE
+__device__ long long g_rows_trace[16 + 8 * 32];
+__device__ long long g_epi_trace[16 * 32];
+__device__ int g_epi_tile;
+#define EPI_TRACE(k) do { if (blockIdx.x == 0 && threadIdx.x == 64 && g_epi_tile < 32) g_epi_trace[g_epi_tile * 16 + (k)] = clock64(); } while (0)
+#define ROWS_TRACE(t, k) do { if (blockIdx.x == 0 && lane == 0 && (t) < 32) g_rows_trace[16 + (t) * 8 + (k)] = clock64(); } while (0)
+#else
+#define ROWS_TRACE(t, k) do { } while (0)
+#define EPI_TRACE(k) do { } while (0)
+#endif
 // Row-major epilogue (SWAP = false).  TMEM hands every thread one output ROW, but global memory
 // wants consecutive lanes on consecutive COLUMNS: each epilogue warp therefore stages its
 // 32 rows x CH columns chunk in shared memory (padded, conflict free both ways) and re-reads it
@@ -68,7 +79,7 @@ struct TcParams {
 // out / out2 stores are row-contiguous 16-byte accesses.  Per-row addresses (the RowMaps) are
 // computed once per row into shared memory.
 struct RowMeta {
-  long long out, res, out2;   // element offsets, out < 0: row not written
+  long long out, res, out2, pad;   // element offsets, out < 0: row not written (32 bytes: two 16-byte shared accesses)
 };
 constexpr int EPI_STAGE_FLOATS = 32 * 36;                     // per warp
 constexpr size_t EPI_SMEM_BYTES = 8 * EPI_STAGE_FLOATS * 4 + BM_TC * sizeof(RowMeta);
@@ -81,11 +92,13 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, int M, int
   constexpr int LD = CH + 4;
   constexpr int LPR = CH / 8;          // lanes per row when re-reading
   constexpr int RPI = 32 / LPR;        // rows per iteration
-  RowMeta* meta = reinterpret_cast<RowMeta*>(scratch + 8 * EPI_STAGE_FLOATS * 4);
-  float* stage = reinterpret_cast<float*>(scratch) + (q + 4 * half) * EPI_STAGE_FLOATS;
+  // shared memory by 32-bit address (LDS / STS; through the generic `scratch` pointer these were LD.E / ST.E)
+  const uint32_t scratch_a = smem_u32(scratch);
+  const uint32_t meta_a = scratch_a + 8u * EPI_STAGE_FLOATS * 4u;
+  const uint32_t stage_a = scratch_a + (uint32_t)(q + 4 * half) * (EPI_STAGE_FLOATS * 4u);
   if (half == 0) {
     const int rl = q * 32 + lane, r = row0 + rl;
-    RowMeta mt{-1, 0, 0};
+    RowMeta mt{-1, 0, 0, 0};
     if (r < M) {
       const int ob = r / ep.out_map.rows_per_batch, ot = r - ob * ep.out_map.rows_per_batch;
       if (ot < ep.out_map.valid_rows) {
@@ -100,9 +113,12 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, int M, int
         }
       }
     }
-    meta[rl] = mt;
+    sts2l(meta_a + (uint32_t)rl * 32u, mt.out, mt.res);
+    sts2l(meta_a + (uint32_t)rl * 32u + 16u, mt.out2, 0);
   }
+  EPI_TRACE(0);
   asm volatile("bar.sync 1, 256;" ::: "memory");   // the 8 epilogue warps
+  EPI_TRACE(1);
   const int sub = lane / LPR, cg = lane % LPR;
 #pragma unroll 1
   for (int ci = half; ci < NCH; ci += 2) {
@@ -111,10 +127,12 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, int M, int
     {
       float v[CH];
       tmem_ld<CH>(taddr + c, v);   // warp-collective
+      EPI_TRACE(2 + 3 * (ci >> 1));
 #pragma unroll
-      for (int j = 0; j < CH; j += 4) *reinterpret_cast<float4*>(stage + lane * LD + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      for (int j = 0; j < CH; j += 4) sts4f(stage_a + (uint32_t)(lane * LD + j) * 4u, make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]));
     }
     __syncwarp();
+    EPI_TRACE(3 + 3 * (ci >> 1));
     const int n = n0 + cg * 8;
     float bias[8], cs[8];
     if (ep.bias) row_load<8>(ep.bias + n, bias);
@@ -122,10 +140,15 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, int M, int
 #pragma unroll
     for (int it = 0; it < LPR; ++it) {
       const int rl = q * 32 + it * RPI + sub;
-      const RowMeta mt = meta[rl];
+      RowMeta mt;
+      lds2l(meta_a + (uint32_t)rl * 32u, mt.out, mt.res);
       if (mt.out >= 0) {
         float x[8], t[8];
-        row_load<8>(stage + (it * RPI + sub) * LD + cg * 8, x);
+        {
+          const uint32_t xa = stage_a + (uint32_t)((it * RPI + sub) * LD + cg * 8) * 4u;
+          const float4 x0 = lds4f(xa), x1 = lds4f(xa + 16u);
+          x[0] = x0.x; x[1] = x0.y; x[2] = x0.z; x[3] = x0.w; x[4] = x1.x; x[5] = x1.y; x[6] = x1.z; x[7] = x1.w;
+        }
         if (ep.bias) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) x[j] += bias[j];
@@ -149,12 +172,17 @@ __device__ __forceinline__ void epilogue_rows(const GemmEpilogue& ep, int M, int
 #pragma unroll
           for (int j = 0; j < 8; ++j) x[j] += t[j];
         }
-        if (ep.out2) row_store<8>(reinterpret_cast<TO*>(ep.out2) + mt.out2 + n, x);
+        if (ep.out2) {
+          long long pad;
+          lds2l(meta_a + (uint32_t)rl * 32u + 16u, mt.out2, pad);
+          row_store<8>(reinterpret_cast<TO*>(ep.out2) + mt.out2 + n, x);
+        }
         act_inplace<8>(x, ep.act_post);
         row_store<8>(reinterpret_cast<TO*>(ep.out) + mt.out + n, x);
       }
     }
     __syncwarp();
+    EPI_TRACE(4 + 3 * (ci >> 1));
   }
 }
 
@@ -581,15 +609,19 @@ gemm_tc_rows_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
   const uint32_t tmem_base = tmem_base_smem;
   const uint32_t tiles_a = smem_u32(tiles), full_a = smem_u32(&full_bar[0]), empty_a = smem_u32(&empty_bar[0]);
   const uint32_t tfull_a = smem_u32(&tfull_bar[0]), tempty_a = smem_u32(&tempty_bar[0]);
+#ifdef TC_ROWS_TRACE
+  if (blockIdx.x == 0 && threadIdx.x == 0) g_rows_trace[0] = clock64();
+#endif
 
   if (warp == 0) {
     // ===== TMA producer =====
-    uint32_t s = 0, ph = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+    uint32_t s = 0, ph = 0, tt = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tt) {
       const int mt = tile / P.tiles_n, nt = tile - mt * P.tiles_n;
       const int row0 = mt * BM_TC, col0 = nt * BN;
       for (int kb = 0; kb < P.num_kb; ++kb) {
         mbar_wait_a(empty_a + 8u * s, ph ^ 1u);
+        if (kb == 0) ROWS_TRACE(tt, 0); else if (kb == P.num_kb - 1) ROWS_TRACE(tt, 1);
         if (lane == 0) {
           const uint32_t st = tiles_a + s * STAGE_BYTES, fb = full_a + 8u * s;
           mbar_expect_tx_a(fb, STAGE_BYTES);
@@ -609,10 +641,12 @@ gemm_tc_rows_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       const uint32_t buf = t & 1u, use = t >> 1;
       mbar_wait_a(tempty_a + 8u * buf, (use & 1u) ^ 1u);   // epilogue drained this accumulator (first use: passes)
       tc_fence_after();
+      ROWS_TRACE(t, 2);
       const uint32_t d_tmem = tmem_base + buf * BN;
       for (int kb = 0; kb < P.num_kb; ++kb) {
         mbar_wait_a(full_a + 8u * s, ph);
         tc_fence_after();
+        if (kb == 0) ROWS_TRACE(t, 3); else if (kb == P.num_kb - 1) ROWS_TRACE(t, 4);
         if (lane == 0) {
           const uint64_t soff = (uint64_t)((s * STAGE_BYTES) >> 4);
           const uint64_t adesc = adesc0 + soff, bdesc = bdesc0 + soff;
@@ -635,11 +669,16 @@ gemm_tc_rows_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_const
       const int mt = tile / P.tiles_n, nt = tile - mt * P.tiles_n;
       mbar_wait_a(tfull_a + 8u * buf, use & 1u);
       tc_fence_after();
+      if (warp == 2) ROWS_TRACE(t, 5);
       const uint32_t taddr = tmem_base + buf * BN + ((uint32_t)(q * 32) << 16);
       asm volatile("bar.sync 1, 256;" ::: "memory");   // previous tile's row metadata no longer in use
       epilogue_rows<BN, TO>(ep, P.M, P.N, taddr, mt * BM_TC, nt * BN, q, half, lane, scratch);
       tc_fence_before();
       __syncwarp();
+      if (warp == 2) ROWS_TRACE(t, 6);
+#ifdef TC_ROWS_TRACE
+      if (blockIdx.x == 0 && threadIdx.x == 64) ++g_epi_tile;
+#endif
       if (lane == 0) mbar_arrive_a(tempty_a + 8u * buf);
     }
   }

@@ -97,6 +97,28 @@ __device__ __forceinline__ void dsmem_st(uint32_t addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 __device__ __forceinline__ float4 ld4f(const float* p) { return *reinterpret_cast<const float4*>(p); }
+// Explicit shared-window accesses by 32-bit address.  A float* derived from a uint8_t* scratch argument is a GENERIC
+// pointer to the compiler: it emits LD.E / ST.E, which resolve the window at run time and cost the row-major epilogue
+// ~600 clk per 8-row pass (clock trace, profiles/r02_rows_gemm_epilogue_trace.txt); LDS / STS do not.
+__device__ __forceinline__ float4 lds4f(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float2 lds2f(uint32_t a) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts4f(uint32_t a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void lds2l(uint32_t a, long long& x, long long& y) {
+  asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "r"(a));
+}
+__device__ __forceinline__ void sts2l(uint32_t a, long long x, long long y) {
+  asm volatile("st.shared.v2.b64 [%0], {%1, %2};" ::"r"(a), "l"(x), "l"(y) : "memory");
+}
 
 // ---- TMEM -> registers: CH consecutive fp32 columns of this thread's lane
 template <int CH> __device__ __forceinline__ void tmem_ld(uint32_t taddr, float* v);

@@ -2,6 +2,9 @@
 // frames: the decoder transformer's four linears and the SEANet convolutions as overlapping-row GEMMs.  Includes
 // the product kernel source directly, so it times exactly what the engine launches.
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 --expt-relaxed-constexpr -o gemm_rows_bench.bin gemm_rows_bench.cu
+#ifdef ROWS_TRACE_BUILD   // -DROWS_TRACE_BUILD: per-tile SM clock stamps of CTA 0 (producer / MMA issuer / epilogue), printed per shape
+#define TC_ROWS_TRACE 1
+#endif
 #include "../../pocket_tts_b200/csrc/gemm_tc.cu"
 
 #include <vector>
@@ -81,6 +84,33 @@ int main(int argc, char** argv) {
     const long long valid_rows = plainA ? M : (long long)s.streams * s.valid;
     const double tf = 2.0 * valid_rows * s.N * s.K / (us * 1e-6) / 1e12;
     printf("%-20s M %7lld N %5d K %5d: %7.1f us  %7.1f TFLOP/s\n", s.name, M, s.N, s.K, us, tf);
+#ifdef TC_ROWS_TRACE
+    {
+      static long long h[16 + 8 * 32];
+      cudaMemcpyFromSymbol(h, g_rows_trace, sizeof h);
+      const long long t0 = h[0];
+      for (int t = 0; t < 32 && h[16 + t * 8 + 5]; ++t) {
+        const long long* r = h + 16 + t * 8;
+        printf("   tile %d (clk since start): load first/last issue %6lld %6lld | mma acc-free %6lld first-operands %6lld last-kb %6lld | epi acc-ready %6lld done %6lld\n",
+               t, r[0] - t0, r[1] - t0, r[2] - t0, r[3] - t0, r[4] - t0, r[5] - t0, r[6] - t0);
+      }
+      static long long e[16 * 32];
+      int ntile = 0;
+      cudaMemcpyFromSymbol(e, g_epi_trace, sizeof e);
+      cudaMemcpyFromSymbol(&ntile, g_epi_tile, sizeof ntile);
+      for (int t = 0; t < 2 && t < ntile; ++t) {
+        const long long* r = e + t * 16;
+        printf("   epilogue of launch-tile %d, warp 2 (clk): entry 0 | tables+barrier %lld | chunk A: tmem_ld %lld staged %lld rows done %lld | chunk B: tmem_ld %lld staged %lld rows done %lld\n",
+               t, r[1] - r[0], r[2] - r[0], r[3] - r[0], r[4] - r[0], r[5] - r[0], r[6] - r[0], r[7] - r[0]);
+      }
+      static long long z[16 + 8 * 32];
+      static long long ze[16 * 32];
+      const int zero = 0;
+      cudaMemcpyToSymbol(g_rows_trace, z, sizeof z);
+      cudaMemcpyToSymbol(g_epi_trace, ze, sizeof ze);
+      cudaMemcpyToSymbol(g_epi_tile, &zero, sizeof zero);
+    }
+#endif
     total += us;
     cudaFree(A); cudaFree(W); cudaFree(out); cudaFree(res); cudaFree(bias);
   }
