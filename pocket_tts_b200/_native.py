@@ -4,11 +4,13 @@ shared library is missing or fails to load, importing this module raises."""
 from __future__ import annotations
 
 import ctypes as C
+import os
 import re
 from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "libpocket_tts_b200.so"
+# PTTS_NATIVE_LIB: developer override, an alternative build of the same library (A/B timing of compile-time choices)
+LIB_PATH = Path(os.environ["PTTS_NATIVE_LIB"]) if os.environ.get("PTTS_NATIVE_LIB") else HERE / "libpocket_tts_b200.so"
 HEADER = HERE.parent / "include" / "pocket_tts_b200.h"
 
 PTTS_OK, PTTS_EINVAL, PTTS_ECUDA, PTTS_ESTATE, PTTS_ENOSLOT = 0, -1, -2, -3, -4

@@ -100,6 +100,8 @@ Engine::~Engine() {
   if (ev_fork) cudaEventDestroy(ev_fork);
   if (ev_join) cudaEventDestroy(ev_join);
   for (int k = 0; k < 2; ++k) {
+    for (int j = 0; j < 8; ++j)
+      if (ev_head[k][j]) cudaEventDestroy(ev_head[k][j]);
     for (cudaEvent_t e : {ev_lat[k], ev_mimi[k], ev_copied_lat[k], ev_copied_pcm[k]})
       if (e) cudaEventDestroy(e);
   }
@@ -178,6 +180,7 @@ int Engine::init() {
   }
   if (const char* f = getenv("PTTS_KV_SIDE")) use_kv_side_prefetch = f[0] == '1';
   if (const char* f = getenv("PTTS_LNFOLD")) use_ln_fold = !(f[0] == '0');
+  if (const char* f = getenv("PTTS_HEAD_GATE")) use_head_gate = f[0] == '1';
   if (const char* f = getenv("PTTS_SEANET_FUSED")) use_fused_stage2 = !(f[0] == '0');
   if (const char* f = getenv("PTTS_FUSED_SMS")) fused_sms = atoi(f);
   if (const char* f = getenv("PTTS_RESBLOCK_FUSED")) use_fused_resblock = !(f[0] == '0');
@@ -185,6 +188,7 @@ int Engine::init() {
   for (int k = 0; k < 2; ++k) {
     for (cudaEvent_t* e : {&ev_lat[k], &ev_mimi[k], &ev_copied_lat[k], &ev_copied_pcm[k]})
       PTTS_CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    for (int j = 0; j < 8; ++j) PTTS_CUDA_CHECK(cudaEventCreateWithFlags(&ev_head[k][j], cudaEventDisableTiming));
   }
   act_type = c.precision == PTTS_PRECISION_BF16 ? 1 : 0;
   act_size = act_type ? 2 : 4;

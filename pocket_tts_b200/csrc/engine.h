@@ -104,6 +104,8 @@ struct GraphEntry {
   long long kernels = 0;
 };
 
+constexpr int MIMI_SEGS = 5;   // segments of a Mimi pass that can be captured separately (Engine::mimi_sequence)
+
 class Engine {
  public:
   explicit Engine(const ptts_config& c) : cfg(c) {}
@@ -177,7 +179,7 @@ class Engine {
   bool mega_eligible(int n) const;
   int mega_plan(int lsd, MegaPlan** out);
   int flow_sequence_mega(int n, int lsd, const float* noise, float* eos_out);
-  int mimi_sequence(int n, const float* latents, int frames = 1, float* pcm_out = nullptr);
+  int mimi_sequence(int n, const float* latents, int frames = 1, float* pcm_out = nullptr, int seg_lo = 0, int seg_hi = MIMI_SEGS - 1);
   int frame(int n, int lsd, int audio);  // eager or graph
   // FlowLM + head of the current frame on `stream` in parallel with the Mimi decode of the previous
   // frame's latents on `stream2` (two branches of one graph), like the reference's decoder thread
@@ -185,6 +187,7 @@ class Engine {
   int launch_captured(const GraphKey& key, cudaStream_t on, const std::function<int()>& body);
   int flow_graph(int n, int lsd, int par, int j);
   int mimi_graph(int n, int g, int par);
+  int mimi_graph_gated(int n, int g, int par, int gate_par);
   int group_graph(int n, int lsd, int parity, int g_flow, int g_mimi);
   void* act_alloc(size_t elems);
   // ResBlock hidden width as stored (bf16 mode pads to a multiple of 64 channels)
@@ -290,6 +293,13 @@ class Engine {
   int head_mode = 3;                         // PTTS_HEAD: 0 flow head as separate launches (A/B reference), 2 feature-split 8-CTA cluster kernel on tcgen05 (flow_head_tc.cu), 3 stream-split kernel without cross-CTA exchange (flow_head_ss.cu, default); the first cluster form on mma.sync (1) was retired in round 2
   cudaStream_t copy_stream = nullptr;        // result copies of run_frames ride beside the next group's graph
   cudaEvent_t ev_lat[2] = {}, ev_mimi[2] = {}, ev_copied_lat[2] = {}, ev_copied_pcm[2] = {};
+  // Head-gated Mimi passes: ev_head[par][j] is recorded inside the FlowLM graph of frame slot j of the
+  // group with parity par when its flow head starts (8 SMs busy, 140 idle for ~65 us); the SEANet segments of the
+  // previous group's Mimi pass - the kernels that fill whole SMs - wait for those events instead of colliding with the
+  // transformer layers of the chain.
+  cudaEvent_t ev_head[2][8] = {};
+  cudaEvent_t gate_record = nullptr;         // set around the capture of a FlowLM frame graph
+  bool use_head_gate = false;                // PTTS_HEAD_GATE=1
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)
   std::map<std::string, std::pair<const void*, std::pair<int, long long>>> debug_bufs;  // name -> (ptr,(type,elems per row unit))
 };

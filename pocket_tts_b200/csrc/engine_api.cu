@@ -416,9 +416,11 @@ int Engine::flow_graph(int n, int lsd, int par, int j) {
     if (prc != PTTS_OK) return prc;
   }
   const size_t fl = (size_t)n * cfg.ldim;
-  return launch_captured(GraphKey{n, lsd, 0, 2000 + j * 2 + par}, stream, [&]() -> int {
+  return launch_captured(GraphKey{n, lsd, 0, 2000 + j * 2 + par + (use_head_gate ? 100 : 0)}, stream, [&]() -> int {
     commit_out = lat_ring[par] + j * fl;
+    gate_record = use_head_gate && j < 8 ? ev_head[par][j] : nullptr;
     const int rc = flow_sequence(n, lsd, noise_grp + j * fl, eos_grp[par] + (size_t)j * n);
+    gate_record = nullptr;
     commit_out = nullptr;
     return rc;
   });
@@ -431,6 +433,30 @@ int Engine::mimi_graph(int n, int g, int par) {
   n_sms = n_sms_mimi;
   const int rc = launch_captured(GraphKey{n, 0, 1, 3000 + g * 2 + par}, stream2,
                                  [&]() -> int { return mimi_sequence(n, lat_ring[par], g, pcm_ring[par]); });
+  stream = main_stream;
+  n_sms = n_sms_flow;
+  return rc;
+}
+
+// Head-gated form of a full-size Mimi pass (group parity `par`, g frames): five graphs on stream2, the SEANet ones
+// each behind "the flow head of frame slot j of the NEXT group (parity gate_par) has started".  The caller has
+// already enqueued that group's FlowLM graphs, so the waits below refer to their event-record nodes.
+int Engine::mimi_graph_gated(int n, int g, int par, int gate_par) {
+  cudaStream_t main_stream = stream;
+  stream = stream2;
+  // the flow head keeps ceil(n / 8) SMs busy during the gated segments: persistent Mimi grids leave them alone
+  const int head_ctas = (n + 7) / 8;
+  int rc = PTTS_OK;
+  for (int seg = 0; seg < MIMI_SEGS && rc == PTTS_OK; ++seg) {
+    n_sms = seg == 0 ? n_sms_mimi : std::max(8, n_sms_mimi - head_ctas);
+    if (seg > 0) {
+      const int j = std::min(seg - 1, g - 1);
+      cudaError_t e = cudaStreamWaitEvent(stream2, ev_head[gate_par][j], 0);
+      if (e != cudaSuccess) { set_error(std::string("cudaStreamWaitEvent: ") + cudaGetErrorString(e)); rc = PTTS_ECUDA; break; }
+    }
+    rc = launch_captured(GraphKey{n, 0, 1, 5000 + g * 100 + seg * 2 + par}, stream2,
+                         [&]() -> int { return mimi_sequence(n, lat_ring[par], g, pcm_ring[par], seg, seg); });
+  }
   stream = main_stream;
   n_sms = n_sms_flow;
   return rc;
@@ -570,7 +596,26 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
     const bool copies = out_pcm_any || out_lat_any || out_eos;
     const bool do_mimi = part != 3;
     int f0 = 0;
-    bool used[2] = {false, false};
+    bool used[2] = {false, false}, used_pcm[2] = {false, false};
+    const bool gate_loop = use_head_gate && do_mimi && part == 0 && use_graphs && use_fused_stage2 && act_type == 1 && use_tc &&
+                           !mega_eligible(n) && head_mode != 0;
+    struct { bool valid = false; int g = 0, par = 0, f0 = 0; } pend;
+    auto enqueue_mimi = [&](int g, int par, int f0m, int gate_par) -> int {
+      int rc2;
+      PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_lat[par], 0));
+      if (copies && used_pcm[par]) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_copied_pcm[par], 0));
+      if ((rc2 = gate_par >= 0 ? mimi_graph_gated(n, g, par, gate_par) : mimi_graph(n, g, par)) != PTTS_OK) return rc2;
+      PTTS_CUDA_CHECK(cudaEventRecord(ev_mimi[par], stream2));
+      if (copies) {
+        PTTS_CUDA_CHECK(cudaStreamWaitEvent(copy_stream, ev_mimi[par], 0));
+        if (out_pcm_any)
+          PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_any + (size_t)f0m * fs, (size_t)n_frames * fs * sizeof(float), pcm_ring[par],
+                                            g * fs * sizeof(float), g * fs * sizeof(float), n, cudaMemcpyDefault, copy_stream));
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_copied_pcm[par], copy_stream));
+      }
+      used_pcm[par] = true;
+      return PTTS_OK;
+    };
     for (int k = 0; f0 < n_frames; ++k) {
       const int par = k & 1;
       const int want = k < 2 ? 1 : std::min(mimi_gmax, 1 << std::min(k - 1, 4));
@@ -597,21 +642,24 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
         PTTS_CUDA_CHECK(cudaEventRecord(ev_copied_lat[par], copy_stream));
       }
       if (do_mimi) {
-        PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_lat[par], 0));
-        if (copies && used[par]) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream2, ev_copied_pcm[par], 0));
-        if ((rc = mimi_graph(n, g, par)) != PTTS_OK) return rc;
-        PTTS_CUDA_CHECK(cudaEventRecord(ev_mimi[par], stream2));
-        if (copies) {
-          PTTS_CUDA_CHECK(cudaStreamWaitEvent(copy_stream, ev_mimi[par], 0));
-          if (out_pcm_any)
-            PTTS_CUDA_CHECK(cudaMemcpy2DAsync(out_pcm_any + (size_t)f0 * fs, (size_t)n_frames * fs * sizeof(float), pcm_ring[par],
-                                              g * fs * sizeof(float), g * fs * sizeof(float), n, cudaMemcpyDefault, copy_stream));
-          PTTS_CUDA_CHECK(cudaEventRecord(ev_copied_pcm[par], copy_stream));
+        // head-gated loop: the Mimi pass of a full-size group is enqueued one group late, behind the FlowLM graphs of
+        // the next group, whose flow-head events gate its SEANet segments; small groups (first chunks, tail) and the
+        // last group run ungated at once
+        if (pend.valid) {
+          const bool gated = g == pend.g;   // the next group has a head phase for every gated segment
+          if ((rc = enqueue_mimi(pend.g, pend.par, pend.f0, gated ? par : -1)) != PTTS_OK) return rc;
+          pend.valid = false;
+        }
+        if (gate_loop && g == mimi_gmax && g >= MIMI_SEGS - 1) {
+          pend.valid = true; pend.g = g; pend.par = par; pend.f0 = f0;
+        } else if ((rc = enqueue_mimi(g, par, f0, -1)) != PTTS_OK) {
+          return rc;
         }
       }
       used[par] = true;
       f0 += g;
     }
+    if (pend.valid && (rc = enqueue_mimi(pend.g, pend.par, pend.f0, -1)) != PTTS_OK) return rc;   // last group: nothing to gate on
     // the caller synchronises `stream`: make it wait for the Mimi passes and copies still in flight
     for (int q = 0; q < 2; ++q)
       if (used[q]) {

@@ -226,17 +226,35 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
       const bool last = s == lsd - 1;
       hp.prev_latent = last ? prev_latent : nullptr;
       hp.commit_out = last ? commit_out : nullptr;
+      const bool gate = gate_record != nullptr && s == 0 && side_stream != nullptr;
+      if (gate) {
+        // head-gated Mimi passes: "the flow head of this frame starts" as an external event record node on a side
+        // branch that hangs off the AdaLN modulation GEMM (the main branch keeps its programmatic edge to the head kernel)
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_side_fork, stream));
+        PTTS_CUDA_CHECK(cudaStreamWaitEvent(side_stream, ev_side_fork, 0));
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        PTTS_CUDA_CHECK(cudaStreamIsCapturing(stream, &cs));
+        if (cs == cudaStreamCaptureStatusActive) PTTS_CUDA_CHECK(cudaEventRecordWithFlags(gate_record, side_stream, cudaEventRecordExternal));
+        else PTTS_CUDA_CHECK(cudaEventRecord(gate_record, side_stream));
+        PTTS_CUDA_CHECK(cudaEventRecord(ev_side_join, side_stream));
+      }
+      auto join_gate = [&]() -> int {
+        if (gate) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_side_join, 0));
+        return PTTS_OK;
+      };
       if (head_mode == 3 && flow_head_ss_supported(F, Ld, c.flow_depth)) {
         FlowHeadTcParams tp;
         tp.h = hp;
         if (!flow_head_ss_prepare(&tp)) PTTS_FAIL(PTTS_ECUDA, "tensor map encode failed (flow head)");
         LAUNCH("head.cluster", launch_flow_head_ss(tp, stream));
+        if ((rc = join_gate()) != PTTS_OK) return rc;
       } else {
         FlowHeadTcParams tp;
         tp.h = hp;
         tp.xchg = head_l2_exchange ? head_xchg : nullptr;
         if (!flow_head_tc_prepare(&tp)) PTTS_FAIL(PTTS_ECUDA, "tensor map encode failed (flow head)");
         LAUNCH("head.cluster", launch_flow_head_tc(tp, stream));
+        if ((rc = join_gate()) != PTTS_OK) return rc;
       }
       continue;
     }
@@ -275,7 +293,12 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
 // Mimi decode of `frames` consecutive latents per stream, latents [frames][n, ldim] (device fp32) ->
 // pcm_out [n, frames * 1920].  One pass over frames * 16 tokens per stream is arithmetically the same as
 // `frames` single-frame passes (causal attention, causal convolutions with carried history).
-int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_out) {
+// Segments (seg_lo..seg_hi, default all; the head-gated loop captures them as separate graphs): 0 = upsample +
+// transformer + conv0, 1 = stage 0, 2 = stage 1, 3 = first half of the streams through the fused last stage,
+// 4 = second half + history write-back.  A whole pass runs the fused last stage as one launch.
+int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_out, int seg_lo, int seg_hi) {
+  auto in = [&](int seg) { return seg >= seg_lo && seg <= seg_hi; };
+  const bool whole = seg_lo <= 0 && seg_hi >= MIMI_SEGS - 1;
   const ptts_config& c = cfg;
   const int Md = c.mimi_d, U = c.upsample_stride * frames;
   int rc;
@@ -283,6 +306,7 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
   if (!pcm_out) pcm_out = pcm;
   HistTable tab = hist_tab;
   for (int k = 0; k < tab.count; ++k) tab.d[k].T *= frames;
+  if (in(0)) {
   {  // developer probe (PTTS_MIMI_PAD_NODES=k): k extra trivial kernel nodes per Mimi pass - measures what a graph node of the
      // Mimi branch costs the FlowLM chain through the shared launch front end
     static const int pad = [] { const char* e = getenv("PTTS_MIMI_PAD_NODES"); return e ? atoi(e) : 0; }();
@@ -294,12 +318,13 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
       return rc;
   LAUNCH("advance", launch_advance(mimi_offsets, d_slot_ids, nullptr, U, n, stream));
   LAUNCH("seanet.hist_gather", launch_hist_gather(tab, d_slot_ids, act_type, n, stream));
+  }
   const int h0 = c.kernel - 1;
-  LAUNCH("seanet.stage", launch_stage_rows(xm, b_conv0, act_type, n, U, Md, h0, stream));
+  if (in(0)) LAUNCH("seanet.stage", launch_stage_rows(xm, b_conv0, act_type, n, U, Md, h0, stream));
   const size_t es = act_size;
   auto off = [&](void* base, long long elems) { return (void*)((char*)base + elems * (long long)es); };
   int T = U, C = Md;
-  {  // Conv1d 512->512 K7 (seanet.py:141-143) -> ELU -> input of the first transposed conv
+  if (in(0)) {  // Conv1d 512->512 K7 (seanet.py:141-143) -> ELU -> input of the first transposed conv
     const int rpb = h0 + T;
     GemmEpilogue ep; ep.bias = conv0_b; ep.act_post = ACT_ELU;
     ep.out = off(b_tr[0], 1LL * C); ep.out_map = batched((long long)(1 + T) * C, rpb, T, C);
@@ -310,13 +335,22 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
     if (i == 2 && use_fused_stage2 && act_type == 1 && use_tc &&
         seanet_stage2_fused_supported(C, C2, r, C2 / 2, hc, c.res_kernel, c.last_kernel)) {
       // the whole last stage + final conv in one persistent kernel (seanet_fused.cu): reads b_tr[2], writes PCM
-      LAUNCH("seanet.stage2_fused",
-             launch_seanet_stage2_fused((const bf16*)b_tr[2], stages[2].tr.b16, stages[2].c3.b16, stages[2].c1.b16, fused2_consts,
-                                        (bf16*)b_res[2], (bf16*)b_last, pcm_out, n, T,
-                                        fused_sms > 0 ? std::min(fused_sms, n_sms) : (fused_sms < 0 ? 1 << 30 : n_sms), pdl_enabled(), stream));
-      LAUNCH("seanet.hist_scatter", launch_hist_scatter(tab, d_slot_ids, act_type, n, stream));
+      const int cap = fused_sms > 0 ? std::min(fused_sms, n_sms) : (fused_sms < 0 ? 1 << 30 : n_sms);
+      const int n_a = whole ? n : n / 2;   // streams of segment 3 (a whole pass: one launch over all streams)
+      for (int half = 0; half < 2; ++half) {
+        const int s0 = half == 0 ? 0 : n_a, ns = half == 0 ? n_a : n - n_a;
+        if (!in(3 + half) || ns <= 0) continue;
+        const long long row_in = (long long)s0 * (1 + T) * C, row_hist = (long long)s0 * (2 + 4 * T) * C2;
+        LAUNCH("seanet.stage2_fused",
+               launch_seanet_stage2_fused((const bf16*)b_tr[2] + row_in, stages[2].tr.b16, stages[2].c3.b16, stages[2].c1.b16, fused2_consts,
+                                          (bf16*)b_res[2] + row_hist, (bf16*)b_last + row_hist, pcm_out + (long long)s0 * 4 * T, ns, T,
+                                          cap, pdl_enabled(), stream));
+      }
+      if (in(4)) LAUNCH("seanet.hist_scatter", launch_hist_scatter(tab, d_slot_ids, act_type, n, stream));
       return PTTS_OK;
     }
+    if (!(i < 2 ? in(1 + i) : (in(3) || in(4)))) { T = T2; C = C2; continue; }
+    if (i == 2 && !whole) PTTS_FAIL(PTTS_ESTATE, "segmented Mimi passes need the fused last stage");
     {  // ConvTranspose1d K=2r (seanet.py:147-152): raw -> b_raw (residual), ELU(raw) -> b_res
       const int rpb = 1 + T;
       GemmEpilogue ep; ep.bias = stages[i].tr_b; ep.act_post = ACT_ELU;
@@ -348,6 +382,7 @@ int Engine::mimi_sequence(int n, const float* latents, int frames, float* pcm_ou
     }
     T = T2; C = C2;
   }
+  if (!whole) return PTTS_OK;   // (unfused last stage: whole passes only, checked above)
   LAUNCH("seanet.last_conv", launch_last_conv(b_last, act_type, last_w, last_b, pcm_out, n, T, C, c.last_kernel, stream));
   LAUNCH("seanet.hist_scatter", launch_hist_scatter(tab, d_slot_ids, act_type, n, stream));
   return PTTS_OK;

@@ -374,8 +374,15 @@ __device__ __forceinline__ void ln_combine(const GemmEpilogue& ep, int M, float2
   asm volatile("bar.sync 2, 256;" ::: "memory");   // the 8 epilogue warps
 }
 
+// Register budget: the skinny (SWAP) form belongs to the latency-bound FlowLM chain and must fit on an SM BESIDE one CTA
+// of the persistent row-major kernel of the Mimi branch (320 threads x 88 registers): 320 x 112 + 320 x 88 = 64 000 of
+// the SM's 65 536.  Left to itself ptxas took 168 (no spills at 112), which made co-residency impossible whatever the
+// shared-memory budgets said.  The row-major form needs 72; 96 allows two CTAs per SM.
+#ifndef PTTS_SKINNY_MAXREG
+#define PTTS_SKINNY_MAXREG 112   // -DPTTS_SKINNY_MAXREG=168 rebuilds the old allocation for A/B runs (PTTS_NATIVE_LIB)
+#endif
 template <int BN, bool SWAP, typename TO>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __maxnreg__(SWAP ? PTTS_SKINNY_MAXREG : 96)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_row, const __grid_constant__ CUtensorMap tm_col,
                TcParams P, GemmEpilogue ep) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
