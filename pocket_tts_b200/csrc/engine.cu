@@ -181,6 +181,7 @@ int Engine::init() {
   if (const char* f = getenv("PTTS_KV_SIDE")) use_kv_side_prefetch = f[0] == '1';
   if (const char* f = getenv("PTTS_LNFOLD")) use_ln_fold = !(f[0] == '0');
   if (const char* f = getenv("PTTS_HEAD_GATE")) use_head_gate = f[0] == '1';
+  if (const char* f = getenv("PTTS_HEAD_GATE_MAX")) head_gate_max = atoi(f);
   if (const char* f = getenv("PTTS_SEANET_FUSED")) use_fused_stage2 = !(f[0] == '0');
   if (const char* f = getenv("PTTS_FUSED_SMS")) fused_sms = atoi(f);
   if (const char* f = getenv("PTTS_RESBLOCK_FUSED")) use_fused_resblock = !(f[0] == '0');

@@ -416,9 +416,9 @@ int Engine::flow_graph(int n, int lsd, int par, int j) {
     if (prc != PTTS_OK) return prc;
   }
   const size_t fl = (size_t)n * cfg.ldim;
-  return launch_captured(GraphKey{n, lsd, 0, 2000 + j * 2 + par + (use_head_gate ? 100 : 0)}, stream, [&]() -> int {
+  return launch_captured(GraphKey{n, lsd, 0, 2000 + j * 2 + par + (gate_active ? 100 : 0)}, stream, [&]() -> int {
     commit_out = lat_ring[par] + j * fl;
-    gate_record = use_head_gate && j < 8 ? ev_head[par][j] : nullptr;
+    gate_record = gate_active && j < 8 ? ev_head[par][j] : nullptr;
     const int rc = flow_sequence(n, lsd, noise_grp + j * fl, eos_grp[par] + (size_t)j * n);
     gate_record = nullptr;
     commit_out = nullptr;
@@ -445,12 +445,20 @@ int Engine::mimi_graph_gated(int n, int g, int par, int gate_par) {
   cudaStream_t main_stream = stream;
   stream = stream2;
   // the flow head keeps ceil(n / 8) SMs busy during the gated segments: persistent Mimi grids leave them alone
-  const int head_ctas = (n + 7) / 8;
+  static const int reserve = [] { const char* e = getenv("PTTS_GATE_RESERVE"); return e ? atoi(e) : -1; }();
+  const int head_ctas = reserve >= 0 ? reserve : (n + 7) / 8;
+  // PTTS_GATE_MAP="a,b,c,d": frame slot whose head start opens segments 1..4 (-1: not gated); default 0,1,2,3
+  static int map[MIMI_SEGS] = {-1, 0, 1, 2, 3};
+  static const bool map_read = [] {
+    if (const char* e = getenv("PTTS_GATE_MAP")) sscanf(e, "%d,%d,%d,%d", &map[1], &map[2], &map[3], &map[4]);
+    return true;
+  }();
+  (void)map_read;
   int rc = PTTS_OK;
   for (int seg = 0; seg < MIMI_SEGS && rc == PTTS_OK; ++seg) {
-    n_sms = seg == 0 ? n_sms_mimi : std::max(8, n_sms_mimi - head_ctas);
-    if (seg > 0) {
-      const int j = std::min(seg - 1, g - 1);
+    n_sms = map[seg] < 0 ? n_sms_mimi : std::max(8, n_sms_mimi - head_ctas);
+    if (map[seg] >= 0) {
+      const int j = std::min(map[seg], g - 1);
       cudaError_t e = cudaStreamWaitEvent(stream2, ev_head[gate_par][j], 0);
       if (e != cudaSuccess) { set_error(std::string("cudaStreamWaitEvent: ") + cudaGetErrorString(e)); rc = PTTS_ECUDA; break; }
     }
@@ -597,8 +605,12 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
     const bool do_mimi = part != 3;
     int f0 = 0;
     bool used[2] = {false, false}, used_pcm[2] = {false, false};
-    const bool gate_loop = use_head_gate && do_mimi && part == 0 && use_graphs && use_fused_stage2 && act_type == 1 && use_tc &&
-                           !mega_eligible(n) && head_mode != 0;
+    // Gated only when the call holds at least two full-size groups (1 + 1 + 2 + gmax + gmax frames): graphs that carry
+    // the event-record node launch more slowly from the host, which short calls (8-frame blocks of the batch
+    // scheduler at 256 streams: 2.2 -> 3.4 s per run) cannot hide.
+    const bool gate_loop = use_head_gate && n <= head_gate_max && n_frames >= 4 + 2 * mimi_gmax && do_mimi && part == 0 &&
+                           use_graphs && use_fused_stage2 && act_type == 1 && use_tc && !mega_eligible(n) && head_mode != 0;
+    gate_active = gate_loop;
     struct { bool valid = false; int g = 0, par = 0, f0 = 0; } pend;
     auto enqueue_mimi = [&](int g, int par, int f0m, int gate_par) -> int {
       int rc2;
@@ -659,6 +671,7 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
       used[par] = true;
       f0 += g;
     }
+    gate_active = false;
     if (pend.valid && (rc = enqueue_mimi(pend.g, pend.par, pend.f0, -1)) != PTTS_OK) return rc;   // last group: nothing to gate on
     // the caller synchronises `stream`: make it wait for the Mimi passes and copies still in flight
     for (int q = 0; q < 2; ++q)

@@ -199,6 +199,26 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
   // LSD / Euler integration from the injected noise (flow_lm.py:32-40).  x_0 = noise is read in place: the first
   // input_proj takes `noise` as its operand and the first Euler update writes x_lat = noise + v / lsd.
   const bool fused_sy = lsd == 1 && cond_b_t0 != nullptr;
+  // where the gate opens: 0 = when the AdaLN modulation GEMM has finished (the head kernel starts), 2 = when it is
+  // launched (cond_embed finished; the Mimi kernels arrive ~5-8 us after the event), 1 = before cond_embed (measured: worse,
+  // the Mimi kernels take the SMs the 80-CTA AdaLN GEMM needs)
+  static const int gate_early = [] { const char* e = getenv("PTTS_GATE_EARLY"); return e ? atoi(e) : 2; }();   // 2: 0.4635 -> 0.4594 ms against 0
+  bool gate_joined = true;
+  auto open_gate = [&]() -> int {
+    PTTS_CUDA_CHECK(cudaEventRecord(ev_side_fork, stream));
+    PTTS_CUDA_CHECK(cudaStreamWaitEvent(side_stream, ev_side_fork, 0));
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    PTTS_CUDA_CHECK(cudaStreamIsCapturing(stream, &cs));
+    if (cs == cudaStreamCaptureStatusActive) PTTS_CUDA_CHECK(cudaEventRecordWithFlags(gate_record, side_stream, cudaEventRecordExternal));
+    else PTTS_CUDA_CHECK(cudaEventRecord(gate_record, side_stream));
+    PTTS_CUDA_CHECK(cudaEventRecord(ev_side_join, side_stream));
+    gate_joined = false;
+    return PTTS_OK;
+  };
+  const bool gating = gate_record != nullptr && side_stream != nullptr && head_cluster;
+  if (gate_early == 1 && gating) {
+    if ((rc = open_gate()) != PTTS_OK) return rc;
+  }
   if (fused_sy) {   // sy = SiLU(cond_embed(c) + b + (te(s)+te(t))/2) straight out of the GEMM epilogue (mlp.py:203-208)
     GemmEpilogue ep; ep.bias = cond_b_t0; ep.act_pre = ACT_SILU; ep.out = sy; ep.out_map = plain(F);
     if ((rc = gemm("head.cond_embed", c_cond, true, plain(D), cond_embed, n, ep, true)) != PTTS_OK) return rc;
@@ -209,6 +229,7 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
   for (int s = 0; s < lsd; ++s) {
     const float* x_in = s == 0 ? noise : x_lat;
     if (!fused_sy) LAUNCH("head.silu_add", launch_silu_add(cemb, tcomb + (size_t)s * F, sy, act_type, n, F, stream));
+    if (gate_early == 2 && gating && s == 0 && (rc = open_gate()) != PTTS_OK) return rc;
     {
       GemmEpilogue ep; ep.bias = mod_b; ep.out = mod; ep.out_map = plain(modld);
       if ((rc = gemm("head.adaln_mod", sy, true, plain(F), mod_all, n, ep, false)) != PTTS_OK) return rc;
@@ -226,20 +247,12 @@ int Engine::flow_sequence(int n, int lsd, const float* noise, float* eos_out) {
       const bool last = s == lsd - 1;
       hp.prev_latent = last ? prev_latent : nullptr;
       hp.commit_out = last ? commit_out : nullptr;
-      const bool gate = gate_record != nullptr && s == 0 && side_stream != nullptr;
-      if (gate) {
-        // head-gated Mimi passes: "the flow head of this frame starts" as an external event record node on a side
-        // branch that hangs off the AdaLN modulation GEMM (the main branch keeps its programmatic edge to the head kernel)
-        PTTS_CUDA_CHECK(cudaEventRecord(ev_side_fork, stream));
-        PTTS_CUDA_CHECK(cudaStreamWaitEvent(side_stream, ev_side_fork, 0));
-        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
-        PTTS_CUDA_CHECK(cudaStreamIsCapturing(stream, &cs));
-        if (cs == cudaStreamCaptureStatusActive) PTTS_CUDA_CHECK(cudaEventRecordWithFlags(gate_record, side_stream, cudaEventRecordExternal));
-        else PTTS_CUDA_CHECK(cudaEventRecord(gate_record, side_stream));
-        PTTS_CUDA_CHECK(cudaEventRecord(ev_side_join, side_stream));
-      }
+      // head-gated Mimi passes: "the flow head of this frame starts" as an external event record node on a side branch
+      // that hangs off the AdaLN modulation GEMM (the main branch keeps its programmatic edge to the head kernel)
+      const bool gate = gating && s == 0 && gate_early == 0;
+      if (gate && (rc = open_gate()) != PTTS_OK) return rc;
       auto join_gate = [&]() -> int {
-        if (gate) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_side_join, 0));
+        if (!gate_joined) { PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_side_join, 0)); gate_joined = true; }
         return PTTS_OK;
       };
       if (head_mode == 3 && flow_head_ss_supported(F, Ld, c.flow_depth)) {

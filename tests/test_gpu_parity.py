@@ -242,6 +242,32 @@ def test_mimi_bf16_tensor_core_window_attention(monkeypatch):
     assert snr["1"] >= SNR_BF16 and snr["1"] >= snr["0"] - 3.0
 
 
+def test_head_gated_mimi_passes_are_bit_identical(monkeypatch):
+    """Default bf16 loop for calls of >= 12 frames: the SEANet segments of a Mimi pass wait for the flow-head events
+    of the next group's frames (engine_api.cu: mimi_graph_gated) and the fused last stage runs as two launches over
+    half the streams each.  Scheduling only: latents, EOS logits and PCM must equal the ungated loop's
+    (PTTS_HEAD_GATE=0) bit for bit — 21 frames = groups 1, 1, 2, 4, 4, 4, 4, 1, odd stream count."""
+    case = load_case("gen_2l")
+    orc = oracle_for(2)
+    G, B = 21, 5
+    noise = torch.randn(G, B, 32, generator=torch.Generator().manual_seed(23)) * 0.7 ** 0.5
+    outs = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("PTTS_HEAD_GATE", flag)
+        eng = make_engine(2, precision="bf16")
+        slots = _prefill_streams(eng, orc, [case["cond"][0]] * B, [case["tokens"][0]] * B)
+        pcm = torch.empty(B, G * 1920, device="cuda")
+        lat = torch.empty(G, B, 32, device="cuda")
+        eng.run_frames(slots, noise.cuda().contiguous(), out_pcm=pcm, out_latents=lat)
+        eng.synchronize()
+        h_pcm, h_lat, h_eos = eng.generate_frames(slots, noise[:14])     # host-buffer call continues the same streams
+        outs[flag] = (lat.cpu(), pcm.cpu(), h_pcm.clone(), h_lat.clone(), h_eos.clone())
+        eng.close()
+    for a, b in zip(outs["1"], outs["0"]):
+        assert torch.equal(a, b)
+    assert bool(torch.isfinite(outs["1"][1]).all()) and float(outs["1"][1].abs().max()) > 0
+
+
 def test_voice_kv_export_matches_reference_cache():
     case = load_case("gen_2l")
     orc = oracle_for(2)
