@@ -456,7 +456,8 @@ int Engine::mimi_graph_gated(int n, int g, int par, int gate_par) {
   (void)map_read;
   int rc = PTTS_OK;
   for (int seg = 0; seg < MIMI_SEGS && rc == PTTS_OK; ++seg) {
-    n_sms = map[seg] < 0 ? n_sms_mimi : std::max(8, n_sms_mimi - head_ctas);
+    static const int seg0_sms = [] { const char* e = getenv("PTTS_GATE_SEG0_SMS"); return e ? atoi(e) : 0; }();   // probe: persistent grids of the ungated segment
+    n_sms = map[seg] < 0 ? (seg0_sms > 0 ? std::min(seg0_sms, n_sms_mimi) : n_sms_mimi) : std::max(8, n_sms_mimi - head_ctas);
     if (map[seg] >= 0) {
       const int j = std::min(map[seg], g - 1);
       cudaError_t e = cudaStreamWaitEvent(stream2, ev_head[gate_par][j], 0);
