@@ -417,7 +417,7 @@ def ncu_traffic_bytes(tag, workload):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` summary of THIS
     workload and kernel (profiles/), taken at the start of the generation; None when no such capture exists."""
     import csv
-    f = {("cfg2", "flow.attn_decode"): ROOT / "profiles" / "r01_attn_head_ncu_full_summary.csv"}.get((workload, tag))
+    f = {("cfg2", "flow.attn_decode"): ROOT / "profiles" / "r02_attn_decode_ncu_full_summary.csv"}.get((workload, tag))
     if not f or not f.exists():
         return None
     rows = list(csv.reader(open(f)))
