@@ -908,6 +908,22 @@ cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const 
     // PTTS_MIMI_HALF=1 (probe): one CTA per SM (shared memory padded past half an SM) so that a kernel of the
     // latency-critical FlowLM branch always finds room beside it
     static const bool half_sm = [] { const char* e = getenv("PTTS_MIMI_HALF"); return e && e[0] == '1'; }();
+    // Full passes of large batches stream the window through a double buffer, four CTAs per SM (attn_window_stream_kernel):
+    // Mimi pass 0.658 -> 0.634 ms at 64 streams, 7.36 -> 7.21 ms at 1024.  At 64 streams the full frame step does not gain
+    // (0.464 vs 0.466 ms: the denser kernel disturbs the FlowLM chain as much as it saves), so small batches keep the staged
+    // form.  PTTS_WIN_STREAM=0 / 1 forces one (read per call: the tests compare both).
+    const char* env_stream = getenv("PTTS_WIN_STREAM");
+    const bool stream_form = env_stream ? env_stream[0] != '0' : n >= 96;
+    if (NQ == 64 && !half_sm && stream_form) {
+      static DeviceOnce sattr;
+      if (sattr.first()) {
+        cudaError_t e = cudaFuncSetAttribute(attn_window_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_window_stream_smem());
+        if (e != cudaSuccess) return e;
+      }
+      launch_k(attn_window_stream_kernel, dim3(kv.H, n), WM_THREADS, attn_window_stream_smem(), st, qkv, rope_freqs, offsets,
+               slot_ids, kv, layer, context, (bf16*)out);
+      return cudaGetLastError();
+    }
     const size_t wsmem = half_sm ? std::max<size_t>(attn_window_mma_smem(), 118 * 1024) : attn_window_mma_smem();
     static DeviceOnce attr;
     if (attr.first()) {

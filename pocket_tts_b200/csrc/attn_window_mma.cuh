@@ -253,6 +253,184 @@ attn_window_mma_kernel(const float* __restrict__ qkv, const float* __restrict__ 
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Streaming form for full passes (NQ == 64: four 16-query tiles, one per warp, no key splits).  The staged form above
+// keeps the whole window in shared memory (101 KB: two CTAs per SM, 512 CTAs = 1.7 waves at 64 streams).  Here the
+// pass's own keys / values go to the ring first and the CTA then walks the visible range lo .. off0 + 63 in 64-key
+// blocks through a double buffer (16-byte asynchronous copies of block b + 1 beside the mma work on block b):
+// 46 KB and <= 128 registers, four CTAs per SM, the whole grid resident at once.
+constexpr int WS_STAGE = 64 * WM_LD;   // bf16 elements of one K (or V) block
+
+__global__ void __launch_bounds__(WM_THREADS, 4)
+attn_window_stream_kernel(const float* __restrict__ qkv, const float* __restrict__ freqs, const int* __restrict__ offsets,
+                          const int* __restrict__ slot_ids, KvGeom g, int layer, int context, bf16* __restrict__ out) {
+  constexpr int NQ = 64;
+  extern __shared__ __align__(16) unsigned char wm_smem[];
+  bf16* Qs = reinterpret_cast<bf16*>(wm_smem);   // [64][WM_LD]
+  bf16* KV = Qs + 64 * WM_LD;                    // [2 buffers][K | V][64][WM_LD]
+  pdl_launch_dependents();
+  pdl_wait();                                    // qkv comes from the previous kernel
+  const int h = blockIdx.x, i = blockIdx.y;
+  const int slot = slot_ids[i];
+  const int off0 = offsets[slot];
+  const int r_pass = i * NQ;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int d_model = g.H * 64;
+  const int lo = max(0, off0 - context + 1);
+  const int W = off0 - lo + NQ;                  // visible rows: positions lo .. off0 + 63
+  const int nblk = (W + 63) >> 6;
+
+  // ---- the pass's own tokens: rotate, round, append to the ring; q rotated and staged
+  {
+    const float fr = freqs[lane];
+    constexpr int TB = 4, WARPS = WM_THREADS / 32;
+    for (int t0 = w; t0 < NQ; t0 += TB * WARPS) {
+      float2 qv[TB], kv[TB], vv[TB];
+#pragma unroll
+      for (int u = 0; u < TB; ++u) {
+        const float* row = qkv + (long long)(r_pass + t0 + u * WARPS) * 3 * d_model + h * 64 + 2 * lane;
+        qv[u] = load2(row); kv[u] = load2(row + d_model); vv[u] = load2(row + 2 * d_model);
+      }
+#pragma unroll
+      for (int u = 0; u < TB; ++u) {
+        const int t = t0 + u * WARPS;
+        const float pos = (float)(off0 + t);
+        const float2 q = rope_pair(qv[u], pos, fr);
+        const float2 k = rope_pair(kv[u], pos, fr);
+        reinterpret_cast<uint32_t*>(Qs + t * WM_LD)[lane] = pack_bf16(q.x, q.y);
+        reinterpret_cast<uint32_t*>(kv_row<bf16>(g, layer, slot, 0, h, off0 + t))[lane] = pack_bf16(k.x, k.y);
+        reinterpret_cast<uint32_t*>(kv_row<bf16>(g, layer, slot, 1, h, off0 + t))[lane] = pack_bf16(vv[u].x, vv[u].y);
+      }
+    }
+  }
+  __syncthreads();   // the appended rows are read back below by this CTA's own asynchronous copies (L2)
+
+  auto load_block = [&](int b) {
+    bf16* Kb = KV + (b & 1) * 2 * WS_STAGE;
+    bf16* Vb = Kb + WS_STAGE;
+    for (int idx = threadIdx.x; idx < 64 * 8; idx += WM_THREADS) {
+      const int j = idx >> 3, c = idx & 7, row = b * 64 + j;
+      if (row < W) {
+        cp_async16(Kb + j * WM_LD + c * 8, kv_row<bf16>(g, layer, slot, 0, h, lo + row) + c * 8);
+        cp_async16(Vb + j * WM_LD + c * 8, kv_row<bf16>(g, layer, slot, 1, h, lo + row) + c * 8);
+      } else {   // past the window: finite values (their probabilities are zero)
+        *reinterpret_cast<uint4*>(Kb + j * WM_LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+        *reinterpret_cast<uint4*>(Vb + j * WM_LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  const int qt = w;
+  const int gq = lane >> 2, qq = lane & 3;
+  float o[8][4];
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.0f;
+  float m_run[2] = {-INFINITY, -INFINITY}, l_run[2] = {0.0f, 0.0f};
+  const int p_first = off0 + 16 * qt, p_last = p_first + 15;
+  const int jmin = max(0, p_first - context + 1 - lo), jmax = p_last - lo;
+  const int b_lo = jmin >> 6, b_hi = (jmax >> 6) + 1;       // this warp's visible blocks
+  uint32_t qa[4][4];
+#pragma unroll
+  for (int kk = 0; kk < 4; ++kk) ldsm_x4(qa[kk], Qs + (16 * qt + (lane & 15)) * WM_LD + kk * 16 + (lane >> 4) * 8);
+  const int pq0 = p_first + gq, pq1 = pq0 + 8;
+
+  load_block(0);
+  for (int kb = 0; kb < nblk; ++kb) {
+    if (kb + 1 < nblk) {
+      load_block(kb + 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    if (kb >= b_lo && kb < b_hi) {
+      const bf16* Ks = KV + (kb & 1) * 2 * WS_STAGE;
+      const bf16* Vs = Ks + WS_STAGE;
+      float s[8][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.0f;
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+        for (int np = 0; np < 4; ++np) {
+          uint32_t b[4];
+          const int key = np * 16 + ((lane >> 4) << 3) + (lane & 7);
+          ldsm_x4(b, Ks + key * WM_LD + kk * 16 + ((lane >> 3) & 1) * 8);
+          mma_bf16_16816(s[2 * np], qa[kk], b[0], b[1]);
+          mma_bf16_16816(s[2 * np + 1], qa[kk], b[2], b[3]);
+        }
+      }
+      float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int pj = lo + kb * 64 + nt * 8 + 2 * qq + (e & 1);
+          const int pq = (e < 2) ? pq0 : pq1;
+          const bool vis = pj <= pq && pj > pq - context;
+          const float v = vis ? s[nt][e] * 0.125f : -INFINITY;
+          s[nt][e] = v;
+          mx[e >> 1] = fmaxf(mx[e >> 1], v);
+        }
+      }
+      float corr[2], m_use[2];
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+        mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+        const float m_new = fmaxf(m_run[r], mx[r]);
+        m_use[r] = m_new == -INFINITY ? 0.0f : m_new;
+        corr[r] = __expf(m_run[r] - m_use[r]);
+        m_run[r] = m_new;
+        l_run[r] *= corr[r];
+      }
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        o[nt][0] *= corr[0]; o[nt][1] *= corr[0];
+        o[nt][2] *= corr[1]; o[nt][3] *= corr[1];
+      }
+      uint32_t pa[4][4];
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        const float p0 = __expf(s[nt][0] - m_use[0]), p1 = __expf(s[nt][1] - m_use[0]);
+        const float p2 = __expf(s[nt][2] - m_use[1]), p3 = __expf(s[nt][3] - m_use[1]);
+        l_run[0] += p0 + p1;
+        l_run[1] += p2 + p3;
+        pa[nt >> 1][(nt & 1) * 2] = pack_bf16(p0, p1);
+        pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2, p3);
+      }
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+#pragma unroll
+        for (int np = 0; np < 4; ++np) {
+          uint32_t b[4];
+          const int key = kk * 16 + (((lane >> 3) & 1) << 3) + (lane & 7);
+          ldsm_x4_t(b, Vs + key * WM_LD + np * 16 + (lane >> 4) * 8);
+          mma_bf16_16816(o[2 * np], pa[kk], b[0], b[1]);
+          mma_bf16_16816(o[2 * np + 1], pa[kk], b[2], b[3]);
+        }
+      }
+    }
+    __syncthreads();   // every warp is done with this buffer before block kb + 2 lands in it
+  }
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+    l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
+  }
+  const float inv0 = 1.0f / l_run[0], inv1 = 1.0f / l_run[1];
+  bf16* o0 = out + (long long)(r_pass + 16 * qt + gq) * d_model + h * 64 + 2 * qq;
+  bf16* o1 = o0 + 8LL * d_model;
+#pragma unroll
+  for (int nt = 0; nt < 8; ++nt) {
+    *reinterpret_cast<uint32_t*>(o0 + nt * 8) = pack_bf16(o[nt][0] * inv0, o[nt][1] * inv0);
+    *reinterpret_cast<uint32_t*>(o1 + nt * 8) = pack_bf16(o[nt][2] * inv1, o[nt][3] * inv1);
+  }
+}
+
+inline size_t attn_window_stream_smem() { return (size_t)(64 + 4 * 64) * WM_LD * sizeof(bf16); }
+
 inline size_t attn_window_mma_smem() { return (size_t)(64 + 2 * WM_MAXW) * WM_LD * sizeof(bf16); }
 
 }  // namespace ptts

@@ -268,6 +268,27 @@ def test_head_gated_mimi_passes_are_bit_identical(monkeypatch):
     assert bool(torch.isfinite(outs["1"][1]).all()) and float(outs["1"][1].abs().max()) > 0
 
 
+def test_mimi_window_attention_streaming_equals_staged(monkeypatch):
+    """Full 4-frame Mimi passes run the window attention in its streaming form (64-key blocks through a double buffer,
+    the pass's own keys read back from the ring); PTTS_WIN_STREAM=0 keeps the whole window staged in shared memory.
+    Same blocks, same order of operations: the waveforms must be identical, on 9 streams x the reference's 52 latents
+    (the 250-token window slides and the 512-position ring wraps), and meet the bf16 gate."""
+    case = load_case("gen_english_6l_long")
+    ref = torch.cat([case["pcm"][0], case["pcm_tail"][0]])
+    lat = case["latents"][0]                                  # [52, 32]
+    pcms = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("PTTS_WIN_STREAM", flag)
+        eng = make_engine(6, precision="bf16", max_streams=9)
+        slots = [eng.open_stream() for _ in range(9)]
+        pcms[flag] = eng.mimi_decode_frames(slots, lat[:, None, :].expand(-1, 9, -1).contiguous())
+        eng.close()
+    assert torch.equal(pcms["1"], pcms["0"])
+    snr = min(po.snr_db(ref, pcms["1"][i]) for i in range(9))
+    print(f"bf16 mimi 52 frames x 9 streams, streaming window attention: worst SNR {snr:.1f} dB")
+    assert snr >= SNR_BF16
+
+
 def test_voice_kv_export_matches_reference_cache():
     case = load_case("gen_2l")
     orc = oracle_for(2)
