@@ -896,7 +896,7 @@ namespace ptts {
 
 cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets, const int* slot_ids,
                                KvGeom kv, int layer, int context, int T, void* out, int out_type, int n,
-                               cudaStream_t st, int frames) {
+                               cudaStream_t st, int frames, bool alone) {
   if (kv.D != 64 || !kv.ring || (kv.cap & (kv.cap - 1)) || T < 1 || T > 16 || frames < 1) return cudaErrorInvalidValue;
   if (context + frames * T > kv.cap) return cudaErrorInvalidValue;   // a pass must not wrap onto keys it still reads
   const int maxw = ((context + T - 1 + 7) / 8) * 8;
@@ -913,7 +913,7 @@ cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const 
     // (0.464 vs 0.466 ms: the denser kernel disturbs the FlowLM chain as much as it saves), so small batches keep the staged
     // form.  PTTS_WIN_STREAM=0 / 1 forces one (read per call: the tests compare both).
     const char* env_stream = getenv("PTTS_WIN_STREAM");
-    const bool stream_form = env_stream ? env_stream[0] != '0' : n >= 96;
+    const bool stream_form = env_stream ? env_stream[0] != '0' : (alone || n >= 96);   // alone: no FlowLM chain beside the pass
     if (NQ == 64 && !half_sm && stream_form) {
       static DeviceOnce sattr;
       if (sattr.first()) {

@@ -301,6 +301,7 @@ class Engine {
   cudaEvent_t gate_record = nullptr;         // set around the capture of a FlowLM frame graph
   bool use_head_gate = true;                 // PTTS_HEAD_GATE=0: Mimi passes run whenever their latents are ready
   int head_gate_max = 256;                   // PTTS_HEAD_GATE_MAX: largest batch the gated loop is used for (measured: +5 % at 64 streams x 6 layers, +2.5 % at 256 x 24)
+  bool mimi_alone = false;                   // the Mimi pass being issued has no FlowLM chain beside it (decoder-only calls)
   bool gate_active = false;                  // the running run_frames call uses the gated loop
   float* commit_out = nullptr;               // extra destination of head.commit (pipelined frames)
   std::map<std::string, std::pair<const void*, std::pair<int, long long>>> debug_bufs;  // name -> (ptr,(type,elems per row unit))

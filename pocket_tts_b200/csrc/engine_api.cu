@@ -523,6 +523,8 @@ int Engine::mimi_decode_frames(int n, const int* slots, int n_frames, const floa
   if ((rc = upload_slots(n, slots)) != PTTS_OK) return rc;
   const size_t fl = (size_t)n * cfg.ldim;
   const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
+  mimi_alone = true;
+  struct Reset { bool& b; ~Reset() { b = false; } } reset_alone{mimi_alone};
   for (int f0 = 0; f0 < n_frames;) {
     const int g = std::min(mimi_gmax, n_frames - f0);
     PTTS_CUDA_CHECK(cudaMemcpyAsync(lat_ring[0], latents_any + (size_t)f0 * fl, g * fl * sizeof(float), cudaMemcpyDefault, stream));
@@ -557,6 +559,8 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
   const size_t fs = (size_t)cfg.upsample_stride * cfg.ratios[0] * cfg.ratios[1] * cfg.ratios[2];
   static const int part = [] { const char* e = getenv("PTTS_PROFILE_PART"); return e ? atoi(e) : 0; }();  // 1: FlowLM+head only, 2: Mimi only (profiling)
   const bool piped = use_pipeline && (part == 0 || part >= 3);   // 3: grouped loop without the Mimi branch (profiling)
+  mimi_alone = part == 4;
+  struct Reset { bool& b; ~Reset() { b = false; } } reset_alone{mimi_alone};
   if (!piped) {
     for (int f = 0; f < n_frames; ++f) {
       PTTS_CUDA_CHECK(cudaMemcpyAsync(noise_buf, noise_any + (size_t)f * fl, fl * sizeof(float), cudaMemcpyDefault, stream));

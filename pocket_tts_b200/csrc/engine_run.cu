@@ -97,7 +97,7 @@ int Engine::transformer_layer_common(const LayerW& L, float* hbuf, int rows, int
   }
   if (mimi) {
     LAUNCH("mimi.attn", launch_attn_window(qkvb, rope_freqs, mimi_offsets, d_slot_ids, kv_mimi, li, cfg.mimi_context,
-                                           cfg.upsample_stride, ao, act_type, n, stream, rows / (n * cfg.upsample_stride)));
+                                           cfg.upsample_stride, ao, act_type, n, stream, rows / (n * cfg.upsample_stride), mimi_alone));
   } else if (rows == n) {
     LAUNCH("flow.attn_decode", launch_attn_decode(qkvb, rope_freqs, offsets, d_slot_ids, flow_kv(), li, ao, act_type, n, stream));
   } else {

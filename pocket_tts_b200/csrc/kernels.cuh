@@ -53,7 +53,7 @@ cudaError_t launch_attn_chunk(float* qkv, const float* rope_freqs, const int* of
 // window `context` over the ring cache; the visible window is staged once in shared memory.
 cudaError_t launch_attn_window(const float* qkv, const float* rope_freqs, const int* offsets,
                                const int* slot_ids, KvGeom kv, int layer, int context, int T, void* out,
-                               int out_type, int n, cudaStream_t st, int frames = 1);
+                               int out_type, int n, cudaStream_t st, int frames = 1, bool alone = false);
 
 // offsets[slot_ids[i]] += inc[i] (inc == nullptr: += const_inc)
 cudaError_t launch_advance(int* offsets, const int* slot_ids, const int* inc, int const_inc, int n,
