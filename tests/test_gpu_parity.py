@@ -242,11 +242,13 @@ def test_mimi_bf16_tensor_core_window_attention(monkeypatch):
     assert snr["1"] >= SNR_BF16 and snr["1"] >= snr["0"] - 3.0
 
 
-def test_head_gated_mimi_passes_are_bit_identical(monkeypatch):
+@pytest.mark.parametrize("lsd", [1, 2])
+def test_head_gated_mimi_passes_are_bit_identical(monkeypatch, lsd):
     """Default bf16 loop for calls of >= 12 frames: the SEANet segments of a Mimi pass wait for the flow-head events
     of the next group's frames (engine_api.cu: mimi_graph_gated) and the fused last stage runs as two launches over
     half the streams each.  Scheduling only: latents, EOS logits and PCM must equal the ungated loop's
-    (PTTS_HEAD_GATE=0) bit for bit — 21 frames = groups 1, 1, 2, 4, 4, 4, 4, 1, odd stream count."""
+    (PTTS_HEAD_GATE=0) bit for bit — 21 frames = groups 1, 1, 2, 4, 4, 4, 4, 1, odd stream count, one and two Euler
+    steps per frame (the gate opens once per frame, before the first step's modulation GEMM)."""
     case = load_case("gen_2l")
     orc = oracle_for(2)
     G, B = 21, 5
@@ -254,7 +256,7 @@ def test_head_gated_mimi_passes_are_bit_identical(monkeypatch):
     outs = {}
     for flag in ("1", "0"):
         monkeypatch.setenv("PTTS_HEAD_GATE", flag)
-        eng = make_engine(2, precision="bf16")
+        eng = make_engine(2, precision="bf16", lsd_steps=lsd)
         slots = _prefill_streams(eng, orc, [case["cond"][0]] * B, [case["tokens"][0]] * B)
         pcm = torch.empty(B, G * 1920, device="cuda")
         lat = torch.empty(G, B, 32, device="cuda")
