@@ -633,10 +633,38 @@ int Engine::run_frames(int n, const int* slots, int n_frames, const float* noise
       used_pcm[par] = true;
       return PTTS_OK;
     };
-    for (int k = 0; f0 < n_frames; ++k) {
+    // Group sizes of the call.  Nothing leaves a blocking call before it returns, so the schedule is a throughput
+    // matter only: the call lasts as long as its FlowLM chain plus the Mimi pass of the LAST group, which nothing
+    // overlaps, and only full-size passes can be head-gated.  Policy 1 (default): full-size groups only, the odd
+    // remainder first.  0: the round-1 ramp-up 1, 1, 2, 4, ..; 2: full-size groups, then a ramp-down 2, 1, 1 (a shorter
+    // drain, but three ungated passes beside the last frames); 3: ramp-up and ramp-down.  20-frame call at 64 streams:
+    // 0.4824 / 0.4558 / 0.4791 / 0.4889 ms per step for 0 / 1 / 2 / 3 (PTTS_SCHED, profiles/r02_group_schedule.txt).
+    // Calls shorter than two full groups keep the ramp-up.
+    static const int sched_policy = [] { const char* e = getenv("PTTS_SCHED"); return e ? atoi(e) : 1; }();
+    std::vector<int> sched;
+    {
+      const int G = mimi_gmax;
+      int left = n_frames;
+      const bool down = (sched_policy == 2 || sched_policy == 3) && G == 4 && n_frames >= 2 * G;
+      const bool up = sched_policy == 0 || sched_policy == 3 || n_frames < 2 * G || G != 4;
+      std::vector<int> tail;
+      if (down) { tail = {2, 1, 1}; left -= 4; }
+      if (up) {
+        for (int k = 0; left > 0; ++k) {
+          const int want = k < 2 ? 1 : std::min(G, 1 << std::min(k - 1, 4));
+          const int g = std::min(want, left);
+          sched.push_back(g);
+          left -= g;
+        }
+      } else {
+        if (left % G) { sched.push_back(left % G); left -= left % G; }   // the odd group first: it also starts the Mimi branch early
+        for (; left > 0; left -= G) sched.push_back(G);
+      }
+      sched.insert(sched.end(), tail.begin(), tail.end());
+    }
+    for (int k = 0; k < (int)sched.size(); ++k) {
       const int par = k & 1;
-      const int want = k < 2 ? 1 : std::min(mimi_gmax, 1 << std::min(k - 1, 4));
-      const int g = std::min(want, n_frames - f0);
+      const int g = sched[k];
       if (used[par]) {   // buffers of this parity: the Mimi pass and the copies of group k-2 must have drained them
         if (do_mimi) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_mimi[par], 0));
         if (copies) PTTS_CUDA_CHECK(cudaStreamWaitEvent(stream, ev_copied_lat[par], 0));

@@ -247,7 +247,7 @@ def test_head_gated_mimi_passes_are_bit_identical(monkeypatch, lsd):
     """Default bf16 loop for calls of >= 12 frames: the SEANet segments of a Mimi pass wait for the flow-head events
     of the next group's frames (engine_api.cu: mimi_graph_gated) and the fused last stage runs as two launches over
     half the streams each.  Scheduling only: latents, EOS logits and PCM must equal the ungated loop's
-    (PTTS_HEAD_GATE=0) bit for bit — 21 frames = groups 1, 1, 2, 4, 4, 4, 4, 1, odd stream count, one and two Euler
+    (PTTS_HEAD_GATE=0) bit for bit — 21 frames = groups 1, 4, 4, 4, 4, 4, odd stream count, one and two Euler
     steps per frame (the gate opens once per frame, before the first step's modulation GEMM)."""
     case = load_case("gen_2l")
     orc = oracle_for(2)
@@ -289,6 +289,35 @@ def test_mimi_window_attention_streaming_equals_staged(monkeypatch):
     snr = min(po.snr_db(ref, pcms["1"][i]) for i in range(9))
     print(f"bf16 mimi 52 frames x 9 streams, streaming window attention: worst SNR {snr:.1f} dB")
     assert snr >= SNR_BF16
+
+
+def test_group_schedules_equal_step_sequence():
+    """Group sizes of a blocking call (engine_api.cu): calls shorter than two full groups ramp up (6 frames: 1, 1, 2, 2),
+    longer ones run full-size groups with the odd remainder first (14: 2, 4, 4, 4; 15: 3, 4, 4, 4).  fp32: three
+    consecutive calls on the same streams are bit-identical to 35 single steps — every Mimi pass size 1..4."""
+    case = load_case("gen_2l")
+    orc = oracle_for(2)
+    B, calls = 3, (6, 14, 15)
+    G = sum(calls)
+    eng = make_engine(2, precision="fp32")
+    noise = torch.randn(G, B, 32, generator=torch.Generator().manual_seed(29)) * 0.7 ** 0.5
+    a = _prefill_streams(eng, orc, [case["cond"][0]] * B, [case["tokens"][0]] * B)
+    b = _prefill_streams(eng, orc, [case["cond"][0]] * B, [case["tokens"][0]] * B)
+    lat_a, pcm_a = [], []
+    for g in range(G):
+        lat, _, pcm = eng.step(a, noise[g])
+        lat_a.append(lat); pcm_a.append(pcm)
+    lat_a, pcm_a = torch.stack(lat_a), torch.cat(pcm_a, dim=1)
+    f0 = 0
+    for K in calls:
+        pcm_b = torch.empty(B, K * 1920, device="cuda")
+        lat_b = torch.empty(K, B, 32, device="cuda")
+        eng.run_frames(b, noise[f0:f0 + K].cuda().contiguous(), out_pcm=pcm_b, out_latents=lat_b)
+        eng.synchronize()
+        assert torch.equal(lat_a[f0:f0 + K], lat_b.cpu()), K
+        assert torch.equal(pcm_a[:, f0 * 1920:(f0 + K) * 1920], pcm_b.cpu()), K
+        f0 += K
+    eng.close()
 
 
 def test_voice_kv_export_matches_reference_cache():
@@ -371,7 +400,7 @@ def test_pipelined_run_frames_equals_step_sequence(precision):
     latents and PCM must be bit-identical to the same frames issued one ptts_step at a time."""
     case = load_case("gen_2l")
     orc = oracle_for(2)
-    G, B = 13, 3          # group schedule 1, 1, 2, 4, 4, 1: every Mimi pass size up to the default maximum
+    G, B = 13, 3          # group schedule 1, 4, 4, 4; the second call (1 frame) and test_group_schedules cover the other sizes
     eng = make_engine(2, precision=precision)
     conds = [case["cond"][0]] * B
     toks = [case["tokens"][0]] * B
